@@ -1,0 +1,456 @@
+// C ABI of libithaca_b200.so (include/ithaca_b200.h): handle, device-resident snapshot matrix,
+// NCCL communicator (loaded with dlopen, so the library links against the CUDA runtime only), and the
+// call sequence gram -> eig -> lift that replaces the dense part of ITHACAPOD::getModes
+// (src/ITHACA_CORE/ITHACAPOD/ITHACAPOD.C:132-264).
+#include "../../include/ithaca_b200.h"
+#include "common.cuh"
+#include <dlfcn.h>
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+static thread_local std::string g_create_error;
+
+namespace ib200 {
+
+void set_error(ithaca_b200* h, const std::string& msg)
+{
+    if (h) h->err = msg;
+    else g_create_error = msg;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+
+int make_tmap_2d(ithaca_b200* h, CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
+                 uint64_t pitch_bytes, uint32_t box_inner, uint32_t box_outer, bool swizzle128)
+{
+    if (!g_encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess || !fn) {
+            set_error(h, "cuTensorMapEncodeTiled entry point not available");
+            return IB200_ERR_CUDA;
+        }
+        g_encode = (EncodeTiledFn)fn;
+    }
+    cuuint64_t dims[2] = {inner, outer};
+    cuuint64_t strides[1] = {pitch_bytes};
+    cuuint32_t box[2] = {box_inner, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<void*>(base), dims, strides, box,
+                          estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                          CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char buf[160];
+        snprintf(buf, sizeof(buf), "cuTensorMapEncodeTiled failed (%d): inner=%llu outer=%llu pitch=%llu box=%ux%u",
+                 (int)r, (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)pitch_bytes,
+                 box_inner, box_outer);
+        set_error(h, buf);
+        return IB200_ERR_CUDA;
+    }
+    return IB200_OK;
+}
+
+// ---- NCCL through dlopen: only the five entry points the path needs ----
+struct NcclApi {
+    void* lib = nullptr;
+    int (*GetUniqueId)(void*) = nullptr;
+    int (*CommInitRank)(void**, int, /* ncclUniqueId by value: 128 bytes */ struct Id128, int) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+struct Id128 { char b[128]; };
+static NcclApi g_nccl;
+
+static int load_nccl(ithaca_b200* h)
+{
+    if (g_nccl.lib) return IB200_OK;
+    const char* names[] = {getenv("ITHACA_B200_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+    void* lib = nullptr;
+    for (const char* n : names) {
+        if (!n || !*n) continue;
+        lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (lib) break;
+    }
+    if (!lib) {
+        set_error(h, "cannot dlopen libnccl.so.2 (set ITHACA_B200_NCCL_LIB)");
+        return IB200_ERR_NCCL;
+    }
+    g_nccl.GetUniqueId = (decltype(g_nccl.GetUniqueId))dlsym(lib, "ncclGetUniqueId");
+    g_nccl.CommInitRank = (decltype(g_nccl.CommInitRank))dlsym(lib, "ncclCommInitRank");
+    g_nccl.AllReduce = (decltype(g_nccl.AllReduce))dlsym(lib, "ncclAllReduce");
+    g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy))dlsym(lib, "ncclCommDestroy");
+    g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString))dlsym(lib, "ncclGetErrorString");
+    if (!g_nccl.GetUniqueId || !g_nccl.CommInitRank || !g_nccl.AllReduce || !g_nccl.CommDestroy) {
+        set_error(h, "libnccl is missing required symbols");
+        return IB200_ERR_NCCL;
+    }
+    g_nccl.lib = lib;
+    return IB200_OK;
+}
+
+static int nccl_fail(ithaca_b200* h, const char* what, int rc)
+{
+    std::string msg = std::string(what) + " failed: ";
+    msg += g_nccl.GetErrorString ? g_nccl.GetErrorString(rc) : "nccl error";
+    set_error(h, msg);
+    return IB200_ERR_NCCL;
+}
+
+// In-place sum all-reduce of `count` doubles on the handle's stream (no-op for a single rank).
+int allreduce_sum(ithaca_b200* h, double* dbuf, size_t count)
+{
+    if (h->nranks <= 1 || !h->nccl_comm) return IB200_OK;
+    const int ncclFloat64 = 8, ncclSum = 0;
+    int rc = g_nccl.AllReduce(dbuf, dbuf, count, ncclFloat64, ncclSum, h->nccl_comm, h->stream);
+    if (rc) return nccl_fail(h, "ncclAllReduce", rc);
+    return IB200_OK;
+}
+
+static int ensure(ithaca_b200* h, double** p, size_t* cap, size_t bytes)
+{
+    if (bytes <= *cap) return IB200_OK;
+    if (*p) cudaFree(*p);
+    *p = nullptr;
+    *cap = 0;
+    IB_CUDA(h, cudaMalloc(p, bytes));
+    *cap = bytes;
+    return IB200_OK;
+}
+
+static int ensure_mats(ithaca_b200* h, int m)
+{
+    if (m <= h->mat_cap) return IB200_OK;
+    for (double** p : {&h->dG, &h->dQ, &h->dW, &h->dEvals}) {
+        if (*p) cudaFree(*p);
+        *p = nullptr;
+    }
+    h->mat_cap = 0;
+    const size_t mm = (size_t)m * m * sizeof(double);
+    IB_CUDA(h, cudaMalloc(&h->dG, mm));
+    IB_CUDA(h, cudaMalloc(&h->dQ, mm));
+    IB_CUDA(h, cudaMalloc(&h->dW, mm));
+    IB_CUDA(h, cudaMalloc(&h->dEvals, (size_t)m * sizeof(double)));
+    h->mat_cap = m;
+    return IB200_OK;
+}
+
+static void tstart(ithaca_b200* h, int which) { cudaEventRecord(h->timers[which].a, h->stream); }
+static void tstop(ithaca_b200* h, int which)
+{
+    cudaEventRecord(h->timers[which].b, h->stream);
+    h->timers[which].used = true;
+}
+
+}  // namespace ib200
+
+using namespace ib200;
+
+extern "C" {
+
+int ithaca_b200_create(ithaca_b200_t** out, int device)
+{
+    if (!out) return IB200_ERR_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        set_error(nullptr, std::string("no CUDA device: ") + cudaGetErrorString(e) +
+                               " (libithaca_b200 has no CPU fallback)");
+        return IB200_ERR_CUDA;
+    }
+    if (device < 0 || device >= ndev) {
+        set_error(nullptr, "device index out of range");
+        return IB200_ERR_ARG;
+    }
+    cudaDeviceProp prop;
+    e = cudaGetDeviceProperties(&prop, device);
+    if (e != cudaSuccess) {
+        set_error(nullptr, cudaGetErrorString(e));
+        return IB200_ERR_CUDA;
+    }
+    if (prop.major != 10) {
+        set_error(nullptr, "libithaca_b200 is built for sm_100a only; device is sm_" +
+                               std::to_string(prop.major) + std::to_string(prop.minor));
+        return IB200_ERR_CUDA;
+    }
+    ithaca_b200* h = new ithaca_b200();
+    h->device = device;
+    h->num_sms = prop.multiProcessorCount;
+    if (cudaSetDevice(device) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking) != cudaSuccess) {
+        set_error(nullptr, "cannot create stream");
+        delete h;
+        return IB200_ERR_CUDA;
+    }
+    for (int i = 0; i < T_COUNT; i++) {
+        cudaEventCreate(&h->timers[i].a);
+        cudaEventCreate(&h->timers[i].b);
+    }
+    cudaMalloc(&h->dFlags, 64 * sizeof(int));
+    *out = h;
+    return IB200_OK;
+}
+
+int ithaca_b200_destroy(ithaca_b200_t* h)
+{
+    if (!h) return IB200_OK;
+    cudaSetDevice(h->device);
+    cudaStreamSynchronize(h->stream);
+    if (h->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->nccl_comm);
+    for (void* p : {(void*)h->dV, (void*)h->dS, (void*)h->dG, (void*)h->dWs, (void*)h->dQ, (void*)h->dW,
+                    (void*)h->dEvals, (void*)h->dQr, (void*)h->dPhi, (void*)h->dNormPart, (void*)h->dNorm,
+                    h->dJobs, (void*)h->dFlags})
+        if (p) cudaFree(p);
+    for (int i = 0; i < T_COUNT; i++) {
+        cudaEventDestroy(h->timers[i].a);
+        cudaEventDestroy(h->timers[i].b);
+    }
+    cudaStreamDestroy(h->stream);
+    delete h;
+    return IB200_OK;
+}
+
+const char* ithaca_b200_last_error(const ithaca_b200_t* h) { return h ? h->err.c_str() : g_create_error.c_str(); }
+
+void* ithaca_b200_stream(ithaca_b200_t* h) { return h ? (void*)h->stream : nullptr; }
+
+int64_t ithaca_b200_launch_count(ithaca_b200_t* h, int reset)
+{
+    if (!h) return 0;
+    int64_t n = h->launches;
+    if (reset) h->launches = 0;
+    return n;
+}
+
+int ithaca_b200_timings(ithaca_b200_t* h, double* out, int n)
+{
+    if (!h || !out) return IB200_ERR_ARG;
+    cudaSetDevice(h->device);
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    for (int i = 0; i < n; i++) {
+        out[i] = 0.0;
+        if (i < T_COUNT && h->timers[i].used) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, h->timers[i].a, h->timers[i].b) == cudaSuccess) out[i] = ms;
+        }
+    }
+    return IB200_OK;
+}
+
+int ithaca_b200_nccl_unique_id(void* id128)
+{
+    if (!id128) return IB200_ERR_ARG;
+    int rc = load_nccl(nullptr);
+    if (rc) return rc;
+    rc = g_nccl.GetUniqueId(id128);
+    if (rc) return nccl_fail(nullptr, "ncclGetUniqueId", rc);
+    return IB200_OK;
+}
+
+int ithaca_b200_comm_init(ithaca_b200_t* h, const void* id128, int rank, int nranks)
+{
+    if (!h || nranks < 1 || rank < 0 || rank >= nranks) return IB200_ERR_ARG;
+    h->rank = rank;
+    h->nranks = nranks;
+    if (nranks == 1) return IB200_OK;
+    if (!id128) { set_error(h, "comm_init: id128 is null"); return IB200_ERR_ARG; }
+    int rc = load_nccl(h);
+    if (rc) return rc;
+    cudaSetDevice(h->device);
+    Id128 id;
+    memcpy(&id, id128, sizeof(id));
+    rc = g_nccl.CommInitRank(&h->nccl_comm, nranks, id, rank);
+    if (rc) return nccl_fail(h, "ncclCommInitRank", rc);
+    return IB200_OK;
+}
+
+int ithaca_b200_cell_range(int64_t nCells, int rank, int nranks, int64_t* begin, int64_t* end)
+{
+    if (nCells < 0 || nranks < 1 || rank < 0 || rank >= nranks || !begin || !end) return IB200_ERR_ARG;
+    *begin = (int64_t)(((__int128)rank * nCells) / nranks);
+    *end = (int64_t)(((__int128)(rank + 1) * nCells) / nranks);
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_set_volumes(ithaca_b200_t* h, const double* V, int64_t nCells)
+{
+    if (!h || !V || nCells <= 0) { set_error(h, "pod_set_volumes: bad argument"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    if (nCells > h->dV_cap) {
+        if (h->dV) cudaFree(h->dV);
+        h->dV = nullptr; h->dV_cap = 0;
+        IB_CUDA(h, cudaMalloc(&h->dV, (size_t)nCells * sizeof(double)));
+        h->dV_cap = nCells;
+    }
+    IB_CUDA(h, cudaMemcpyAsync(h->dV, V, (size_t)nCells * sizeof(double), cudaMemcpyDefault, h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->nCells = nCells;
+    h->have_gram = h->have_eig = h->have_lift = false;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_upload(ithaca_b200_t* h, const double* const* snap_ptrs, int m, int dim, int64_t nCells)
+{
+    if (!h || !snap_ptrs || m <= 0 || dim <= 0 || nCells <= 0) { set_error(h, "pod_upload: bad argument"); return IB200_ERR_ARG; }
+    if (h->nCells != nCells) { set_error(h, "pod_upload: nCells differs from pod_set_volumes"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    const int64_t Nd = nCells * dim;
+    const int64_t ld = (Nd + 15) / 16 * 16;
+    int rc = ensure(h, &h->dS, &h->dS_cap, (size_t)ld * m * sizeof(double));
+    if (rc) return rc;
+    tstart(h, T_UPLOAD);
+    for (int j = 0; j < m; j++) {
+        if (!snap_ptrs[j]) { set_error(h, "pod_upload: null snapshot pointer"); return IB200_ERR_ARG; }
+        IB_CUDA(h, cudaMemcpyAsync(h->dS + (size_t)j * ld, snap_ptrs[j], (size_t)Nd * sizeof(double),
+                                   cudaMemcpyDefault, h->stream));
+    }
+    tstop(h, T_UPLOAD);
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->m = m; h->dim = dim; h->Nd = Nd; h->ld = ld;
+    h->have_gram = h->have_eig = h->have_lift = false;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_gram(ithaca_b200_t* h, double* G_out)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->dS || h->m <= 0 || !h->dV) { set_error(h, "pod_gram: upload snapshots and volumes first"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    int rc = ensure_mats(h, h->m);
+    if (rc) return rc;
+    tstart(h, T_GRAM);
+    rc = gram_launch(h);
+    if (rc) return rc;
+    tstop(h, T_GRAM);
+    tstart(h, T_ALLREDUCE);
+    rc = allreduce_sum(h, h->dG, (size_t)h->m * h->m);
+    if (rc) return rc;
+    tstop(h, T_ALLREDUCE);
+    if (G_out)
+        IB_CUDA(h, cudaMemcpyAsync(G_out, h->dG, (size_t)h->m * h->m * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->have_gram = true;
+    h->have_eig = h->have_lift = false;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_set_gram(ithaca_b200_t* h, const double* G, int m)
+{
+    if (!h || !G || m <= 0) return IB200_ERR_ARG;
+    cudaSetDevice(h->device);
+    int rc = ensure_mats(h, m);
+    if (rc) return rc;
+    if (h->m != m) { h->m = m; h->Nd = 0; }  // detached from any snapshot matrix
+    IB_CUDA(h, cudaMemcpyAsync(h->dG, G, (size_t)m * m * sizeof(double), cudaMemcpyDefault, h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->have_gram = true;
+    h->have_eig = h->have_lift = false;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_eig(ithaca_b200_t* h, int r, double* evals_out, double* evecs_out, int* sweeps_out)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->have_gram) { set_error(h, "pod_eig: no Gram matrix (call pod_gram first)"); return IB200_ERR_ARG; }
+    if (r < 0 || r > h->m) { set_error(h, "pod_eig: The number of requested modes cannot be bigger than the number of Snapshots"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    int sweeps = 0;
+    tstart(h, T_EIG);
+    int rc = eig_launch(h, &sweeps);
+    if (rc) return rc;
+    tstop(h, T_EIG);
+    if (sweeps_out) *sweeps_out = sweeps;
+    if (evals_out)
+        IB_CUDA(h, cudaMemcpyAsync(evals_out, h->dEvals, (size_t)h->m * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (evecs_out && r > 0)
+        IB_CUDA(h, cudaMemcpyAsync(evecs_out, h->dQ, (size_t)h->m * r * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->have_eig = true;
+    h->have_lift = false;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_postprocess_eigenvalues(const double* evals_all, int m, int nmodes, int solver,
+                                            double* evals_norm_out, double* cum_out, int* n_out)
+{
+    if (!evals_all || m <= 0 || nmodes <= 0 || nmodes > m || !evals_norm_out || !n_out) return IB200_ERR_ARG;
+    // ITHACAPOD.C:169 (spectra keeps nmodes values) / :179 (eigen keeps all m)
+    const int n = (solver == 0) ? nmodes : m;
+    double mn = evals_all[0];
+    for (int i = 0; i < n; i++) mn = std::min(mn, evals_all[i]);
+    // ITHACAPOD.C:182-186
+    const double shift = (mn < 0) ? 2 * std::fabs(mn) : 0.0;
+    double sum = 0.0;
+    for (int i = 0; i < n; i++) { evals_norm_out[i] = evals_all[i] + shift; sum += evals_norm_out[i]; }
+    // ITHACAPOD.C:281-287
+    double c = 0.0;
+    for (int i = 0; i < n; i++) {
+        evals_norm_out[i] /= sum;
+        c += evals_norm_out[i];
+        if (cum_out) cum_out[i] = c;
+    }
+    *n_out = n;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_lift(ithaca_b200_t* h, int r, int norm_kind, double* const* mode_ptrs, double* normfact_out)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->have_eig || h->Nd <= 0) { set_error(h, "pod_lift: call pod_upload, pod_gram and pod_eig first"); return IB200_ERR_ARG; }
+    if (r <= 0 || r > h->m) { set_error(h, "pod_lift: The number of requested modes cannot be bigger than the number of Snapshots"); return IB200_ERR_ARG; }
+    if (norm_kind != 0 && norm_kind != 1) { set_error(h, "pod_lift: The PODnorm can be only L2 or Frobenius"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    int rc = lift_launch(h, r, norm_kind);
+    if (rc) return rc;
+    tstart(h, T_DOWNLOAD);
+    if (mode_ptrs)
+        for (int i = 0; i < r; i++) {
+            if (!mode_ptrs[i]) { set_error(h, "pod_lift: null mode pointer"); return IB200_ERR_ARG; }
+            IB_CUDA(h, cudaMemcpyAsync(mode_ptrs[i], h->dPhi + (size_t)i * h->ld, (size_t)h->Nd * sizeof(double),
+                                       cudaMemcpyDefault, h->stream));
+        }
+    if (normfact_out)
+        IB_CUDA(h, cudaMemcpyAsync(normfact_out, h->dNorm, (size_t)r * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    tstop(h, T_DOWNLOAD);
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->have_lift = true;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_lift_patch(ithaca_b200_t* h, const double* Sbc, int64_t rows, double* out)
+{
+    if (!h || !Sbc || !out || rows <= 0) return IB200_ERR_ARG;
+    if (!h->have_lift) { set_error(h, "pod_lift_patch: call pod_lift first"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    double *dIn = nullptr, *dOut = nullptr;
+    IB_CUDA(h, cudaMalloc(&dIn, (size_t)rows * h->m * sizeof(double)));
+    if (cudaMalloc(&dOut, (size_t)rows * h->r * sizeof(double)) != cudaSuccess) {
+        cudaFree(dIn);
+        set_error(h, "pod_lift_patch: out of device memory");
+        return IB200_ERR_CUDA;
+    }
+    int rc = IB200_OK;
+    do {
+        if (cudaMemcpyAsync(dIn, Sbc, (size_t)rows * h->m * sizeof(double), cudaMemcpyDefault, h->stream) != cudaSuccess) { rc = IB200_ERR_CUDA; break; }
+        rc = lift_patch_launch(h, dIn, rows, dOut);
+        if (rc) break;
+        if (cudaMemcpyAsync(out, dOut, (size_t)rows * h->r * sizeof(double), cudaMemcpyDefault, h->stream) != cudaSuccess) { rc = IB200_ERR_CUDA; break; }
+        if (cudaStreamSynchronize(h->stream) != cudaSuccess) { rc = IB200_ERR_CUDA; break; }
+    } while (0);
+    if (rc == IB200_ERR_CUDA && h->err.empty()) set_error(h, cudaGetErrorString(cudaGetLastError()));
+    cudaFree(dIn);
+    cudaFree(dOut);
+    return rc;
+}
+
+}  // extern "C"

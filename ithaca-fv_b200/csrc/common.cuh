@@ -1,0 +1,167 @@
+// Shared device helpers for libithaca_b200 (sm_100a only): mbarrier / TMA PTX wrappers, the FP64
+// tensor-core instruction, and the handle layout. Internal; the public boundary is include/ithaca_b200.h.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+namespace ib200 {
+
+// ---- FP64 tensor core: DMMA.8x8x4 is the only native f64 MMA shape on sm_100a (larger PTX shapes
+// are lowered to it, checked with cuobjdump). Fragment layout (lane = 4*g + t):
+//   A (8x4, row-major): a = A[g][t]     B (4x8, col-major): b = B[t][g]
+//   C/D (8x8): c0 = C[g][2t], c1 = C[g][2t+1]
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b)
+{
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p)
+{
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init()
+{
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+        : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity)
+{
+    while (!mbar_try_wait(bar, parity)) { }
+}
+
+// TMA: 2-D tiled bulk tensor load global -> shared, completion counted in bytes on an mbarrier.
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tmap, int c0, int c1,
+                                            uint64_t* bar)
+{
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+        ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tmap)
+{
+    asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
+}
+
+// Byte offset of element (row, k) inside a TMA box whose rows are 16 doubles (128 B) written with
+// CU_TENSOR_MAP_SWIZZLE_128B into 1024-B aligned shared memory: the 16-B chunk index is XOR-ed with
+// (row & 7).
+__device__ __forceinline__ uint32_t swz128(uint32_t row, uint32_t k)
+{
+    return row * 128u + ((((k >> 1) ^ (row & 7u)) << 4) | ((k & 1u) << 3));
+}
+
+}  // namespace ib200
+
+// ------------------------------------------------------------------------------------------------
+// Host side
+// ------------------------------------------------------------------------------------------------
+#define IB_CUDA(h, call)                                                                          \
+    do {                                                                                          \
+        cudaError_t e__ = (call);                                                                 \
+        if (e__ != cudaSuccess) {                                                                 \
+            ib200::set_error(h, std::string(#call) + ": " + cudaGetErrorString(e__));             \
+            return IB200_ERR_CUDA;                                                                \
+        }                                                                                         \
+    } while (0)
+
+struct ithaca_b200;
+
+namespace ib200 {
+void set_error(ithaca_b200* h, const std::string& msg);
+
+// cuTensorMapEncodeTiled through cudaGetDriverEntryPoint (no link-time libcuda dependency).
+// 2-D FP64 tensor: inner dimension `inner` (contiguous), outer dimension `outer` with `pitch_bytes`.
+int make_tmap_2d(ithaca_b200* h, CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
+                 uint64_t pitch_bytes, uint32_t box_inner, uint32_t box_outer, bool swizzle128);
+
+struct Timer {
+    cudaEvent_t a = nullptr, b = nullptr;
+    bool used = false;
+};
+enum { T_UPLOAD = 0, T_GRAM, T_ALLREDUCE, T_EIG, T_LIFT, T_SCALE, T_DOWNLOAD, T_GRAMK, T_COUNT };
+
+}  // namespace ib200
+
+// ---- launchers implemented in the .cu files ----
+namespace ib200 {
+// gram.cu: ws/partials live in the handle. Writes the full symmetric m x m Gram (col-major) to dG.
+int gram_launch(ithaca_b200* h);
+// eig.cu: one-sided Jacobi of h->dG. Fills h->dEvals (m, descending) and h->dQ (m x m col-major, sorted).
+int eig_launch(ithaca_b200* h, int* sweeps);
+// lift.cu
+int lift_launch(ithaca_b200* h, int r, int norm_kind);
+int lift_patch_launch(ithaca_b200* h, const double* dSbc, int64_t rows, double* dOut);
+}  // namespace ib200
+
+typedef int (*ib200_allreduce_fn)(void* comm, const void* send, void* recv, size_t count, int dtype,
+                                  int op, void* comm2, cudaStream_t stream);
+
+struct ithaca_b200 {
+    int device = 0;
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    int64_t launches = 0;
+    ib200::Timer timers[ib200::T_COUNT];
+
+    // communicator (NCCL loaded with dlopen; null = single rank)
+    void* nccl_comm = nullptr;
+    int rank = 0, nranks = 1;
+
+    // POD state
+    int64_t nCells = 0;  // cells of this rank
+    int dim = 0, m = 0;
+    int64_t Nd = 0;      // nCells*dim
+    int64_t ld = 0;      // leading dimension (doubles) of dS, multiple of 16
+    double* dV = nullptr;
+    int64_t dV_cap = 0;
+    double* dS = nullptr;  // snapshot matrix, m columns of ld doubles
+    size_t dS_cap = 0;
+    double* dG = nullptr;  // m x m Gram (col-major, symmetric, all-reduced)
+    double* dWs = nullptr; // split-K workspace
+    size_t dWs_cap = 0;
+    double* dQ = nullptr;      // m x m eigenvectors (col-major, sorted descending)
+    double* dW = nullptr;      // Jacobi work matrix
+    double* dEvals = nullptr;  // m
+    int mat_cap = 0;           // capacity (m) of dG/dQ/dW/dEvals
+    bool have_gram = false, have_eig = false;
+    // lift state
+    int r = 0, rpad = 0;
+    double* dQr = nullptr;  // [m][rpad+2] k-major copy of Q_r for the lift kernel
+    size_t dQr_cap = 0;
+    double* dPhi = nullptr;  // modes, r columns of ld doubles
+    size_t dPhi_cap = 0;
+    double* dNormPart = nullptr;
+    size_t dNormPart_cap = 0;
+    double* dNorm = nullptr;  // rpad doubles: squared norms then norm factors
+    int norm_cap = 0;
+    bool have_lift = false;
+    void* dJobs = nullptr;
+    size_t dJobs_cap = 0;
+    int* dFlags = nullptr;
+};

@@ -1,0 +1,212 @@
+// TEST INFRASTRUCTURE ONLY -- never linked, imported or executed by the product path.
+//
+// pod_ref: the reference's OWN dense arithmetic for ITHACAPOD::getModes, compiled against the
+// reference's OWN vendored Eigen (src/thirdparty/Eigen) and Spectra (src/thirdparty/spectra)
+// headers where they lie under /root/reference (see oracle/Makefile; output goes to oracle/_ref/).
+// Only the OpenFOAM PtrList<GeometricField> -> raw pointer marshalling is restated, because
+// OpenFOAM itself is not installed in this image. Every expression below cites the reference
+// line it follows (paths relative to /root/reference/src/ITHACA_CORE).
+//
+//   Gram        : ITHACAutilities/ITHACAcoeffsMass.C:85-105   (both branches, threshold on V.size())
+//   V repetition: ITHACAutilities/ITHACAcoeffsMass.C:312-326, EigenFunctions/EigenFunctions.C:125-143
+//   eigensolve  : ITHACAPOD/ITHACAPOD.C:157-180               (Spectra / Eigen)
+//   neg. shift  : ITHACAPOD/ITHACAPOD.C:182-186
+//   lift        : ITHACAPOD/ITHACAPOD.C:194
+//   norm factors: ITHACAPOD/ITHACAPOD.C:196-243
+//   BC lift     : ITHACAPOD/ITHACAPOD.C:245-264
+//   eigenvalue normalisation / cumulative sum: ITHACAPOD/ITHACAPOD.C:281-287
+//
+// Used by: tests/ (checker), tests/golden/make_golden.py (fixture generator),
+// bench.py cpu_baseline / --impl reference (timed CPU baseline). Nothing else.
+
+#include <Eigen/Eigen>
+#include <Spectra/SymEigsSolver.h>
+#include <Spectra/MatOp/DenseSymMatProd.h>
+#include <cmath>
+#include <cstring>
+
+typedef long long i64;
+typedef Eigen::Map<const Eigen::MatrixXd> CMap;
+
+// getMassMatrixFV (ITHACAcoeffsMass.C:312-326) + repeatElements (EigenFunctions.C:125-143)
+static Eigen::VectorXd mass_fv(const double* Vc, i64 Nc, int dim)
+{
+    Eigen::VectorXd out(Nc * dim);
+    for (i64 i = 0; i < Nc; i++)
+        for (int r = 0; r < dim; r++)
+            out(i * dim + r) = Vc[i];
+    return out;
+}
+
+// branch: -1 = the reference's own rule (V.size() > 1e6 -> loop), 0 = force GEMM, 1 = force loop
+static Eigen::MatrixXd gram(const CMap& F, const Eigen::VectorXd& V, int branch)
+{
+    const int Msize = (int)F.cols();
+    Eigen::MatrixXd M = Eigen::MatrixXd::Zero(Msize, Msize);
+    bool loop = (branch < 0) ? (V.size() > 1e6) : (branch == 1);
+    if (loop)
+    {
+        // ITHACAcoeffsMass.C:95-101
+        for (i64 i = 0; i < V.size(); i++)
+        {
+            M += V(i) * F.transpose().topRows(Msize).col(i) * F.leftCols(Msize).row(i);
+        }
+    }
+    else
+    {
+        // ITHACAcoeffsMass.C:104
+        M = F.transpose().topRows(Msize) * V.asDiagonal() * F.leftCols(Msize);
+    }
+    return M;
+}
+
+extern "C" {
+
+// G_out: m x m col-major.  S: Nd x m col-major (Nd = dim*Nc), AoS-interleaved components.
+int podref_gram(const double* S, i64 Nc, int dim, int m, const double* Vc, int branch,
+                double* G_out)
+{
+    CMap F(S, Nc * dim, m);
+    Eigen::VectorXd V = mass_fv(Vc, Nc, dim);
+    Eigen::MatrixXd M = gram(F, V, branch);
+    std::memcpy(G_out, M.data(), sizeof(double) * m * m);
+    return 0;
+}
+
+// Eigensolve + post-processing only, on a given Gram matrix (ITHACAPOD.C:157-186).
+// solver: 0 = spectra, 1 = eigen. evals_out must hold m doubles; *n_evals = nmodes (spectra) or m (eigen).
+// evecs_out: m x nmodes col-major. Returns 0 on success, 1 if the solver reports failure.
+int podref_eig(const double* G, int m, int nmodes, int solver, double* evals_out, int* n_evals,
+               double* evecs_out)
+{
+    Eigen::MatrixXd _corMatrix = CMap(G, m, m);
+    Eigen::VectorXd eigenValueseig;
+    Eigen::MatrixXd eigenVectoreig;
+    if (solver == 0)
+    {
+        int ncv = m;
+        Spectra::DenseSymMatProd<double> op(_corMatrix);
+        Spectra::SymEigsSolver<Spectra::DenseSymMatProd<double>> es(op, nmodes, ncv);
+        es.init();
+        es.compute(Spectra::SortRule::LargestAlge);
+        if (es.info() != Spectra::CompInfo::Successful) return 1;
+        eigenVectoreig = es.eigenvectors().real();
+        eigenValueseig = es.eigenvalues().real();
+    }
+    else
+    {
+        Eigen::SelfAdjointEigenSolver<Eigen::MatrixXd> esEg;
+        esEg.compute(_corMatrix);
+        if (esEg.info() != Eigen::Success) return 1;
+        eigenVectoreig = esEg.eigenvectors().real().rowwise().reverse().leftCols(nmodes);
+        eigenValueseig = esEg.eigenvalues().real().array().reverse();
+    }
+    if (eigenValueseig.array().minCoeff() < 0)
+    {
+        eigenValueseig = eigenValueseig.array() + 2 * std::abs(eigenValueseig.array().minCoeff());
+    }
+    *n_evals = (int)eigenValueseig.size();
+    std::memcpy(evals_out, eigenValueseig.data(), sizeof(double) * eigenValueseig.size());
+    std::memcpy(evecs_out, eigenVectoreig.data(), sizeof(double) * m * nmodes);
+    return 0;
+}
+
+// The whole dense part of getModes (ITHACAPOD.C:132-287), serial (Pstream::parRun() == false).
+//   norm: 0 = "L2", 1 = "Frobenius".  (Quirk: the Gram is V-weighted under both, ITHACAcoeffsMass.C:87-105.)
+//   Sbc : all boundary patches stacked row-wise, nbc x m col-major (may be null when nbc == 0); the
+//         reference processes each patch separately (ITHACAPOD.C:245-264) with per-row arithmetic
+//         identical to the stacked form.
+// Outputs (any may be null): G m*m; evals (post-shift, un-normalised) m; evals_norm, cum (n_evals
+// entries); evecs m*nmodes; normfact nmodes; modes Nd*nmodes col-major; modes_bc nbc*nmodes.
+int podref_getmodes(const double* S, i64 Nc, int dim, int m, const double* Vc, int nmodes,
+                    int solver, int norm, int branch, const double* Sbc, i64 nbc,
+                    double* G_out, double* evals_out, int* n_evals, double* evals_norm_out,
+                    double* cum_out, double* evecs_out, double* normfact_out, double* modes_out,
+                    double* modes_bc_out)
+{
+    const i64 Nd = Nc * dim;
+    CMap SnapMatrix(S, Nd, m);
+    Eigen::VectorXd V = mass_fv(Vc, Nc, dim);
+    Eigen::MatrixXd _corMatrix = gram(SnapMatrix, V, branch);
+    if (G_out) std::memcpy(G_out, _corMatrix.data(), sizeof(double) * m * m);
+
+    Eigen::VectorXd ev(m);
+    Eigen::MatrixXd eigenVectoreig(m, nmodes);
+    int ne = 0;
+    int rc = podref_eig(_corMatrix.data(), m, nmodes, solver, ev.data(), &ne, eigenVectoreig.data());
+    if (rc) return rc;
+    Eigen::VectorXd eigenValueseig = ev.head(ne);
+    if (n_evals) *n_evals = ne;
+    if (evals_out) std::memcpy(evals_out, eigenValueseig.data(), sizeof(double) * ne);
+    if (evecs_out) std::memcpy(evecs_out, eigenVectoreig.data(), sizeof(double) * m * nmodes);
+
+    // ITHACAPOD.C:194
+    Eigen::MatrixXd modesEig = (SnapMatrix * eigenVectoreig);
+    // ITHACAPOD.C:196-233
+    Eigen::MatrixXd normFact(nmodes, 1);
+    for (int i = 0; i < nmodes; i++)
+    {
+        if (norm == 0)
+        {
+            normFact(i, 0) = std::sqrt((modesEig.col(i).transpose() * V.asDiagonal() *
+                                        modesEig.col(i))(0, 0));
+        }
+        else
+        {
+            normFact(i, 0) = std::sqrt((modesEig.col(i).transpose() * modesEig.col(i))(0, 0));
+        }
+    }
+    // ITHACAPOD.C:245-264
+    Eigen::MatrixXd modesEigBC;
+    if (nbc > 0)
+    {
+        CMap SnapMatrixBC(Sbc, nbc, m);
+        modesEigBC = SnapMatrixBC * eigenVectoreig;
+    }
+    for (int i = 0; i < nmodes; i++)
+    {
+        modesEig.col(i) = modesEig.col(i).array() / normFact(i, 0);
+        if (nbc > 0) modesEigBC.col(i) = modesEigBC.col(i).array() / normFact(i, 0);
+    }
+    if (normfact_out) std::memcpy(normfact_out, normFact.data(), sizeof(double) * nmodes);
+    if (modes_out) std::memcpy(modes_out, modesEig.data(), sizeof(double) * Nd * nmodes);
+    if (modes_bc_out && nbc > 0)
+        std::memcpy(modes_bc_out, modesEigBC.data(), sizeof(double) * nbc * nmodes);
+
+    // ITHACAPOD.C:281-287
+    eigenValueseig = eigenValueseig / eigenValueseig.sum();
+    Eigen::VectorXd cumEigenValues(eigenValueseig);
+    for (int j = 1; j < cumEigenValues.size(); ++j)
+    {
+        cumEigenValues(j) += cumEigenValues(j - 1);
+    }
+    if (evals_norm_out) std::memcpy(evals_norm_out, eigenValueseig.data(), sizeof(double) * ne);
+    if (cum_out) std::memcpy(cum_out, cumEigenValues.data(), sizeof(double) * ne);
+    return 0;
+}
+
+// Lift + normalise only, for a given eigenvector block (ITHACAPOD.C:194-264); used to time the
+// CPU lift separately and to check the CUDA lift against the reference with identical Q.
+int podref_lift(const double* S, i64 Nc, int dim, int m, const double* Vc, const double* Q, int nmodes,
+                int norm, double* normfact_out, double* modes_out)
+{
+    const i64 Nd = Nc * dim;
+    CMap SnapMatrix(S, Nd, m);
+    CMap eigenVectoreig(Q, m, nmodes);
+    Eigen::VectorXd V = mass_fv(Vc, Nc, dim);
+    Eigen::MatrixXd modesEig = (SnapMatrix * eigenVectoreig);
+    for (int i = 0; i < nmodes; i++)
+    {
+        double nf = (norm == 0)
+            ? std::sqrt((modesEig.col(i).transpose() * V.asDiagonal() * modesEig.col(i))(0, 0))
+            : std::sqrt((modesEig.col(i).transpose() * modesEig.col(i))(0, 0));
+        modesEig.col(i) = modesEig.col(i).array() / nf;
+        if (normfact_out) normfact_out[i] = nf;
+    }
+    if (modes_out) std::memcpy(modes_out, modesEig.data(), sizeof(double) * Nd * nmodes);
+    return 0;
+}
+
+const char* podref_version() { return "eigen+spectra vendored by ITHACA-FV @8e7d6c09"; }
+
+} // extern "C"
