@@ -1,0 +1,252 @@
+"""ithaca-fv_b200 -- ctypes binding of libithaca_b200.so (include/ithaca_b200.h) for the test and
+benchmark harnesses, plus a host-side mirror of ITHACAPOD::getModes' argument handling.
+
+The product is the CUDA library; this module only marshals pointers. There is NO CPU fallback: if the
+library is missing, or no sm_100 device is present, every compute call raises.
+
+Reference semantics mirrored here (paths relative to /root/reference/src/ITHACA_CORE):
+  ITHACAPOD/ITHACAPOD.C:92-323   getModes (nmodes rules, solver-dependent eigenvalue handling, norms)
+"""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libithaca_b200.so")
+
+# every symbol include/ithaca_b200.h declares (checked by tests/test_abi.py)
+SYMBOLS = [
+    "ithaca_b200_create", "ithaca_b200_destroy", "ithaca_b200_last_error", "ithaca_b200_stream",
+    "ithaca_b200_launch_count", "ithaca_b200_timings", "ithaca_b200_nccl_unique_id",
+    "ithaca_b200_comm_init", "ithaca_b200_cell_range", "ithaca_b200_pod_set_volumes",
+    "ithaca_b200_pod_upload", "ithaca_b200_pod_gram", "ithaca_b200_pod_eig", "ithaca_b200_pod_set_gram",
+    "ithaca_b200_pod_postprocess_eigenvalues", "ithaca_b200_pod_lift", "ithaca_b200_pod_lift_patch",
+    "ithaca_b200_dmma_peak",
+]
+
+_lib = None
+
+
+class IthacaB200Error(RuntimeError):
+    pass
+
+
+def lib():
+    """Load libithaca_b200.so; raises (never falls back) when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise IthacaB200Error(
+                "libithaca_b200.so is not built (run `python -c 'import __graft_entry__ as g; g.build()'`); "
+                "there is no CPU fallback")
+        L = ctypes.CDLL(LIB_PATH)
+        P, I, L64, D = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_double
+        L.ithaca_b200_create.argtypes = [ctypes.POINTER(P), I]
+        L.ithaca_b200_destroy.argtypes = [P]
+        L.ithaca_b200_last_error.argtypes = [P]
+        L.ithaca_b200_last_error.restype = ctypes.c_char_p
+        L.ithaca_b200_stream.argtypes = [P]
+        L.ithaca_b200_stream.restype = P
+        L.ithaca_b200_launch_count.argtypes = [P, I]
+        L.ithaca_b200_launch_count.restype = L64
+        L.ithaca_b200_timings.argtypes = [P, P, I]
+        L.ithaca_b200_nccl_unique_id.argtypes = [P]
+        L.ithaca_b200_comm_init.argtypes = [P, P, I, I]
+        L.ithaca_b200_cell_range.argtypes = [L64, I, I, ctypes.POINTER(L64), ctypes.POINTER(L64)]
+        L.ithaca_b200_pod_set_volumes.argtypes = [P, P, L64]
+        L.ithaca_b200_pod_upload.argtypes = [P, P, I, I, L64]
+        L.ithaca_b200_pod_gram.argtypes = [P, P]
+        L.ithaca_b200_pod_eig.argtypes = [P, I, P, P, ctypes.POINTER(I)]
+        L.ithaca_b200_pod_set_gram.argtypes = [P, P, I]
+        L.ithaca_b200_pod_postprocess_eigenvalues.argtypes = [P, I, I, I, P, P, ctypes.POINTER(I)]
+        L.ithaca_b200_pod_lift.argtypes = [P, I, I, P, P]
+        L.ithaca_b200_pod_lift_patch.argtypes = [P, P, L64, P]
+        L.ithaca_b200_dmma_peak.argtypes = [I, ctypes.POINTER(D)]
+        _lib = L
+    return _lib
+
+
+def cell_range(nCells, rank, nranks):
+    b, e = ctypes.c_int64(), ctypes.c_int64()
+    rc = lib().ithaca_b200_cell_range(nCells, rank, nranks, ctypes.byref(b), ctypes.byref(e))
+    if rc:
+        raise IthacaB200Error("cell_range: bad argument")
+    return b.value, e.value
+
+
+def postprocess_eigenvalues(evals_all, nmodes, solver):
+    """Host arithmetic of ITHACAPOD.C:169/179, :182-186, :281-287 (through the C ABI)."""
+    ev = np.ascontiguousarray(evals_all, dtype=np.float64)
+    m = len(ev)
+    out = np.zeros(m)
+    cum = np.zeros(m)
+    n = ctypes.c_int(0)
+    rc = lib().ithaca_b200_pod_postprocess_eigenvalues(ev.ctypes.data, m, nmodes, 0 if solver == "spectra" else 1,
+                                                       out.ctypes.data, cum.ctypes.data, ctypes.byref(n))
+    if rc:
+        raise IthacaB200Error("postprocess_eigenvalues: bad argument")
+    return out[:n.value].copy(), cum[:n.value].copy()
+
+
+def dmma_peak(device=0):
+    v = ctypes.c_double(0)
+    rc = lib().ithaca_b200_dmma_peak(device, ctypes.byref(v))
+    if rc:
+        raise IthacaB200Error("dmma_peak failed (no sm_100 device?)")
+    return v.value
+
+
+def _ptr(x):
+    """Address of a numpy array / torch tensor / raw int."""
+    if x is None:
+        return None
+    if isinstance(x, int):
+        return x
+    if isinstance(x, np.ndarray):
+        return x.ctypes.data
+    return x.data_ptr()  # torch tensor (host pinned or device)
+
+
+class Pod:
+    """One handle = one GPU = one rank's cell shard. Mirrors the call sequence of getModes."""
+
+    TIMER_NAMES = ["upload", "gram", "allreduce", "eig", "lift", "scale", "download", "gram_kernel"]
+
+    def __init__(self, device=0):
+        self.L = lib()
+        self.h = ctypes.c_void_p()
+        rc = self.L.ithaca_b200_create(ctypes.byref(self.h), device)
+        if rc:
+            raise IthacaB200Error(self.L.ithaca_b200_last_error(None).decode())
+        self.m = self.dim = self.nCells = 0
+
+    def close(self):
+        if self.h:
+            self.L.ithaca_b200_destroy(self.h)
+            self.h = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _chk(self, rc):
+        if rc:
+            raise IthacaB200Error("status %d: %s" % (rc, self.L.ithaca_b200_last_error(self.h).decode()))
+
+    @property
+    def stream(self):
+        return self.L.ithaca_b200_stream(self.h)
+
+    def launch_count(self, reset=False):
+        return self.L.ithaca_b200_launch_count(self.h, 1 if reset else 0)
+
+    def timings(self):
+        out = np.zeros(8)
+        self._chk(self.L.ithaca_b200_timings(self.h, out.ctypes.data, 8))
+        return dict(zip(self.TIMER_NAMES, out.tolist()))
+
+    def comm_init(self, id128, rank, nranks):
+        buf = (ctypes.c_char * 128).from_buffer_copy(bytes(id128)) if id128 is not None else None
+        self._chk(self.L.ithaca_b200_comm_init(self.h, buf, rank, nranks))
+
+    def set_volumes(self, V):
+        n = V.shape[0]
+        self._chk(self.L.ithaca_b200_pod_set_volumes(self.h, _ptr(V), n))
+        self.nCells = n
+
+    def upload(self, snaps, dim, nCells=None):
+        """snaps: list of m arrays/tensors (each nCells*dim contiguous doubles), or a Fortran-ordered
+        (Nd, m) numpy array whose columns are the snapshots."""
+        if isinstance(snaps, np.ndarray) and snaps.ndim == 2:
+            assert snaps.flags.f_contiguous and snaps.dtype == np.float64
+            ptrs = [snaps.ctypes.data + j * snaps.strides[1] for j in range(snaps.shape[1])]
+            Nd = snaps.shape[0]
+            self._keep = snaps
+        else:
+            ptrs = [_ptr(s) for s in snaps]
+            Nd = int(snaps[0].numel()) if hasattr(snaps[0], "numel") else int(snaps[0].size)
+            self._keep = snaps
+        m = len(ptrs)
+        nCells = Nd // dim if nCells is None else nCells
+        arr = (ctypes.c_void_p * m)(*ptrs)
+        self._chk(self.L.ithaca_b200_pod_upload(self.h, arr, m, dim, nCells))
+        self.m, self.dim = m, dim
+
+    def gram(self, want=True):
+        G = np.zeros((self.m, self.m), order="F") if want else None
+        self._chk(self.L.ithaca_b200_pod_gram(self.h, _ptr(G)))
+        return G
+
+    def set_gram(self, G):
+        G = np.asfortranarray(G, dtype=np.float64)
+        self._chk(self.L.ithaca_b200_pod_set_gram(self.h, G.ctypes.data, G.shape[0]))
+        self.m = G.shape[0]
+
+    def eig(self, r):
+        ev = np.zeros(self.m)
+        Q = np.zeros((self.m, r), order="F")
+        sw = ctypes.c_int(0)
+        self._chk(self.L.ithaca_b200_pod_eig(self.h, r, ev.ctypes.data, Q.ctypes.data if r else None, ctypes.byref(sw)))
+        self.sweeps = sw.value
+        return ev, Q
+
+    def lift(self, r, norm="L2", out=None, want=True):
+        """out: optional list of r host/device buffers; want=False keeps the modes on the device."""
+        if norm not in ("L2", "Frobenius"):
+            raise IthacaB200Error("The PODnorm can be only L2 or Frobenius")
+        nf = np.zeros(r)
+        Phi = None
+        arr = None
+        if out is not None:
+            arr = (ctypes.c_void_p * r)(*[_ptr(o) for o in out])
+        elif want:
+            Phi = np.zeros((self.nCells * self.dim, r), order="F")
+            arr = (ctypes.c_void_p * r)(*[Phi.ctypes.data + i * Phi.strides[1] for i in range(r)])
+        self._chk(self.L.ithaca_b200_pod_lift(self.h, r, 0 if norm == "L2" else 1, arr, nf.ctypes.data))
+        return Phi, nf
+
+    def lift_patch(self, Sbc, r):
+        Sbc = np.asfortranarray(Sbc, dtype=np.float64)
+        out = np.zeros((Sbc.shape[0], r), order="F")
+        self._chk(self.L.ithaca_b200_pod_lift_patch(self.h, Sbc.ctypes.data, Sbc.shape[0], out.ctypes.data))
+        return out
+
+
+def check_nmodes(m, nmodes, solver):
+    """nmodes rules of getModes (ITHACAPOD.C:109-130), same messages as the reference's M_Assert."""
+    if solver == "spectra":
+        if nmodes == 0:
+            nmodes = m - 2
+        if nmodes > m - 2:
+            raise IthacaB200Error(
+                "The number of requested modes cannot be bigger than the number of Snapshots - 2")
+    elif solver == "eigen":
+        if nmodes == 0:
+            nmodes = m
+        if nmodes > m:
+            raise IthacaB200Error("The number of requested modes cannot be bigger than the number of Snapshots")
+    else:
+        raise IthacaB200Error("unknown EigenSolver '%s' (spectra|eigen)" % solver)
+    return nmodes
+
+
+def getModes(pod, snapshots, V, dim, nmodes=0, solver="spectra", norm="L2", Sbc=None):
+    """Host mirror of the dense part of ITHACAPOD::getModes (ITHACAPOD.C:109-287) on a Pod handle.
+    snapshots: Fortran (Nd, m) array or list of per-snapshot buffers; V: cell volumes of this rank.
+    Returns dict(G, evals_norm, cum, evecs, normfact, modes, modes_bc) laid out like the reference's
+    Eigen objects."""
+    if norm not in ("L2", "Frobenius"):
+        raise IthacaB200Error("The PODnorm can be only L2 or Frobenius")
+    m = snapshots.shape[1] if isinstance(snapshots, np.ndarray) else len(snapshots)
+    nmodes = check_nmodes(m, nmodes, solver)
+    pod.set_volumes(V)
+    pod.upload(snapshots, dim)
+    G = pod.gram()
+    ev_all, Q = pod.eig(nmodes)
+    evn, cum = postprocess_eigenvalues(ev_all, nmodes, solver)
+    Phi, nf = pod.lift(nmodes, norm)
+    Pbc = pod.lift_patch(Sbc, nmodes) if Sbc is not None else None
+    return dict(G=G, evals_all=ev_all, evals_norm=evn, cum=cum, evecs=Q, normfact=nf, modes=Phi, modes_bc=Pbc)

@@ -1,0 +1,82 @@
+"""CPU tests: the numpy restatement (oracle/pod_oracle.py) against the committed golden vectors produced
+by the reference's own Eigen/Spectra expressions, and against oracle/_ref directly when it is present."""
+import glob
+import os
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.join(os.path.dirname(__file__), "golden"))
+from make_golden import CASES, inputs  # noqa: E402
+from oracle import pod_oracle as po, synth  # noqa: E402
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def load(name):
+    return np.load(os.path.join(GOLD, "pod_%s.npz" % name), allow_pickle=False)
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_numpy_oracle_matches_golden(case):
+    name, Nc, dim, m, r, seed, solver, norm, nbc = case
+    g = load(name)
+    S, V, Sbc = inputs(Nc, dim, m, r, seed, nbc)
+    out = po.getmodes(S, V, dim, r, solver, norm, Sbc)
+    assert np.abs(out["G"] - g["G"]).max() <= 1e-13 * np.abs(g["G"]).max()
+    assert len(out["evals_norm"]) == len(g["evals_norm"])  # quirk Q4: m values (eigen) or nmodes (spectra)
+    # eigenvalues: 1e-10 relative on the kept modes; absolute (relative to lambda_1) on the rest
+    assert np.all(np.abs(out["evals_norm"][:r] - g["evals_norm"][:r]) <= 1e-10 * g["evals_norm"][:r])
+    assert np.abs(out["evals_norm"] - g["evals_norm"]).max() <= 1e-12 * g["evals_norm"][0]
+    assert np.abs(out["cum"] - g["cum"]).max() <= 1e-12
+    assert np.all(np.abs(out["normfact"] - g["normfact"]) <= 1e-9 * g["normfact"])
+    st = int(g["stride"])
+    A = po.sign_align(out["modes"], np.zeros_like(out["modes"]) + 0)  # no-op, keeps shape
+    sub = out["modes"][::st]
+    sub = po.sign_align(sub, g["modes_sub"])
+    rel = np.abs(sub - g["modes_sub"]).max(axis=0) / np.abs(g["modes_sub"]).max(axis=0)
+    assert rel.max() <= 1e-8, rel
+    if nbc:
+        s = np.sign(np.einsum("ij,ij->j", out["modes"][::st], g["modes_sub"]))
+        rel = np.abs(out["modes_bc"] * s - g["modes_bc"]).max(axis=0) / np.abs(g["modes_bc"]).max(axis=0)
+        assert rel.max() <= 1e-8
+
+
+@pytest.mark.skipif(not po.ref_available(), reason="oracle/_ref not built (reference tree absent)")
+def test_numpy_oracle_matches_reference_build_both_gram_branches():
+    Nc, dim, m = 4000, 3, 15
+    S = synth.snapshots(Nc, dim, m, 10, 5)
+    V = synth.volumes(Nc, 5)
+    G = po.gram(S, V, dim)
+    for branch in (0, 1):  # GEMM branch and the V.size()>1e6 rank-1 loop (ITHACAcoeffsMass.C:95-104)
+        Gr = po.ref_gram(S, V, dim, branch)
+        assert np.abs(G - Gr).max() <= 1e-13 * np.abs(Gr).max()
+
+
+@pytest.mark.skipif(not po.ref_available(), reason="oracle/_ref not built (reference tree absent)")
+def test_golden_is_reproducible_from_reference_build():
+    name, Nc, dim, m, r, seed, solver, norm, nbc = CASES[1]
+    g = load(name)
+    S, V, Sbc = inputs(Nc, dim, m, r, seed, nbc)
+    out = po.ref_getmodes(S, V, dim, r, solver, norm, Sbc)
+    assert np.array_equal(out["G"], g["G"])
+    assert np.array_equal(out["evals_norm"], g["evals_norm"])
+
+
+def test_nmodes_rules():
+    assert po.check_nmodes(20, 0, "spectra") == 18
+    assert po.check_nmodes(20, 0, "eigen") == 20
+    with pytest.raises(ValueError):
+        po.check_nmodes(20, 19, "spectra")
+    with pytest.raises(ValueError):
+        po.check_nmodes(20, 21, "eigen")
+
+
+def test_negative_shift_rule():
+    # ITHACAPOD.C:182-186: lambda += 2|min| when the smallest kept value is negative
+    G = np.diag([3.0, 1.0, -0.5])
+    ev, _ = po.eig(G, 2, "eigen")
+    assert np.allclose(ev, [4.0, 2.0, 0.5])
+    ev, _ = po.eig(G, 2, "spectra")  # only the kept values are inspected: no shift
+    assert np.allclose(ev, [3.0, 1.0])

@@ -1,0 +1,174 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the oracle on the same seeded inputs,
+against the committed golden vectors, and through size-independent properties at larger sizes.
+Tolerances are BASELINE.json's: eigenvalues 1e-10 relative, sign-aligned modes 1e-8 max relative; the Gram
+itself is held to 1e-13 relative (max norm)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.join(os.path.dirname(__file__), "golden"))
+from make_golden import CASES, inputs  # noqa: E402
+from oracle import pod_oracle as po, synth  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def rel_max(A, B):
+    return np.abs(A - B).max() / np.abs(B).max()
+
+
+def modes_rel(A, B):
+    A = po.sign_align(A, B)
+    return (np.abs(A - B).max(axis=0) / np.abs(B).max(axis=0)).max()
+
+
+@pytest.mark.parametrize("case", CASES, ids=[c[0] for c in CASES])
+def test_getmodes_matches_golden(pkg, pod, case):
+    name, Nc, dim, m, r, seed, solver, norm, nbc = case
+    g = np.load(os.path.join(GOLD, "pod_%s.npz" % name))
+    S, V, Sbc = inputs(Nc, dim, m, r, seed, nbc)
+    out = pkg.getModes(pod, S, V, dim, r, solver, norm, Sbc)
+    assert rel_max(out["G"], g["G"]) <= 1e-13
+    assert len(out["evals_norm"]) == len(g["evals_norm"])
+    assert np.all(np.abs(out["evals_norm"][:r] - g["evals_norm"][:r]) <= 1e-10 * g["evals_norm"][:r])
+    assert np.abs(out["evals_norm"] - g["evals_norm"]).max() <= 1e-12 * g["evals_norm"][0]
+    assert np.abs(out["cum"] - g["cum"]).max() <= 1e-12
+    assert np.all(np.abs(out["normfact"] - g["normfact"]) <= 1e-9 * g["normfact"])
+    st = int(g["stride"])
+    assert modes_rel(out["modes"][::st], g["modes_sub"]) <= 1e-8
+    if nbc:
+        s = np.sign(np.einsum("ij,ij->j", out["modes"][::st], g["modes_sub"]))
+        assert rel_max(out["modes_bc"] * s, g["modes_bc"]) <= 1e-8
+
+
+@pytest.mark.parametrize("Nc,dim,m", [(1, 1, 3), (5, 3, 4), (17, 1, 8), (1000, 1, 40), (1000, 3, 41), (777, 3, 100),
+                                       (3001, 1, 200), (2111, 3, 233), (12000, 1, 411)])
+def test_gram_matches_oracle_ragged(pkg, pod, Nc, dim, m):
+    """Every tile-edge case: m not a multiple of 8/40/200, Nd not a multiple of 16, single cell."""
+    rng = np.random.default_rng(Nc * 31 + m)
+    S = np.asfortranarray(rng.standard_normal((Nc * dim, m)))
+    V = rng.random(Nc) + 0.1
+    pod.set_volumes(V)
+    pod.upload(S, dim)
+    G = pod.gram()
+    Gr = po.gram(S, V, dim)
+    assert rel_max(G, Gr) <= 1e-13
+    assert np.array_equal(G, G.T)  # symmetric by construction (quirk-free: the reference's is up to rounding)
+
+
+def test_gram_vs_reference_build(pkg, pod):
+    if not po.ref_available():
+        pytest.skip("oracle/_ref not present")
+    Nc, dim, m = 20000, 3, 64
+    S = synth.snapshots(Nc, dim, m, 20, 3)
+    V = synth.volumes(Nc, 3)
+    pod.set_volumes(V)
+    pod.upload(S, dim)
+    G = pod.gram()
+    assert rel_max(G, po.ref_gram(S, V, dim, 0)) <= 1e-13
+    assert rel_max(G, po.ref_gram(S, V, dim, 1)) <= 1e-13
+
+
+@pytest.mark.parametrize("m", [2, 3, 16, 57, 200, 333])
+def test_eig_matches_numpy(pkg, pod, m):
+    rng = np.random.default_rng(m)
+    A = rng.standard_normal((m + 5, m))
+    G = A.T @ A
+    pod.set_gram(G)
+    ev, Q = pod.eig(m)
+    w = np.linalg.eigvalsh(G)[::-1]
+    assert np.abs(ev - w).max() <= 1e-12 * w[0]
+    assert np.abs(Q.T @ Q - np.eye(m)).max() <= 1e-12
+    assert np.abs(G @ Q - Q * ev).max() <= 1e-12 * w[0]
+
+
+def test_eig_indefinite_and_degenerate(pkg, pod):
+    """Negative eigenvalues must come out signed (the reference then shifts, ITHACAPOD.C:182-186);
+    repeated eigenvalues and an exactly singular matrix must converge."""
+    rng = np.random.default_rng(9)
+    Qo, _ = np.linalg.qr(rng.standard_normal((30, 30)))
+    lam = np.array([5.0, 5.0, 3.0, 1.0, 1.0, 1.0] + [0.0] * 20 + [-1e-3, -0.5, -0.5, -2.0])
+    G = (Qo * lam) @ Qo.T
+    G = 0.5 * (G + G.T)
+    pod.set_gram(G)
+    ev, Q = pod.eig(30)
+    assert np.abs(ev - np.sort(lam)[::-1]).max() <= 1e-13 * 5
+    assert np.abs(Q.T @ Q - np.eye(30)).max() <= 1e-13
+    evn, cum = pkg.postprocess_eigenvalues(ev, 30, "eigen")
+    ref_ev, _ = po.eig(G, 30, "eigen")
+    assert np.allclose(evn, ref_ev / ref_ev.sum(), rtol=0, atol=1e-13)
+
+
+def test_lift_matches_reference_with_identical_eigenvectors(pkg, pod):
+    """Lift + norms checked in isolation: feed the oracle the GPU's own eigenvectors."""
+    Nc, dim, m, r = 5003, 3, 48, 20
+    S = synth.snapshots(Nc, dim, m, 2 * r, 21)
+    V = synth.volumes(Nc, 21)
+    for norm in ("L2", "Frobenius"):
+        out = pkg.getModes(pod, S, V, dim, r, "eigen", norm)
+        Phi, nf, _ = po.lift(S, V, dim, out["evecs"], norm)
+        assert np.all(np.abs(out["normfact"] - nf) <= 1e-12 * nf)
+        assert (np.abs(out["modes"] - Phi).max(axis=0) / np.abs(Phi).max(axis=0)).max() <= 1e-11
+
+
+@pytest.mark.parametrize("r", [1, 10, 24, 25, 50, 100])
+def test_lift_all_column_block_sizes(pkg, pod, r):
+    Nc, dim, m = 2000, 1, 120
+    rng = np.random.default_rng(r)
+    S = np.asfortranarray(rng.standard_normal((Nc, m)))
+    V = rng.random(Nc) + 0.5
+    out = pkg.getModes(pod, S, V, dim, r, "eigen", "L2")
+    Phi, nf, _ = po.lift(S, V, dim, out["evecs"], "L2")
+    assert np.all(np.abs(out["normfact"] - nf) <= 1e-12 * nf)
+    assert (np.abs(out["modes"] - Phi).max(axis=0) / np.abs(Phi).max(axis=0)).max() <= 1e-11
+    # modes are V-orthonormal (property of the method)
+    Mm = out["modes"].T @ (out["modes"] * V[:, None])
+    assert np.abs(Mm - np.eye(r)).max() <= 1e-9
+
+
+def test_full_size_properties_c2_shape(pkg, pod):
+    """BASELINE config 2 shape (2M cells x 200 scalar snapshots) through properties that need no oracle pass:
+    a rank-2 snapshot set has the closed-form Gram  G = aa^T F11 + (ab^T + ba^T) F12 + bb^T F22."""
+    Nc, m, r = 2_000_000, 200, 2
+    rng = np.random.default_rng(77)
+    x = np.linspace(0, 1, Nc)
+    f, g2 = np.sin(3 * x) + 0.2, np.cos(5 * x)
+    a, b = rng.standard_normal(m), rng.standard_normal(m)
+    V = (1.0 + 0.5 * np.sin(11 * x)) / Nc
+    S = np.asfortranarray(np.outer(f, a) + np.outer(g2, b))
+    pod.set_volumes(V)
+    pod.upload(S, 1)
+    G = pod.gram()
+    F11, F12, F22 = (V * f * f).sum(), (V * f * g2).sum(), (V * g2 * g2).sum()
+    Gx = np.outer(a, a) * F11 + (np.outer(a, b) + np.outer(b, a)) * F12 + np.outer(b, b) * F22
+    assert rel_max(G, Gx) <= 1e-12
+    ev, Q = pod.eig(r)
+    w = np.linalg.eigvalsh(Gx)[::-1]
+    assert np.all(np.abs(ev[:2] - w[:2]) <= 1e-10 * w[:2])
+    assert np.abs(ev[2:]).max() <= 1e-12 * w[0]
+    Phi, nf = pod.lift(r, "L2")
+    assert np.abs(Phi.T @ (Phi * V[:, None]) - np.eye(2)).max() <= 1e-10
+    # modes span {f, g}: residual of projecting f on the modes vanishes
+    c = Phi.T @ (V * f)
+    assert np.abs(Phi @ c - f).max() <= 1e-9 * np.abs(f).max()
+
+
+def test_error_paths(pkg):
+    p = pkg.Pod(0)
+    with pytest.raises(pkg.IthacaB200Error):
+        p.gram()  # nothing uploaded
+    V = np.ones(10)
+    p.set_volumes(V)
+    with pytest.raises(pkg.IthacaB200Error):
+        p.upload(np.asfortranarray(np.ones((12, 3))), 1)  # nCells mismatch
+    p.upload(np.asfortranarray(np.random.default_rng(0).standard_normal((10, 3))), 1)
+    p.gram()
+    with pytest.raises(pkg.IthacaB200Error):
+        p.eig(4)  # more modes than snapshots
+    p.eig(3)
+    with pytest.raises(pkg.IthacaB200Error):
+        p.lift(2, "H1")
+    p.close()
