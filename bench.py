@@ -1,0 +1,400 @@
+#!/usr/bin/env python
+"""bench.py -- POD time-to-modes (ITHACAPOD::getModes hot path) on N B200s, one rank per GPU.
+
+A "step" is one pass of the hot path over one synthetic snapshot set: Gram (DMMA) -> all-reduce ->
+Jacobi eigensolve -> lift + normalise.  Workloads (BASELINE.json configs):
+  c2 (default): 2M cells x 200 scalar FP64 snapshots, 20 modes PER RANK (weak scaling: N ranks = N x 2M cells)
+  c3          : 20M cells x 1000 vector snapshots, 50 modes, cell-sharded over the N ranks (needs N >= 4)
+  c1          : 10k cells x 100 vector snapshots, 10 modes (tutorial scale)
+`value`  = time-to-modes with the snapshot matrix already resident in HBM (seconds, lower is better)
+`e2e`    = the same through the C ABI with HOST buffers: H2D of every snapshot and D2H of every mode inside
+           the timed region.
+`--impl reference` times the reference's own CPU expressions (oracle/_ref: its vendored Eigen/Spectra) with
+one shard per host thread (= one MPI rank per core, the reference's only parallelism) on a bounded sample.
+"""
+import argparse
+import importlib
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WORKLOADS = {
+    "c1": dict(cells=10_000, dim=3, m=100, r=10, sharded=False, name="C1 10k cells x 100 vector snapshots, 10 modes"),
+    "c2": dict(cells=2_000_000, dim=1, m=200, r=20, sharded=False,
+               name="C2 2M cells x 200 scalar FP64 snapshots, 20 modes (per rank)"),
+    "c3": dict(cells=20_000_000, dim=3, m=1000, r=50, sharded=True,
+               name="C3 20M cells x 1000 vector FP64 snapshots, 50 modes (cell-sharded over ranks)"),
+}
+METRIC = "pod_time_to_modes"
+UNIT = "s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampler (pynvml; falls back to nothing if NVML is unavailable)
+# ------------------------------------------------------------------------------------------------
+class Clocks:
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+               0x80: "hw_power_brake", 0x2: "applications_clocks_setting"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._thr = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.dev = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.dev, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.dev, self.nv.NVML_CLOCK_SM))
+                bits = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.dev)
+                for b, n in self.REASONS.items():
+                    if bits & b:
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def start(self):
+        if self.nv:
+            self._thr = threading.Thread(target=self._run, daemon=True)
+            self._thr.start()
+
+    def stop(self):
+        if self._thr:
+            self._stop.set()
+            self._thr.join()
+        return {"sm_mhz": (statistics.median(self.samples) if self.samples else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+# synthetic snapshots on the device (torch = plumbing only): low rank + noise, spectrum ~ 1/(k+1)^2
+# ------------------------------------------------------------------------------------------------
+def make_device_snapshots(torch, dev, cells, dim, m, seed):
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    Nd = cells * dim
+    R = 64
+    coef, _ = torch.linalg.qr(torch.randn(m, R, generator=g, device=dev, dtype=torch.float64))
+    sig = 1.0 / torch.arange(1, R + 1, device=dev, dtype=torch.float64)
+    S = torch.empty((m, Nd), device=dev, dtype=torch.float64)  # row j = snapshot j, contiguous
+    chunk = max(1, (1 << 26) // max(m, R))
+    for r0 in range(0, Nd, chunk):
+        r1 = min(Nd, r0 + chunk)
+        x = (torch.arange(r0, r1, device=dev, dtype=torch.float64) + 0.5) / Nd
+        k = torch.arange(1, R + 1, device=dev, dtype=torch.float64)
+        U = torch.sin(x[:, None] * k[None, :] * 3.141592653589793) * torch.cos(x[:, None] * (k[None, :] + 1.0))
+        blk = (U * sig) @ coef.T
+        blk += 1e-6 * torch.randn(r1 - r0, m, generator=g, device=dev, dtype=torch.float64)
+        S[:, r0:r1] = blk.T
+        del U, blk
+    V = torch.exp(0.5 * torch.randn(cells, generator=g, device=dev, dtype=torch.float64))
+    V /= V.sum()
+    return S, V
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the reference's expressions on its vendored Eigen/Spectra (oracle/_ref), else the numpy port
+# ------------------------------------------------------------------------------------------------
+def host_threads():
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
+
+
+def cpu_time_to_modes(wl, n_ranks_cells, threads, rows_per_thread, seed=5):
+    """Times Gram + eigensolve + lift of the reference on `threads` cell shards of `rows_per_thread` cells
+    each (one shard per host thread = one MPI rank per core), then scales the two stages that are linear in
+    the cell count to the full workload (the eigensolve is run at full size m x m).
+    Returns (seconds_full, detail)."""
+    from oracle import pod_oracle as po
+    cells_full, dim, m, r = n_ranks_cells, wl["dim"], wl["m"], wl["r"]
+    kind = "reference" if po.ref_available() else "port"
+    rng = np.random.default_rng(seed)
+    shards = []
+    for t in range(threads):
+        S = np.asfortranarray(rng.standard_normal((rows_per_thread * dim, m)))
+        V = rng.random(rows_per_thread) + 0.5
+        shards.append((S, V))
+    # the reference's Gram branch is chosen by the FULL per-rank size (ITHACAcoeffsMass.C:95): V.size() > 1e6
+    per_rank_Nd = cells_full * dim / threads
+    branch = 1 if per_rank_Nd > 1e6 else 0
+    Gs = [None] * threads
+
+    def run_gram(t):
+        S, V = shards[t]
+        Gs[t] = po.ref_gram(S, V, dim, branch) if kind == "reference" else po.gram(S, V, dim)
+
+    t0 = time.perf_counter()
+    th = [threading.Thread(target=run_gram, args=(t,)) for t in range(threads)]
+    [x.start() for x in th]
+    [x.join() for x in th]
+    G = sum(Gs)  # = Pstream reduce
+    t_gram = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    ev, Q = (po.ref_eig(G, r, "spectra") if kind == "reference" else po.eig(G, r, "spectra"))
+    t_eig = time.perf_counter() - t0
+
+    def run_lift(t):
+        S, V = shards[t]
+        if kind == "reference":
+            po.ref_lift(S, V, dim, Q, "L2")
+        else:
+            po.lift(S, V, dim, Q, "L2")
+
+    t0 = time.perf_counter()
+    th = [threading.Thread(target=run_lift, args=(t,)) for t in range(threads)]
+    [x.start() for x in th]
+    [x.join() for x in th]
+    t_lift = time.perf_counter() - t0
+    scale = cells_full / float(threads * rows_per_thread)
+    total = (t_gram + t_lift) * scale + t_eig
+    detail = dict(kind=kind, cores=threads, gram_s=t_gram * scale, eig_s=t_eig, lift_s=t_lift * scale,
+                  gram_branch=("rank1-loop" if branch else "gemm"), scale=scale,
+                  sample="%d threads x %d cells x %d snapshots (dim %d), Gram+lift scaled x%.1f to %d cells, "
+                         "eigensolve %dx%d in full" % (threads, rows_per_thread, m, dim, scale, cells_full, m, m))
+    return total, detail
+
+
+def run_reference_arm(args, wl, rank, world):
+    if rank != 0:
+        return
+    threads = host_threads()
+    cells_total = wl["cells"] if wl["sharded"] else wl["cells"] * world
+    rows = max(256, min(wl["cells"] // threads, int(2.5e9 / (2.0 * wl["m"] * wl["m"] * wl["dim"]))))
+    times, detail = [], None
+    for it in range(args.warmup + args.steps):
+        t, detail = cpu_time_to_modes(wl, cells_total, threads, rows, seed=it)
+        if it >= args.warmup:
+            times.append(t)
+    v = statistics.mean(times)
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": v * 1e3, "higher_is_better": False, "scaling": "weak" if not wl["sharded"] else "strong",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": wl["name"], "cells_total": cells_total, "snapshots": wl["m"], "modes": wl["r"]},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": detail["cores"], "kind": detail["kind"],
+                             "sample": detail["sample"], "stages_s": {k: detail[k] for k in ("gram_s", "eig_s", "lift_s")},
+                             "gram_branch": detail["gram_branch"], "extrapolated": True},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# B200 arm
+# ------------------------------------------------------------------------------------------------
+def run_b200(args, wl, rank, local_rank, world):
+    import torch
+    import torch.distributed as dist
+    pkg = importlib.import_module("ithaca-fv_b200")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    multi = world > 1
+    if multi:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if multi:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    pod = pkg.Pod(local_rank)
+    if multi:
+        idt = torch.zeros(128, dtype=torch.uint8, device=dev)
+        if rank == 0:
+            buf = (__import__("ctypes").c_char * 128)()
+            rc = pkg.lib().ithaca_b200_nccl_unique_id(buf)
+            assert rc == 0, "ncclGetUniqueId failed"
+            idt.copy_(torch.frombuffer(bytearray(bytes(buf)), dtype=torch.uint8))
+        dist.broadcast(idt, 0)
+        pod.comm_init(bytes(idt.cpu().numpy().tobytes()), rank, world)
+
+    dim, m, r = wl["dim"], wl["m"], wl["r"]
+    if wl["sharded"]:
+        b, e = pkg.cell_range(wl["cells"], rank, world)
+        cells = e - b
+        cells_total = wl["cells"]
+    else:
+        cells = wl["cells"]
+        cells_total = cells * world
+    Nd = cells * dim
+    S, V = make_device_snapshots(torch, dev, cells, dim, m, 20251104 + 17 * rank)
+    if multi:  # volumes of the global mesh sum to 1
+        V /= world
+    torch.cuda.synchronize()
+    snaps_dev = [S[j] for j in range(m)]
+
+    stream = torch.cuda.ExternalStream(pod.stream, device=dev)
+    peak_dmma = pkg.dmma_peak(local_rank)
+
+    # ---------------- device-resident leg: snapshots already in the library's HBM matrix ----------------
+    pod.set_volumes(V)
+    pod.upload(snaps_dev, dim, cells)
+
+    def step_resident():
+        pod.gram(want=False)
+        pod.eig(r)
+        pod.lift(r, "L2", want=False)
+
+    for _ in range(args.warmup):
+        step_resident()
+    clocks = Clocks(local_rank)
+    barrier()
+    pod.launch_count(reset=True)
+    stage_acc = {}
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        step_resident()
+        for k, v in pod.timings().items():
+            stage_acc[k] = stage_acc.get(k, 0.0) + v
+    e1.record(stream)
+    barrier()
+    clk = clocks.stop()
+    launches = pod.launch_count()
+    el = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    if multi:
+        dist.all_reduce(el, op=dist.ReduceOp.MAX)
+    ms_step = el.item() / args.steps
+    stages = {k: v / args.steps for k, v in stage_acc.items()}
+    gk = torch.tensor([stages["gram_kernel"]], device=dev, dtype=torch.float64)
+    if multi:
+        dist.all_reduce(gk, op=dist.ReduceOp.MAX)
+    gram_kernel_ms = gk.item()
+
+    # ---------------- end-to-end leg: host buffers in, host buffers out ----------------
+    e2e = None
+    if not args.no_e2e:
+        host_bytes = (m + r) * Nd * 8
+        try:
+            S_host = torch.empty((m, Nd), dtype=torch.float64, pin_memory=True)
+            S_host.copy_(S)
+            V_host = torch.empty(cells, dtype=torch.float64, pin_memory=True)
+            V_host.copy_(V)
+            modes_host = torch.empty((r, Nd), dtype=torch.float64, pin_memory=True)
+            torch.cuda.synchronize()
+            snaps_host = [S_host[j] for j in range(m)]
+            modes_out = [modes_host[i] for i in range(r)]
+
+            def step_e2e():
+                pod.set_volumes(V_host)
+                pod.upload(snaps_host, dim, cells)
+                pod.gram(want=False)
+                ev, Q = pod.eig(r)
+                pod.lift(r, "L2", out=modes_out)
+                return ev
+
+            for _ in range(max(1, min(args.warmup, 3))):
+                step_e2e()
+            barrier()
+            t0 = time.perf_counter()
+            e0.record(stream)
+            for _ in range(args.steps):
+                step_e2e()
+            e1.record(stream)
+            barrier()
+            wall = (time.perf_counter() - t0) / args.steps
+            el = torch.tensor([e0.elapsed_time(e1) / 1e3 / args.steps, wall], device=dev, dtype=torch.float64)
+            if multi:
+                dist.all_reduce(el, op=dist.ReduceOp.MAX)
+            e2e = {"value": el[0].item(), "unit": UNIT, "h2d_bytes_per_step": (m * Nd + cells) * 8,
+                   "d2h_bytes_per_step": (r * Nd + m + m * r + r) * 8, "wall_s": el[1].item(),
+                   "stages_ms": pod.timings()}
+        except RuntimeError as ex:  # not enough pinned host memory for this workload
+            e2e = {"value": None, "unit": UNIT, "error": "host buffers (%.1f GB pinned) unavailable: %s" % (host_bytes / 1e9, str(ex)[:80])}
+
+    if rank != 0:
+        if multi:
+            dist.destroy_process_group()
+        return
+
+    # ---------------- roofline of the dominant kernel (Gram) ----------------
+    Nd_total_rank = Nd  # per launch: this rank's shard
+    gram_flops = float(Nd_total_rank) * m * (m + 1)  # lower triangle incl. diagonal, mul+add
+    achieved = gram_flops / (gram_kernel_ms * 1e-3) / 1e12
+    traffic = None
+    tf = os.path.join(ROOT, "profiles", "gram_traffic.json")
+    if os.path.exists(tf):
+        try:
+            traffic = json.load(open(tf)).get(args.workload)
+        except Exception:
+            traffic = None
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    lift_bytes = 8.0 * Nd * (m + r)
+    line = {
+        "metric": METRIC, "value": ms_step / 1e3, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": False,
+        "scaling": "strong" if wl["sharded"] else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": wl["name"], "cells_total": cells_total, "cells_per_rank": cells, "dim": dim,
+                   "snapshots": m, "modes": r, "l2": "inputs (%.1f GB per rank) larger than L2" % (m * Nd * 8 / 1e9),
+                   "eigensolver": "one-sided Jacobi (%d sweeps)" % pod.sweeps},
+        "roofline": {"bound": "tensor", "kernel": "gram_kernel", "achieved": achieved, "peak": peak_dmma,
+                     "unit": "TFLOP/s", "frac": achieved / peak_dmma, "traffic": traffic,
+                     "peak_source": "measured live: register-resident DMMA.8x8x4 microbenchmark (ithaca_b200_dmma_peak); "
+                                    "MEASURED_PEAKS.json holds no FP64 figure; nominal B200 FP64 tensor = 37-40 TFLOP/s",
+                     "algorithmic_flops_per_launch": gram_flops, "kernel_ms": gram_kernel_ms},
+        "roofline_lift": {"bound": "hbm", "kernel": "lift_kernel", "achieved": lift_bytes / (stages["lift"] * 1e-3) / 1e9,
+                          "peak": hbm_peak, "unit": "GB/s", "frac": lift_bytes / (stages["lift"] * 1e-3) / 1e9 / hbm_peak,
+                          "traffic": None, "algorithmic_bytes_per_launch": lift_bytes},
+        "gram_tflops_total": achieved * world,
+        "stages_ms": stages, "gpu_launches": int(launches), "clocks": clk, "e2e": e2e,
+    }
+    if not args.no_cpu_baseline and world >= 1:
+        threads = 1
+        rows = max(256, min(cells, int(2.0e10 / (2.0 * m * m * dim))))  # ~10-20 s of single-core Gram
+        v, d = cpu_time_to_modes(wl, cells_total, threads, rows)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": d["cores"], "kind": d["kind"], "sample": d["sample"],
+                                "stages_s": {k: d[k] for k in ("gram_s", "eig_s", "lift_s")},
+                                "gram_branch": d["gram_branch"], "extrapolated": True, "host_threads_available": host_threads()}
+    print(json.dumps(line), flush=True)
+    if multi:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference_arm(args, wl, rank, world)
+        return
+    run_b200(args, wl, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()
