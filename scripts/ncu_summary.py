@@ -1,0 +1,69 @@
+#!/usr/bin/env python
+"""Summarise ncu output brought back in gpurun_out/ into profiles/ (tracked).
+  python scripts/ncu_summary.py launches gpurun_out/launches_r1.csv profiles/r1_launches.md
+  python scripts/ncu_summary.py full gpurun_out/prof_r1_pod.ncu-rep profiles/r1_pod_full.md
+"""
+import collections
+import csv
+import subprocess
+import sys
+
+KEYS = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
+        "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__t_bytes.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_tensor_subpipe_dmma.avg.pct_of_peak_sustained_active",
+        "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "smsp__issue_active.avg.pct_of_peak_sustained_active",
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
+        "smsp__inst_executed.sum", "sm__cycles_elapsed.max"]
+
+
+def launches(src, dst):
+    lines = [l for l in open(src) if not l.startswith("==")]
+    agg = collections.OrderedDict()
+    for row in csv.DictReader(lines):
+        if row.get("Metric Name") != "gpu__time_duration.sum":
+            continue
+        v = float(row["Metric Value"].replace(",", ""))
+        u = row["Metric Unit"]
+        v = v / 1e3 if u == "ns" else (v * 1e3 if u == "ms" else v)
+        a = agg.setdefault(row["Kernel Name"][:90], [0, 0.0])
+        a[0] += 1
+        a[1] += v
+    ours = {k: v for k, v in agg.items() if "ib200::" in k and "dmma_peak" not in k}
+    tot = sum(v[1] for v in ours.values())
+    with open(dst, "w") as f:
+        f.write("# ncu launch list (gpu__time_duration.sum, --clock-control none; cold-cache, serialised)\n\n")
+        f.write("source: `%s`; shares are over this library's kernels of the step (torch data-generation and the\n"
+                "DMMA-peak microbenchmark listed below for completeness).\n\n" % src)
+        f.write("| kernel | launches | total us | us/launch | share of step |\n|---|---|---|---|---|\n")
+        for k, (n, t) in sorted(ours.items(), key=lambda x: -x[1][1]):
+            f.write("| `%s` | %d | %.1f | %.1f | %.1f%% |\n" % (k, n, t, t / n, 100 * t / tot))
+        f.write("\nother kernels in the capture:\n\n| kernel | launches | total us |\n|---|---|---|\n")
+        for k, (n, t) in sorted(agg.items(), key=lambda x: -x[1][1]):
+            if k not in ours:
+                f.write("| `%s` | %d | %.1f |\n" % (k, n, t))
+    print(open(dst).read())
+
+
+def full(src, dst):
+    raw = subprocess.run(["ncu", "-i", src, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    hdr, units = rows[0], rows[1]
+    with open(dst, "w") as f:
+        f.write("# ncu --set full summary\n\nsource: `%s` (per launch)\n" % src)
+        for r in rows[2:]:
+            name = r[hdr.index("Kernel Name")]
+            f.write("\n## `%s`\n\n| metric | value | unit |\n|---|---|---|\n" % name[:100])
+            for k in KEYS:
+                if k in hdr:
+                    i = hdr.index(k)
+                    f.write("| %s | %s | %s |\n" % (k, r[i], units[i]))
+    print(open(dst).read())
+
+
+if __name__ == "__main__":
+    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2], sys.argv[3])
