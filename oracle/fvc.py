@@ -1,0 +1,167 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes binding of oracle/libfvc_oracle.so (oracle/fvc_oracle.c) and the seeded
+synthetic basis used by the projection tests and benchmark. Parity status: see fvc_oracle.c (UNPINNED at the
+OpenFOAM boundary; the term-builder loop nests follow steadyNS.C:883-1137)."""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB = os.path.join(_HERE, "libfvc_oracle.so")
+_lib = None
+P = ctypes.c_void_p
+
+
+class _Mesh(ctypes.Structure):
+    _fields_ = [("nCells", ctypes.c_longlong), ("nInt", ctypes.c_longlong), ("nBnd", ctypes.c_longlong),
+                ("owner", P), ("neighbour", P), ("Sf", P), ("magSf", P), ("w", P), ("dc", P), ("dcB", P),
+                ("corr", P), ("V", P), ("bmask", P)]
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        L = ctypes.CDLL(LIB)
+        L.fvo_domain_integrate_dot.restype = ctypes.c_double
+        _lib = L
+    return _lib
+
+
+def _c(a, dt=np.float64):
+    return np.ascontiguousarray(a, dtype=dt)
+
+
+class Oracle:
+    """Holds the C mesh struct (and keeps the numpy arrays it points into alive)."""
+
+    def __init__(self, mesh, corrected=True):
+        self.mesh = mesh
+        self.keep = dict(owner=_c(mesh.owner, np.int32), neighbour=_c(mesh.neighbour, np.int32), Sf=_c(mesh.Sf),
+                         magSf=_c(mesh.magSf), w=_c(mesh.w), dc=_c(mesh.dc), dcB=_c(mesh.dcB), corr=_c(mesh.corr),
+                         V=_c(mesh.V), bmask=_c(mesh.bmask, np.uint8))
+        k = self.keep
+        self.m = _Mesh(mesh.nCells, mesh.nInt, mesh.nBnd, k["owner"].ctypes.data, k["neighbour"].ctypes.data,
+                       k["Sf"].ctypes.data, k["magSf"].ctypes.data, k["w"].ctypes.data, k["dc"].ctypes.data,
+                       k["dcB"].ctypes.data, k["corr"].ctypes.data if corrected else None, k["V"].ctypes.data,
+                       k["bmask"].ctypes.data)
+        self.L = lib()
+
+    def _ref(self):
+        return ctypes.byref(self.m)
+
+    @staticmethod
+    def _ptrs(fields):
+        fs = [_c(f) for f in fields]
+        return fs, (P * len(fs))(*[f.ctypes.data for f in fs])
+
+    # ---- operators ----
+    def flux(self, U, Ub):
+        U, Ub = _c(U), _c(Ub)
+        out = np.zeros(self.mesh.nInt + self.mesh.nBnd)
+        self.L.fvo_flux(self._ref(), P(U.ctypes.data), P(Ub.ctypes.data), P(out.ctypes.data))
+        return out
+
+    def div_phi(self, phi, U, Ub):
+        phi, U, Ub = _c(phi), _c(U), _c(Ub)
+        out = np.zeros(3 * self.mesh.nCells)
+        self.L.fvo_div_phi_vec(self._ref(), P(phi.ctypes.data), P(U.ctypes.data), P(Ub.ctypes.data), P(out.ctypes.data))
+        return out
+
+    def div(self, U, Ub):
+        U, Ub = _c(U), _c(Ub)
+        out = np.zeros(self.mesh.nCells)
+        self.L.fvo_div_vec(self._ref(), P(U.ctypes.data), P(Ub.ctypes.data), P(out.ctypes.data))
+        return out
+
+    def grad(self, p, pb):
+        p, pb = _c(p), _c(pb)
+        out = np.zeros(3 * self.mesh.nCells)
+        self.L.fvo_grad_scalar(self._ref(), P(p.ctypes.data), P(pb.ctypes.data), P(out.ctypes.data))
+        return out
+
+    def grad_vec(self, U, Ub):
+        U, Ub = _c(U), _c(Ub)
+        out = np.zeros(9 * self.mesh.nCells)
+        self.L.fvo_grad_vec(self._ref(), P(U.ctypes.data), P(Ub.ctypes.data), P(out.ctypes.data))
+        return out
+
+    def laplacian(self, U, Ub):
+        U, Ub = _c(U), _c(Ub)
+        out = np.zeros(3 * self.mesh.nCells)
+        self.L.fvo_laplacian_vec(self._ref(), P(U.ctypes.data), P(Ub.ctypes.data), P(out.ctypes.data))
+        return out
+
+    # ---- term builders ----
+    def mass_term(self, U):
+        fs, pu = self._ptrs(U)
+        N = len(fs)
+        M = np.zeros((N, N), order="F")
+        self.L.fvo_mass_term(self._ref(), N, pu, P(M.ctypes.data))
+        return M
+
+    def diffusive_term(self, U, Ub):
+        fs, pu = self._ptrs(U)
+        fb, pb = self._ptrs(Ub)
+        N = len(fs)
+        B = np.zeros((N, N), order="F")
+        self.L.fvo_diffusive_term(self._ref(), N, pu, pb, P(B.ctypes.data))
+        return B
+
+    def pressure_gradient_term(self, U, Pm, Pb):
+        fs, pu = self._ptrs(U)
+        fp, pp = self._ptrs(Pm)
+        fb, pb = self._ptrs(Pb)
+        K = np.zeros((len(fs), len(fp)), order="F")
+        self.L.fvo_pressure_gradient_term(self._ref(), len(fs), len(fp), pu, pp, pb, P(K.ctypes.data))
+        return K
+
+    def divergence_term(self, U, Ub, Pm):
+        fs, pu = self._ptrs(U)
+        fb, pb = self._ptrs(Ub)
+        fp, pp = self._ptrs(Pm)
+        Pmat = np.zeros((len(fp), len(fs)), order="F")
+        self.L.fvo_divergence_term(self._ref(), len(fs), len(fp), pu, pb, pp, P(Pmat.ctypes.data))
+        return Pmat
+
+    def convective_term_tens(self, U, Ub, cache=True):
+        fs, pu = self._ptrs(U)
+        fb, pb = self._ptrs(Ub)
+        N = len(fs)
+        C = np.zeros((N, N, N), order="F")
+        fn = self.L.fvo_convective_term_tens_cache if cache else self.L.fvo_convective_term_tens
+        fn(self._ref(), N, pu, pb, P(C.ctypes.data))
+        return C
+
+    def cell_faces(self):
+        nnz = 2 * self.mesh.nInt + self.mesh.nBnd
+        off = np.zeros(self.mesh.nCells + 1, dtype=np.int32)
+        ent = np.zeros(nnz, dtype=np.int32)
+        other = np.zeros(nnz, dtype=np.int32)
+        self.L.fvo_cell_faces(self._ref(), P(off.ctypes.data), P(ent.ctypes.data), P(other.ctypes.data))
+        return off, ent, other
+
+
+def synthetic_basis(mesh, N, Np, seed=0, noise=1e-3):
+    """N vector fields + Np scalar fields: smooth functions of the cell / boundary-face centres plus noise;
+    boundary values = the same functions evaluated at the face centres (SURVEY.md section 8(d), C4 inputs)."""
+    rng = np.random.default_rng(seed)
+    nI = mesh.nInt
+    Cc, Cb = mesh.Cc, mesh.Cf[nI:]
+    L = np.abs(np.concatenate([Cc, Cb])).max() + 1e-30
+
+    def vec(k, X, nz):
+        x, y, z = X[:, 0] / L, X[:, 1] / L, X[:, 2] / L
+        out = np.stack([np.sin((k + 1) * x + 0.3) * np.cos((k + 2) * y) + 0.2 * z,
+                        np.cos((k + 1) * y - 0.1) * np.sin((k + 3) * x) - 0.1 * z * x,
+                        0.3 * np.sin((k + 1) * (x + y + z))], axis=1)
+        return np.ascontiguousarray((out + nz).ravel())
+
+    U, Ub, Pm, Pb = [], [], [], []
+    for k in range(N):
+        U.append(vec(k, Cc, noise * rng.standard_normal((mesh.nCells, 3))))
+        Ub.append(vec(k, Cb, noise * rng.standard_normal((mesh.nBnd, 3))))
+    for k in range(Np):
+        f = lambda X: np.cos((k + 1) * X[:, 0] / L) * np.sin((k + 2) * X[:, 1] / L + 0.5) + 0.1 * X[:, 2] / L
+        Pm.append(f(Cc) + noise * rng.standard_normal(mesh.nCells))
+        Pb.append(f(Cb) + noise * rng.standard_normal(mesh.nBnd))
+    return U, Ub, Pm, Pb

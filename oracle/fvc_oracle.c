@@ -1,0 +1,308 @@
+/* TEST INFRASTRUCTURE ONLY -- never linked, imported or executed by the product path.
+ *
+ * fvc_oracle: plain-C restatement of (a) the OpenFOAM finite-volume-calculus operators that ITHACA-FV's
+ * Galerkin projection calls and (b) the reference's own term-builder loop nests.
+ *
+ * Parity status: UNPINNED at the OpenFOAM boundary. The term builders (b) follow the reference line by
+ * line (/root/reference/src/ITHACA_FOMPROBLEMS/steadyNS/steadyNS.C, cited at each function); the operators
+ * (a) live in OpenFOAM, a third-party dependency absent from /root/reference (pinned by the reference to
+ * v2412, README.md:19) and not installable here, so they restate OpenFOAM's published algorithms for the
+ * scheme set "Gauss linear" (grad, div, interpolate) and "Gauss linear corrected|uncorrected" (laplacian):
+ *   fvc::surfaceIntegrate  finiteVolume/fvc/fvcSurfaceIntegrate.C : += owner, -= neighbour over internal faces,
+ *                          += faceCells over boundary patches, then /= V
+ *   fvc::domainIntegrate   finiteVolume/fvc/fvcVolumeIntegrate.C  : sum_c V_c * vf_c
+ *   linearInterpolate      interpolation/surfaceInterpolation/schemes/linear/linear.H : w*vf[own] + (1-w)*vf[nei];
+ *                          boundary face = patch value
+ *   fvc::div(flux, vf)     convectionSchemes/gaussConvectionScheme : surfaceIntegrate(flux * interpolate(vf))
+ *   fvc::div(vf)           fvc/fvcDiv.C + divSchemes/gaussDivScheme : surfaceIntegrate(Sf & interpolate(vf))
+ *   fvc::grad(vf)          gradSchemes/gaussGrad/gaussGrad.C : surfaceIntegrate-like sum of Sf * vf_f (boundary-value
+ *                          correction of grad only alters boundary values, which domainIntegrate never reads)
+ *   fvc::laplacian(1, vf)  laplacianSchemes/gaussLaplacianScheme : surfaceIntegrate(|Sf| * snGrad(vf)),
+ *                          snGradSchemes/correctedSnGrad : nonOrthDeltaCoeffs*(vf[nei]-vf[own])
+ *                          + nonOrthCorrectionVectors & linearInterpolate(grad(vf.component)); boundary faces:
+ *                          fvPatchField::snGrad = deltaCoeffs*(patchValue - patchInternalValue)
+ * Faces of `empty` patches hold no values in OpenFOAM and never contribute (bmask == 0).
+ * Known answers that check (a): tests/test_fvc_oracle.py.
+ *
+ * Layouts: vector fields AoS (x0,y0,z0,x1,...) as OpenFOAM stores them; boundary values as one flat array over
+ * boundary faces (face nInt+b <-> entry b); matrices column-major (Eigen); the C tensor column-major with the test
+ * index i fastest (Eigen::Tensor<double,3>, steadyNS.C:1002-1003).
+ */
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+typedef struct {
+    long long nCells, nInt, nBnd;
+    const int* owner;      /* nInt + nBnd */
+    const int* neighbour;  /* nInt */
+    const double* Sf;      /* 3*(nInt+nBnd) */
+    const double* magSf;   /* nInt+nBnd */
+    const double* w;       /* nInt: linear interpolation weights */
+    const double* dc;      /* nInt: nonOrthDeltaCoeffs */
+    const double* dcB;     /* nBnd: boundary deltaCoeffs */
+    const double* corr;    /* 3*nInt nonOrthCorrectionVectors, or NULL for "uncorrected" */
+    const double* V;       /* nCells */
+    const unsigned char* bmask; /* nBnd: 0 = face of an `empty` patch */
+} fvo_mesh;
+
+/* ---- operators ------------------------------------------------------------------------------------- */
+
+/* phi_f = linearInterpolate(U) & Sf   (steadyNS.C:1019-1021). phi: nInt+nBnd. */
+void fvo_flux(const fvo_mesh* m, const double* U, const double* Ub, double* phi)
+{
+    for (long long f = 0; f < m->nInt; f++) {
+        const int o = m->owner[f], n = m->neighbour[f];
+        const double w = m->w[f];
+        double s = 0.0;
+        for (int c = 0; c < 3; c++) s += (w * U[3 * o + c] + (1.0 - w) * U[3 * n + c]) * m->Sf[3 * f + c];
+        phi[f] = s;
+    }
+    for (long long b = 0; b < m->nBnd; b++) {
+        const long long f = m->nInt + b;
+        double s = 0.0;
+        if (m->bmask[b])
+            for (int c = 0; c < 3; c++) s += Ub[3 * b + c] * m->Sf[3 * f + c];
+        phi[f] = s;
+    }
+}
+
+/* out = fvc::div(phi, U) with Gauss linear: surfaceIntegrate(phi * linearInterpolate(U)). out: 3*nCells. */
+void fvo_div_phi_vec(const fvo_mesh* m, const double* phi, const double* U, const double* Ub, double* out)
+{
+    memset(out, 0, sizeof(double) * 3 * m->nCells);
+    for (long long f = 0; f < m->nInt; f++) {
+        const int o = m->owner[f], n = m->neighbour[f];
+        const double w = m->w[f];
+        for (int c = 0; c < 3; c++) {
+            const double v = phi[f] * (w * U[3 * o + c] + (1.0 - w) * U[3 * n + c]);
+            out[3 * o + c] += v;
+            out[3 * n + c] -= v;
+        }
+    }
+    for (long long b = 0; b < m->nBnd; b++) {
+        if (!m->bmask[b]) continue;
+        const int o = m->owner[m->nInt + b];
+        for (int c = 0; c < 3; c++) out[3 * o + c] += phi[m->nInt + b] * Ub[3 * b + c];
+    }
+    for (long long i = 0; i < m->nCells; i++)
+        for (int c = 0; c < 3; c++) out[3 * i + c] /= m->V[i];
+}
+
+/* out = fvc::div(U): surfaceIntegrate(Sf & linearInterpolate(U)). out: nCells. */
+void fvo_div_vec(const fvo_mesh* m, const double* U, const double* Ub, double* out)
+{
+    double* phi = (double*)malloc(sizeof(double) * (m->nInt + m->nBnd));
+    fvo_flux(m, U, Ub, phi);
+    memset(out, 0, sizeof(double) * m->nCells);
+    for (long long f = 0; f < m->nInt; f++) {
+        out[m->owner[f]] += phi[f];
+        out[m->neighbour[f]] -= phi[f];
+    }
+    for (long long b = 0; b < m->nBnd; b++)
+        if (m->bmask[b]) out[m->owner[m->nInt + b]] += phi[m->nInt + b];
+    for (long long i = 0; i < m->nCells; i++) out[i] /= m->V[i];
+    free(phi);
+}
+
+/* out = fvc::grad(p), Gauss linear. out: 3*nCells. */
+void fvo_grad_scalar(const fvo_mesh* m, const double* p, const double* pb, double* out)
+{
+    memset(out, 0, sizeof(double) * 3 * m->nCells);
+    for (long long f = 0; f < m->nInt; f++) {
+        const int o = m->owner[f], n = m->neighbour[f];
+        const double pf = m->w[f] * p[o] + (1.0 - m->w[f]) * p[n];
+        for (int c = 0; c < 3; c++) {
+            const double v = m->Sf[3 * f + c] * pf;
+            out[3 * o + c] += v;
+            out[3 * n + c] -= v;
+        }
+    }
+    for (long long b = 0; b < m->nBnd; b++) {
+        if (!m->bmask[b]) continue;
+        const int o = m->owner[m->nInt + b];
+        for (int c = 0; c < 3; c++) out[3 * o + c] += m->Sf[3 * (m->nInt + b) + c] * pb[b];
+    }
+    for (long long i = 0; i < m->nCells; i++)
+        for (int c = 0; c < 3; c++) out[3 * i + c] /= m->V[i];
+}
+
+/* T = fvc::grad(U), Gauss linear: T[cell][i][j] = sum_f Sf_i U_f,j / V (outer product Sf * U_f). out: 9*nCells. */
+void fvo_grad_vec(const fvo_mesh* m, const double* U, const double* Ub, double* out)
+{
+    memset(out, 0, sizeof(double) * 9 * m->nCells);
+    for (long long f = 0; f < m->nInt; f++) {
+        const int o = m->owner[f], n = m->neighbour[f];
+        const double w = m->w[f];
+        for (int j = 0; j < 3; j++) {
+            const double uf = w * U[3 * o + j] + (1.0 - w) * U[3 * n + j];
+            for (int i = 0; i < 3; i++) {
+                const double v = m->Sf[3 * f + i] * uf;
+                out[9 * o + 3 * i + j] += v;
+                out[9 * n + 3 * i + j] -= v;
+            }
+        }
+    }
+    for (long long b = 0; b < m->nBnd; b++) {
+        if (!m->bmask[b]) continue;
+        const int o = m->owner[m->nInt + b];
+        for (int j = 0; j < 3; j++)
+            for (int i = 0; i < 3; i++) out[9 * o + 3 * i + j] += m->Sf[3 * (m->nInt + b) + i] * Ub[3 * b + j];
+    }
+    for (long long c = 0; c < m->nCells; c++)
+        for (int k = 0; k < 9; k++) out[9 * c + k] /= m->V[c];
+}
+
+/* out = fvc::laplacian(dimensionedScalar(1), U), Gauss linear corrected (m->corr != NULL) or uncorrected.
+ * gamma = 1 so gammaMagSf = |Sf| (gaussLaplacianScheme::fvcLaplacian). out: 3*nCells. */
+void fvo_laplacian_vec(const fvo_mesh* m, const double* U, const double* Ub, double* out)
+{
+    double* T = NULL;
+    if (m->corr) {
+        T = (double*)malloc(sizeof(double) * 9 * m->nCells);
+        fvo_grad_vec(m, U, Ub, T);
+    }
+    memset(out, 0, sizeof(double) * 3 * m->nCells);
+    for (long long f = 0; f < m->nInt; f++) {
+        const int o = m->owner[f], n = m->neighbour[f];
+        const double w = m->w[f];
+        for (int j = 0; j < 3; j++) {
+            double sn = m->dc[f] * (U[3 * n + j] - U[3 * o + j]);
+            if (T) {
+                double cr = 0.0; /* nonOrthCorrectionVectors & linearInterpolate(grad(U.component(j))) */
+                for (int i = 0; i < 3; i++)
+                    cr += m->corr[3 * f + i] * (w * T[9 * o + 3 * i + j] + (1.0 - w) * T[9 * n + 3 * i + j]);
+                sn += cr;
+            }
+            const double v = m->magSf[f] * sn;
+            out[3 * o + j] += v;
+            out[3 * n + j] -= v;
+        }
+    }
+    for (long long b = 0; b < m->nBnd; b++) {
+        if (!m->bmask[b]) continue;
+        const long long f = m->nInt + b;
+        const int o = m->owner[f];
+        for (int j = 0; j < 3; j++) out[3 * o + j] += m->magSf[f] * (m->dcB[b] * (Ub[3 * b + j] - U[3 * o + j]));
+    }
+    for (long long c = 0; c < m->nCells; c++)
+        for (int j = 0; j < 3; j++) out[3 * c + j] /= m->V[c];
+    free(T);
+}
+
+/* fvc::domainIntegrate(a & b).value() for dim-component fields: sum_c V_c * (a_c . b_c) */
+double fvo_domain_integrate_dot(const fvo_mesh* m, const double* a, const double* b, int dim)
+{
+    double s = 0.0;
+    for (long long c = 0; c < m->nCells; c++) {
+        double d = 0.0;
+        for (int k = 0; k < dim; k++) d += a[dim * c + k] * b[dim * c + k];
+        s += m->V[c] * d;
+    }
+    return s;
+}
+
+/* ---- term builders: the reference's loop nests ----------------------------------------------------------
+ * U[i], Ub[i]: the N fields of L_U_SUPmodes (lift, U modes, supremizer modes; steadyNS.C:561-585), internal and
+ * boundary values; P[j], Pb[j]: the Np pressure modes. */
+
+/* steadyNS::mass_term, steadyNS.C:1085-1108.  M: N x N col-major. */
+void fvo_mass_term(const fvo_mesh* m, int N, const double* const* U, double* M)
+{
+    for (int i = 0; i < N; i++)
+        for (int j = 0; j < N; j++) M[i + (size_t)j * N] = fvo_domain_integrate_dot(m, U[i], U[j], 3);
+}
+
+/* steadyNS::diffusive_term, steadyNS.C:883-907: B(i,j) = domainIntegrate(U_i & laplacian(1, U_j)).
+ * The laplacian of U_j is evaluated once per j instead of once per (i,j): same values, same order inside. */
+void fvo_diffusive_term(const fvo_mesh* m, int N, const double* const* U, const double* const* Ub, double* B)
+{
+    double* L = (double*)malloc(sizeof(double) * 3 * m->nCells);
+    for (int j = 0; j < N; j++) {
+        fvo_laplacian_vec(m, U[j], Ub[j], L);
+        for (int i = 0; i < N; i++) B[i + (size_t)j * N] = fvo_domain_integrate_dot(m, U[i], L, 3);
+    }
+    free(L);
+}
+
+/* steadyNS::pressure_gradient_term, steadyNS.C:935-960: K(i,j) = domainIntegrate(U_i & grad(P_j)). K: N x Np. */
+void fvo_pressure_gradient_term(const fvo_mesh* m, int N, int Np, const double* const* U, const double* const* P,
+                                const double* const* Pb, double* K)
+{
+    double* G = (double*)malloc(sizeof(double) * 3 * m->nCells);
+    for (int j = 0; j < Np; j++) {
+        fvo_grad_scalar(m, P[j], Pb[j], G);
+        for (int i = 0; i < N; i++) K[i + (size_t)j * N] = fvo_domain_integrate_dot(m, U[i], G, 3);
+    }
+    free(G);
+}
+
+/* steadyNS::divergence_term, steadyNS.C:1112-1137: P(i,j) = domainIntegrate(P_i * div(U_j)). Pm: Np x N. */
+void fvo_divergence_term(const fvo_mesh* m, int N, int Np, const double* const* U, const double* const* Ub,
+                         const double* const* P, double* Pm)
+{
+    double* D = (double*)malloc(sizeof(double) * m->nCells);
+    for (int j = 0; j < N; j++) {
+        fvo_div_vec(m, U[j], Ub[j], D);
+        for (int i = 0; i < Np; i++) Pm[i + (size_t)j * Np] = fvo_domain_integrate_dot(m, P[i], D, 1);
+    }
+    free(D);
+}
+
+/* steadyNS::convective_term_tens, steadyNS.C:997-1036 (fluxMethod != "consistent"): the reference's own loop
+ * nest, flux and div re-evaluated for every (i,j,k).  C(i,j,k) at C[i + N*(j + N*k)]. */
+void fvo_convective_term_tens(const fvo_mesh* m, int N, const double* const* U, const double* const* Ub, double* C)
+{
+    double* phi = (double*)malloc(sizeof(double) * (m->nInt + m->nBnd));
+    double* D = (double*)malloc(sizeof(double) * 3 * m->nCells);
+    for (int i = 0; i < N; i++)
+        for (int j = 0; j < N; j++)
+            for (int k = 0; k < N; k++) {
+                fvo_flux(m, U[j], Ub[j], phi);
+                fvo_div_phi_vec(m, phi, U[k], Ub[k], D);
+                C[i + (size_t)N * (j + (size_t)N * k)] = fvo_domain_integrate_dot(m, U[i], D, 3);
+            }
+    free(phi);
+    free(D);
+}
+
+/* steadyNS::convective_term_tens_cache, steadyNS.C:1038-1083: flux hoisted per j, div per (j,k). */
+void fvo_convective_term_tens_cache(const fvo_mesh* m, int N, const double* const* U, const double* const* Ub, double* C)
+{
+    double* phi = (double*)malloc(sizeof(double) * (m->nInt + m->nBnd));
+    double* D = (double*)malloc(sizeof(double) * 3 * m->nCells);
+    for (int j = 0; j < N; j++) {
+        fvo_flux(m, U[j], Ub[j], phi);
+        for (int k = 0; k < N; k++) {
+            fvo_div_phi_vec(m, phi, U[k], Ub[k], D);
+            for (int i = 0; i < N; i++) C[i + (size_t)N * (j + (size_t)N * k)] = fvo_domain_integrate_dot(m, U[i], D, 3);
+        }
+    }
+    free(phi);
+    free(D);
+}
+
+/* ---- addressing: cell -> face CSR in ascending face order (= primitiveMesh::cells() order) -------------
+ * entry = +(f+1) when the cell owns face f (Sf points outwards), -(f+1) when it is the neighbour.
+ * off: nCells+1, ent/other: 2*nInt+nBnd. other = the cell across the face, or -(b+1) for boundary face b. */
+void fvo_cell_faces(const fvo_mesh* m, int* off, int* ent, int* other)
+{
+    const long long nF = m->nInt + m->nBnd;
+    int* cnt = (int*)calloc(m->nCells + 1, sizeof(int));
+    for (long long f = 0; f < nF; f++) cnt[m->owner[f] + 1]++;
+    for (long long f = 0; f < m->nInt; f++) cnt[m->neighbour[f] + 1]++;
+    off[0] = 0;
+    for (long long c = 0; c < m->nCells; c++) off[c + 1] = off[c] + cnt[c + 1];
+    for (long long c = 0; c < m->nCells; c++) cnt[c] = off[c];
+    for (long long f = 0; f < nF; f++) {
+        const int o = m->owner[f];
+        ent[cnt[o]] = (int)(f + 1);
+        other[cnt[o]++] = (f < m->nInt) ? m->neighbour[f] : -(int)(f - m->nInt + 1);
+        if (f < m->nInt) {
+            const int n = m->neighbour[f];
+            ent[cnt[n]] = -(int)(f + 1);
+            other[cnt[n]++] = o;
+        }
+    }
+    free(cnt);
+}

@@ -1,0 +1,136 @@
+"""CPU tests of the projection oracle (oracle/fvc_oracle.c + oracle/polymesh.py) against known answers.
+The reference ships no golden values for the projected operators and OpenFOAM is not
+installable here, so the oracle is checked through closed-form properties of the discrete operators."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import fvc, polymesh as pm
+
+REF = "/root/reference/tutorials/CFD"
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def lin_vec(X, A, b):
+    return np.ascontiguousarray((X @ A.T + b).ravel())
+
+
+@pytest.fixture(scope="module")
+def box():
+    return pm.synthetic_hex(7, 6, 5, kind="box", seed=3, perturb=0.0)
+
+
+@pytest.fixture(scope="module")
+def cyl():
+    return pm.synthetic_hex(8, 20, 3, kind="cylinder", seed=4, perturb=0.2)
+
+
+def test_cavity_mesh_known_volume():
+    if not os.path.isdir(REF):
+        pytest.skip("reference tree absent")
+    m = pm.load_reference_mesh(os.path.join(REF, "01POD"))
+    assert (m.nCells, m.nInt, m.nBnd) == (10000, 19800, 20400)
+    assert np.abs(m.V - 1e-8).max() < 1e-20  # 100x100x1 block of a 0.1x0.1x0.01 box (system/blockMeshDict)
+    assert np.abs(m.w - 0.5).max() < 1e-12 and np.abs(m.corr).max() < 1e-12
+    assert m.bmask.sum() == 400
+
+
+def test_fixture_mesh_matches_reference_files():
+    m = pm.load_compact(os.path.join(GOLD, "mesh_04unsteadyNS.npz"))
+    assert (m.nCells, m.nInt, m.nBnd) == (11644, 23266, 23886)
+    if os.path.isdir(REF):
+        r = pm.load_reference_mesh(os.path.join(REF, "04unsteadyNS"))
+        assert np.array_equal(m.owner, r.owner) and np.array_equal(m.neighbour, r.neighbour)
+        assert np.array_equal(m.Sf, r.Sf) and np.array_equal(m.V, r.V)
+
+
+@pytest.mark.parametrize("which", ["box", "cyl"])
+def test_closed_cells_and_constant_fields(which, box, cyl):
+    m = box if which == "box" else cyl
+    o = fvc.Oracle(m)
+    s = np.zeros((m.nCells, 3))
+    np.add.at(s, m.owner, m.Sf)
+    np.add.at(s, m.neighbour, -m.Sf[:m.nInt])
+    assert np.abs(s).max() < 1e-13 * m.magSf.max()
+    U = np.tile([1.0, -2.0, 0.5], m.nCells)
+    Ub = np.tile([1.0, -2.0, 0.5], m.nBnd)
+    scale = m.magSf.max() / m.V.min()
+    assert np.abs(o.div(U, Ub)).max() < 1e-12 * scale
+    assert np.abs(o.laplacian(U, Ub)).max() < 1e-10 * scale
+    assert np.abs(o.grad(np.ones(m.nCells), np.ones(m.nBnd))).max() < 1e-12 * scale
+    assert np.abs(o.grad_vec(U, Ub)).max() < 1e-12 * scale
+
+
+def test_linear_fields_exact_on_orthogonal_mesh(box):
+    m = box
+    o = fvc.Oracle(m)
+    rng = np.random.default_rng(0)
+    A, b = rng.standard_normal((3, 3)), rng.standard_normal(3)
+    U, Ub = lin_vec(m.Cc, A, b), lin_vec(m.Cf[m.nInt:], A, b)
+    T = o.grad_vec(U, Ub).reshape(-1, 3, 3)  # T[c][i][j] = d_i u_j = A[j][i]
+    assert np.abs(T - A.T).max() < 1e-11
+    assert np.abs(o.div(U, Ub) - np.trace(A)).max() < 1e-11
+    g = rng.standard_normal(3)
+    p, pb = m.Cc @ g + 0.3, m.Cf[m.nInt:] @ g + 0.3
+    assert np.abs(o.grad(p, pb).reshape(-1, 3) - g).max() < 1e-11
+    assert np.abs(o.laplacian(U, Ub)).max() < 1e-9  # laplacian of a linear field vanishes
+
+
+def test_gauss_theorem_and_flux_conservation(cyl):
+    m = cyl
+    o = fvc.Oracle(m)
+    U, Ub, _, _ = fvc.synthetic_basis(m, 2, 0, seed=1)
+    phi = o.flux(U[0], Ub[0])
+    d = o.div(U[0], Ub[0])
+    assert abs((m.V * d).sum() - phi[m.nInt:].sum()) < 1e-11 * np.abs(phi).sum()
+    dv = o.div_phi(phi, U[1], Ub[1]).reshape(-1, 3)
+    bsum = (phi[m.nInt:, None] * Ub[1].reshape(-1, 3)).sum(0)
+    assert np.abs((m.V[:, None] * dv).sum(0) - bsum).max() < 1e-11 * np.abs(phi).sum()
+
+
+def test_builders_consistent(cyl):
+    m = cyl
+    o = fvc.Oracle(m)
+    U, Ub, P, Pb = fvc.synthetic_basis(m, 4, 2, seed=2)
+    C1 = o.convective_term_tens(U, Ub, cache=False)
+    C2 = o.convective_term_tens(U, Ub, cache=True)
+    assert np.array_equal(C1, C2)  # convective_term_tens == convective_term_tens_cache (steadyNS.C:997 vs :1038)
+    # C(i,j,k) is linear in the convecting field j
+    U2 = [U[0], U[1] + 2.0 * U[2], U[2], U[3]]
+    Ub2 = [Ub[0], Ub[1] + 2.0 * Ub[2], Ub[2], Ub[3]]
+    C3 = o.convective_term_tens(U2, Ub2)
+    ii = [0, 2, 3]  # test functions that did not change
+    assert np.abs(C3[ii, 1, 0] - (C2[ii, 1, 0] + 2.0 * C2[ii, 2, 0])).max() < 1e-12 * np.abs(C2).max()
+    M = o.mass_term(U)
+    Vd = np.repeat(m.V, 3)
+    assert np.allclose(M, np.array([[np.sum(Vd * a * b) for b in U] for a in U]), rtol=1e-13)
+    B = o.diffusive_term(U, Ub)
+    assert np.allclose(B[:, 1], [np.sum(Vd * a * o.laplacian(U[1], Ub[1])) for a in U], rtol=1e-13)
+    K = o.pressure_gradient_term(U, P, Pb)
+    assert K.shape == (4, 2)
+    Pm = o.divergence_term(U, Ub, P)
+    assert Pm.shape == (2, 4)
+    assert np.allclose(Pm[1, 2], np.sum(m.V * P[1] * o.div(U[2], Ub[2])), rtol=1e-13)
+
+
+def test_uncorrected_equals_corrected_on_orthogonal_mesh(box):
+    U, Ub, _, _ = fvc.synthetic_basis(box, 1, 0, seed=5)
+    a = fvc.Oracle(box, corrected=True).laplacian(U[0], Ub[0])
+    b = fvc.Oracle(box, corrected=False).laplacian(U[0], Ub[0])
+    assert np.abs(a - b).max() < 1e-9 * np.abs(a).max()
+
+
+def test_cell_faces_csr(cyl):
+    m = cyl
+    off, ent, other = fvc.Oracle(m).cell_faces()
+    assert off[-1] == 2 * m.nInt + m.nBnd
+    for c in [0, 1, m.nCells // 2, m.nCells - 1]:
+        e = ent[off[c]:off[c + 1]]
+        f = np.abs(e) - 1
+        assert np.all(np.diff(f) > 0)  # ascending face order
+        for fe, ee, oc in zip(f, e, other[off[c]:off[c + 1]]):
+            if ee > 0:
+                assert m.owner[fe] == c and (oc == (m.neighbour[fe] if fe < m.nInt else -(fe - m.nInt + 1)))
+            else:
+                assert m.neighbour[fe] == c and oc == m.owner[fe]
