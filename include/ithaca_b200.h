@@ -111,6 +111,61 @@ int ithaca_b200_pod_lift(ithaca_b200_t* h, int r, int norm_kind, double* const* 
  * Foam2Eigen.C:272-411); out: rows*r col-major. Host pointers. Must follow pod_lift. */
 int ithaca_b200_pod_lift_patch(ithaca_b200_t* h, const double* Sbc, int64_t rows, double* out);
 
+/* ---- Galerkin projection: steadyNS::projectSUP term builders ---------------------------------------
+ * (src/ITHACA_FOMPROBLEMS/steadyNS/steadyNS.C:556-707 calls :883-1137; inherited by unsteadyNS,
+ *  src/ITHACA_FOMPROBLEMS/unsteadyNS/unsteadyNS.H:61). Scheme set: Gauss linear (grad, div, interpolate),
+ *  Gauss linear corrected | uncorrected (laplacian). */
+
+/* Mesh addressing and geometry exactly as OpenFOAM holds them (32-bit labels):
+ *   owner[nInt+nBnd], neighbour[nInt]      mesh.owner(), mesh.neighbour() (faces in OpenFOAM order: internal, then patches)
+ *   Sf[3*(nInt+nBnd)], magSf[nInt+nBnd]    mesh.Sf(), mesh.magSf() (internal field then boundary patches in order)
+ *   weights[nInt]                          mesh.weights() (linear interpolation)
+ *   nonOrthDeltaCoeffs[nInt]               mesh.nonOrthDeltaCoeffs()
+ *   bndDeltaCoeffs[nBnd]                   patch.deltaCoeffs() of every boundary face
+ *   nonOrthCorrVec[3*nInt] or NULL         mesh.nonOrthCorrectionVectors(); NULL selects the "uncorrected" laplacian
+ *   V[nCells]                              mesh.V()
+ *   bndMask[nBnd] or NULL                  0 for faces of `empty` patches (they hold no values and never contribute)
+ * The cell->face addressing is built on the device. Host or device pointers. */
+int ithaca_b200_mesh_upload(ithaca_b200_t* h, int64_t nCells, int64_t nIntFaces, int64_t nBndFaces,
+                            const int32_t* owner, const int32_t* neighbour, const double* Sf, const double* magSf,
+                            const double* weights, const double* nonOrthDeltaCoeffs, const double* bndDeltaCoeffs,
+                            const double* nonOrthCorrVec, const double* V, const unsigned char* bndMask);
+
+/* The device-built cell->face CSR, for the bit-exact addressing check: off[nCells+1]; ent[2*nInt+nBnd] = +(f+1) when
+ * the cell owns face f, -(f+1) when it is its neighbour, ascending face index per cell (primitiveMesh::cells() order);
+ * other[...] = the cell across the face, -(b+1) for boundary face b. digest = FNV-1a 64 of the three arrays.
+ * Any output may be NULL. */
+int ithaca_b200_mesh_addressing(ithaca_b200_t* h, int32_t* off, int32_t* ent, int32_t* other, uint64_t* digest);
+
+/* Basis fields. which = 0: the n vector fields of L_U_SUPmodes (lift, U modes, supremizer modes in that order,
+ * steadyNS.C:561-585), int_ptrs[j] -> 3*nCells doubles (&field.ref()[0][0]), bnd_ptrs[j] -> 3*nBnd doubles (boundary
+ * patch values in face order). which = 1: the n scalar fields of Pmodes (nCells / nBnd doubles). */
+int ithaca_b200_basis_upload(ithaca_b200_t* h, int which, const double* const* int_ptrs,
+                             const double* const* bnd_ptrs, int n);
+
+enum { IB200_OP_M = 0, IB200_OP_B = 1, IB200_OP_K = 2, IB200_OP_P = 3, IB200_OP_C = 4 };
+/* One projected operator, laid out as the reference's Eigen object (column-major):
+ *   IB200_OP_M  mass_term              steadyNS.C:1085-1108   N x N        M(i,j) = int U_i . U_j
+ *   IB200_OP_B  diffusive_term         steadyNS.C:883-907     N x N        B(i,j) = int U_i . laplacian(1, U_j)
+ *   IB200_OP_K  pressure_gradient_term steadyNS.C:935-960     N x Np       K(i,j) = int U_i . grad(P_j)
+ *   IB200_OP_P  divergence_term        steadyNS.C:1112-1137   Np x N       P(i,j) = int P_i div(U_j)
+ *   IB200_OP_C  convective_term_tens   steadyNS.C:997-1036    N x N x N    C(i,j,k) = int U_i . div(interpolate(U_j) & Sf, U_k),
+ *               (values identical to convective_term_tens_cache :1038-1083), stored with i fastest. */
+int ithaca_b200_project(ithaca_b200_t* h, int op, double* out);
+
+enum { IB200_FVC_FLUX = 0, IB200_FVC_DIV_PHI = 1, IB200_FVC_LAPLACIAN = 2, IB200_FVC_GRAD_P = 3, IB200_FVC_DIV_U = 4 };
+/* One materialised fvc operator field (used by the parity tests of the gather kernels):
+ *   FLUX      linearInterpolate(U_j) & Sf                 nInt+nBnd doubles
+ *   DIV_PHI   fvc::div(flux_j, U_k)                       3*nCells
+ *   LAPLACIAN fvc::laplacian(1, U_j)                      3*nCells
+ *   GRAD_P    fvc::grad(P_j)                              3*nCells
+ *   DIV_U     fvc::div(U_j)                               nCells */
+int ithaca_b200_fvc_eval(ithaca_b200_t* h, int op, int j, int k, double* out);
+
+/* Device times (ms) of the last ithaca_b200_project call: out[0]=face flux, [1]=div(phi,U), [2]=laplacian (+grad tensor),
+ * [3]=grad(p), [4]=div(U), [5]=contraction. */
+int ithaca_b200_proj_timings(ithaca_b200_t* h, double* out, int n);
+
 /* ---- measurement helpers -------------------------------------------------------------------- */
 /* Register-resident DMMA.8x8x4 (mma.sync.m8n8k4.f64) issue-rate microbenchmark on `device`:
  * the measured FP64 tensor peak used as the Gram kernel's roofline denominator. */

@@ -23,6 +23,8 @@ SYMBOLS = [
     "ithaca_b200_pod_upload", "ithaca_b200_pod_gram", "ithaca_b200_pod_eig", "ithaca_b200_pod_set_gram",
     "ithaca_b200_pod_postprocess_eigenvalues", "ithaca_b200_pod_lift", "ithaca_b200_pod_lift_patch",
     "ithaca_b200_dmma_peak",
+    "ithaca_b200_mesh_upload", "ithaca_b200_mesh_addressing", "ithaca_b200_basis_upload", "ithaca_b200_project",
+    "ithaca_b200_fvc_eval", "ithaca_b200_proj_timings",
 ]
 
 _lib = None
@@ -63,6 +65,12 @@ def lib():
         L.ithaca_b200_pod_lift.argtypes = [P, I, I, P, P]
         L.ithaca_b200_pod_lift_patch.argtypes = [P, P, L64, P]
         L.ithaca_b200_dmma_peak.argtypes = [I, ctypes.POINTER(D)]
+        L.ithaca_b200_mesh_upload.argtypes = [P, L64, L64, L64] + [P] * 11
+        L.ithaca_b200_mesh_addressing.argtypes = [P, P, P, P, ctypes.POINTER(ctypes.c_uint64)]
+        L.ithaca_b200_basis_upload.argtypes = [P, I, P, P, I]
+        L.ithaca_b200_project.argtypes = [P, I, P]
+        L.ithaca_b200_fvc_eval.argtypes = [P, I, I, I, P]
+        L.ithaca_b200_proj_timings.argtypes = [P, P, I]
         _lib = L
     return _lib
 
@@ -213,6 +221,74 @@ class Pod:
         out = np.zeros((Sbc.shape[0], r), order="F")
         self._chk(self.L.ithaca_b200_pod_lift_patch(self.h, Sbc.ctypes.data, Sbc.shape[0], out.ctypes.data))
         return out
+
+
+OPS = {"M": 0, "B": 1, "K": 2, "P": 3, "C": 4}
+FVC = {"flux": 0, "div_phi": 1, "laplacian": 2, "grad_p": 3, "div_u": 4}
+
+
+class Projector:
+    """Galerkin projection on a Pod handle's GPU: mirrors the steadyNS term builders
+    (src/ITHACA_FOMPROBLEMS/steadyNS/steadyNS.C:883-1137). `mesh` is any object with the attributes of
+    ithaca_b200_mesh_upload's arguments (nCells, nInt, nBnd, owner, neighbour, Sf, magSf, w, dc, dcB, corr, V, bmask)."""
+
+    TIMER_NAMES = ["flux", "div_phi", "laplacian", "grad_p", "div_u", "contraction"]
+
+    def __init__(self, pod):
+        self.pod, self.L, self.h = pod, pod.L, pod.h
+        self.N = self.Np = 0
+
+    def set_mesh(self, mesh, corrected=True):
+        c = lambda a, dt: np.ascontiguousarray(a, dtype=dt)
+        own = np.concatenate([c(mesh.owner, np.int32)])
+        k = dict(owner=own, nei=c(mesh.neighbour, np.int32), Sf=c(mesh.Sf, np.float64), magSf=c(mesh.magSf, np.float64),
+                 w=c(mesh.w, np.float64), dc=c(mesh.dc, np.float64), dcB=c(mesh.dcB, np.float64),
+                 corr=c(mesh.corr, np.float64) if corrected else None, V=c(mesh.V, np.float64),
+                 bmask=c(mesh.bmask, np.uint8))
+        self.nCells, self.nInt, self.nBnd = int(mesh.nCells), int(mesh.nInt), int(mesh.nBnd)
+        self.pod._chk(self.L.ithaca_b200_mesh_upload(
+            self.h, self.nCells, self.nInt, self.nBnd, _ptr(k["owner"]), _ptr(k["nei"]), _ptr(k["Sf"]), _ptr(k["magSf"]),
+            _ptr(k["w"]), _ptr(k["dc"]), _ptr(k["dcB"]), _ptr(k["corr"]), _ptr(k["V"]), _ptr(k["bmask"])))
+
+    def addressing(self):
+        nnz = 2 * self.nInt + self.nBnd
+        off = np.zeros(self.nCells + 1, dtype=np.int32)
+        ent = np.zeros(nnz, dtype=np.int32)
+        other = np.zeros(nnz, dtype=np.int32)
+        d = ctypes.c_uint64(0)
+        self.pod._chk(self.L.ithaca_b200_mesh_addressing(self.h, off.ctypes.data, ent.ctypes.data, other.ctypes.data, ctypes.byref(d)))
+        return off, ent, other, d.value
+
+    def set_basis(self, which, fields, bfields):
+        keep = [np.ascontiguousarray(f, dtype=np.float64) if isinstance(f, np.ndarray) else f for f in fields]
+        keepb = [np.ascontiguousarray(f, dtype=np.float64) if isinstance(f, np.ndarray) else f for f in bfields]
+        n = len(keep)
+        a = (ctypes.c_void_p * n)(*[_ptr(f) for f in keep])
+        b = (ctypes.c_void_p * n)(*[_ptr(f) for f in keepb])
+        self.pod._chk(self.L.ithaca_b200_basis_upload(self.h, 0 if which == "U" else 1, a, b, n))
+        if which == "U":
+            self.N = n
+        else:
+            self.Np = n
+
+    def project(self, op):
+        N, Np = self.N, self.Np
+        shape = {"M": (N, N), "B": (N, N), "K": (N, Np), "P": (Np, N), "C": (N, N, N)}[op]
+        out = np.zeros(shape, order="F")
+        self.pod._chk(self.L.ithaca_b200_project(self.h, OPS[op], out.ctypes.data))
+        return out
+
+    def fvc(self, op, j, k=0):
+        n = {"flux": self.nInt + self.nBnd, "div_phi": 3 * self.nCells, "laplacian": 3 * self.nCells,
+             "grad_p": 3 * self.nCells, "div_u": self.nCells}[op]
+        out = np.zeros(n)
+        self.pod._chk(self.L.ithaca_b200_fvc_eval(self.h, FVC[op], j, k, out.ctypes.data))
+        return out
+
+    def timings(self):
+        out = np.zeros(6)
+        self.pod._chk(self.L.ithaca_b200_proj_timings(self.h, out.ctypes.data, 6))
+        return dict(zip(self.TIMER_NAMES, out.tolist()))
 
 
 def check_nmodes(m, nmodes, solver):

@@ -206,6 +206,7 @@ int ithaca_b200_destroy(ithaca_b200_t* h)
     if (!h) return IB200_OK;
     cudaSetDevice(h->device);
     cudaStreamSynchronize(h->stream);
+    proj_destroy(h);
     if (h->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->nccl_comm);
     for (void* p : {(void*)h->dV, (void*)h->dS, (void*)h->dG, (void*)h->dWs, (void*)h->dQ, (void*)h->dW,
                     (void*)h->dEvals, (void*)h->dQr, (void*)h->dPhi, (void*)h->dNormPart, (void*)h->dNorm,

@@ -92,6 +92,8 @@ __device__ __forceinline__ uint32_t swz128(uint32_t row, uint32_t k)
 struct ithaca_b200;
 
 namespace ib200 {
+struct ProjState;  // proj.cu
+void proj_destroy(ithaca_b200* h);
 void set_error(ithaca_b200* h, const std::string& msg);
 
 // cuTensorMapEncodeTiled through cudaGetDriverEntryPoint (no link-time libcuda dependency).
@@ -116,6 +118,14 @@ int eig_launch(ithaca_b200* h, int* sweeps);
 // lift.cu
 int lift_launch(ithaca_b200* h, int r, int norm_kind);
 int lift_patch_launch(ithaca_b200* h, const double* dSbc, int64_t rows, double* dOut);
+// gram.cu: general weighted contraction  out(i,j) = sum_k A(k,i) * V[k/dim] * B(k,j)  (V == nullptr: unweighted).
+// A: Ma columns of lda doubles, B: Nb columns of ldb doubles, both with K valid rows (K-contiguous columns).
+// symmetric != 0: B == A, only the lower triangle is computed and mirrored. out(i,j) is written to
+// out[i*rs + (j / cinner)*cso + (j % cinner)*csi] (doubles), so the caller can scatter straight into a matrix
+// (cinner = INT_MAX, csi = column stride) or into slices of a tensor.
+int atvb_launch(ithaca_b200* h, const double* A, long long lda, int Ma, const double* B, long long ldb, int Nb,
+                long long K, const double* V, int dim, int symmetric, double* out, long long rs, int cinner,
+                long long cso, long long csi);
 }  // namespace ib200
 
 typedef int (*ib200_allreduce_fn)(void* comm, const void* send, void* recv, size_t count, int dtype,
@@ -164,4 +174,7 @@ struct ithaca_b200 {
     void* dJobs = nullptr;
     size_t dJobs_cap = 0;
     int* dFlags = nullptr;
+
+    // ---- projection state (proj.cu) ----
+    ib200::ProjState* proj = nullptr;
 };

@@ -30,7 +30,8 @@ constexpr int GRAM_THREADS = 512;                // 15 MMA warps + 1 producer wa
 struct GramJob {
     int nbox;
     int ntiles;
-    int boxrow[GRAM_NBMAX];          // first snapshot of each box
+    int boxrow[GRAM_NBMAX];          // first column (snapshot / field) of each box
+    int boxmap[GRAM_NBMAX];          // 0 = operand A (tile rows), 1 = operand B (tile columns)
     unsigned char ta[GRAM_MAXTILES]; // box index of the tile's rows (i)
     unsigned char tb[GRAM_MAXTILES]; // box index of the tile's columns (j)
     unsigned char pad[2];
@@ -38,9 +39,10 @@ struct GramJob {
 };
 
 __global__ void __launch_bounds__(GRAM_THREADS, 1)
-gram_kernel(const __grid_constant__ CUtensorMap tmS, const double* __restrict__ V, int dim,
-            long long Nd, int m, const GramJob* __restrict__ jobs, int njobs, long long kchunk,
-            int nstages, int stage_bytes, double* __restrict__ ws)
+gram_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const double* __restrict__ V, int dim, long long Nd, int Ma, int Nb,
+            const GramJob* __restrict__ jobs, int njobs, long long kchunk, int nstages, int stage_bytes,
+            double* __restrict__ ws)
 {
     constexpr int WF = GRAM_WF;
     extern __shared__ __align__(1024) unsigned char smem[];
@@ -73,7 +75,7 @@ gram_kernel(const __grid_constant__ CUtensorMap tmS, const double* __restrict__ 
 
     if (warp == GRAM_MAXTILES) {
         // ---------------- producer warp ----------------
-        if (lane == 0) tma_prefetch_desc(&tmS);
+        if (lane == 0) { tma_prefetch_desc(&tmA); tma_prefetch_desc(&tmB); }
         const int nbox = job->nbox;
         for (int it = 0; it < niter; it++) {
             const int s = it % nstages;
@@ -81,14 +83,14 @@ gram_kernel(const __grid_constant__ CUtensorMap tmS, const double* __restrict__ 
             const long long k0 = k_begin + (long long)it * GRAM_KT;
             if (lane < GRAM_KT) {
                 const long long k = k0 + lane;
-                wsm[s * GRAM_KT + lane] = (k < Nd) ? V[k / dim] : 0.0;
+                wsm[s * GRAM_KT + lane] = (k < Nd) ? (V ? V[k / dim] : 1.0) : 0.0;
             }
             __syncwarp();
             if (lane == 0) {
                 mbar_arrive_expect_tx(&full[s], (uint32_t)(nbox * GRAM_BOXB));
                 unsigned char* dst = panels + (size_t)s * stage_bytes;
                 for (int b = 0; b < nbox; b++)
-                    tma_load_2d(dst + b * GRAM_BOXB, &tmS, (int)k0, job->boxrow[b], &full[s]);
+                    tma_load_2d(dst + b * GRAM_BOXB, job->boxmap[b] ? &tmB : &tmA, (int)k0, job->boxrow[b], &full[s]);
             }
         }
         return;
@@ -148,7 +150,7 @@ gram_kernel(const __grid_constant__ CUtensorMap tmS, const double* __restrict__ 
 
     // ---------------- epilogue: partial tile -> workspace slab (row-major lower triangle) ----------------
     if (active) {
-        double* out = ws + (size_t)ksl * (size_t)m * (size_t)m;
+        double* out = ws + (size_t)ksl * (size_t)Ma * (size_t)Nb;
         const int row0 = job->boxrow[ta], col0 = job->boxrow[tb];
 #pragma unroll
         for (int i = 0; i < WF; i++) {
@@ -157,27 +159,29 @@ gram_kernel(const __grid_constant__ CUtensorMap tmS, const double* __restrict__ 
             for (int j = 0; j < WF; j++) {
                 if (!(mask & (1u << (i * WF + j)))) continue;
                 const int gj = col0 + 8 * j + 2 * t;
-                if (gi < m) {
-                    if (gj < m) out[(size_t)gi * m + gj] = acc[i][j][0];
-                    if (gj + 1 < m) out[(size_t)gi * m + gj + 1] = acc[i][j][1];
+                if (gi < Ma) {
+                    if (gj < Nb) out[(size_t)gi * Nb + gj] = acc[i][j][0];
+                    if (gj + 1 < Nb) out[(size_t)gi * Nb + gj + 1] = acc[i][j][1];
                 }
             }
         }
     }
 }
 
-// Deterministic split-K reduction + symmetrisation: G(i,j) = G(j,i) = sum_s ws[s][i*m+j], i >= j.
-__global__ void gram_reduce_kernel(const double* __restrict__ ws, int nsplit, int m, double* __restrict__ G)
+// Deterministic split-K reduction (+ symmetrisation): out(i,j) = sum_s ws[s][i*Nb+j], written to
+// out[i*rs + (j / cinner)*cso + (j % cinner)*csi] (two-level column stride: matrix columns or tensor slices).
+__global__ void gram_reduce_kernel(const double* __restrict__ ws, int nsplit, int Ma, int Nb, int symmetric,
+                                   double* __restrict__ out, long long rs, int cinner, long long cso, long long csi)
 {
-    const size_t mm = (size_t)m * m;
+    const size_t mm = (size_t)Ma * Nb;
     for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < mm;
          idx += (size_t)gridDim.x * blockDim.x) {
-        const int i = (int)(idx / m), j = (int)(idx % m);
-        if (j > i) continue;
+        const int i = (int)(idx / Nb), j = (int)(idx % Nb);
+        if (symmetric && j > i) continue;
         double s = 0.0;
         for (int k = 0; k < nsplit; k++) s += ws[(size_t)k * mm + idx];
-        G[(size_t)i + (size_t)j * m] = s;
-        G[(size_t)j + (size_t)i * m] = s;
+        out[(size_t)i * rs + (size_t)(j / cinner) * cso + (size_t)(j % cinner) * csi] = s;
+        if (symmetric) out[(size_t)j * rs + (size_t)(i / cinner) * cso + (size_t)(i % cinner) * csi] = s;
     }
 }
 
@@ -253,11 +257,52 @@ static void build_jobs(int m, std::vector<GramJob>& jobs)
         }
 }
 
-int gram_launch(ithaca_b200* h)
+// Host: rectangular A^T B. The fragment rows (Ma/8) and columns (Nb/8) are cut into balanced tiles of <= WF
+// fragments; a job is a group of gr row tiles x gc column tiles (<= 15 warp tiles, <= 10 boxes).
+static void build_jobs_rect(int Ma, int Nb, std::vector<GramJob>& jobs)
 {
-    const int m = h->m;
+    constexpr int WF = GRAM_WF;
+    auto cut = [&](int n, std::vector<std::pair<int, int>>& tiles) {  // (first fragment, #fragments)
+        const int nfr = (n + 7) / 8, nt = (nfr + WF - 1) / WF;
+        int f = 0;
+        for (int t = 0; t < nt; t++) {
+            const int len = nfr / nt + (t < nfr % nt ? 1 : 0);
+            tiles.push_back({f, len});
+            f += len;
+        }
+    };
+    std::vector<std::pair<int, int>> rt, ct;
+    cut(Ma, rt);
+    cut(Nb, ct);
+    const int gr = std::min<int>((int)rt.size(), 3);
+    const int gc = std::max(1, std::min<int>({(int)ct.size(), GRAM_MAXTILES / gr, GRAM_NBMAX - gr}));
+    for (size_t r0 = 0; r0 < rt.size(); r0 += gr)
+        for (size_t c0 = 0; c0 < ct.size(); c0 += gc) {
+            GramJob jb;
+            std::memset(&jb, 0, sizeof(jb));
+            const size_t r1 = std::min(rt.size(), r0 + gr), c1 = std::min(ct.size(), c0 + gc);
+            for (size_t r = r0; r < r1; r++) { jb.boxrow[jb.nbox] = 8 * rt[r].first; jb.boxmap[jb.nbox++] = 0; }
+            for (size_t c = c0; c < c1; c++) { jb.boxrow[jb.nbox] = 8 * ct[c].first; jb.boxmap[jb.nbox++] = 1; }
+            for (size_t r = r0; r < r1; r++)
+                for (size_t c = c0; c < c1; c++) {
+                    unsigned mk = 0;
+                    for (int i = 0; i < rt[r].second; i++)
+                        for (int j = 0; j < ct[c].second; j++) mk |= 1u << (i * WF + j);
+                    jb.ta[jb.ntiles] = (unsigned char)(r - r0);
+                    jb.tb[jb.ntiles] = (unsigned char)((r1 - r0) + (c - c0));
+                    jb.mask[jb.ntiles++] = mk;
+                }
+            jobs.push_back(jb);
+        }
+}
+
+int atvb_launch(ithaca_b200* h, const double* A, long long lda, int Ma, const double* B, long long ldb, int Nb,
+                long long K, const double* V, int dim, int symmetric, double* out, long long rs, int cinner,
+                long long cso, long long csi)
+{
     std::vector<GramJob> jobs;
-    build_jobs(m, jobs);
+    if (symmetric) build_jobs(Ma, jobs);
+    else build_jobs_rect(Ma, Nb, jobs);
     const int njobs = (int)jobs.size();
     int nbox_max = 0;
     for (auto& j : jobs) nbox_max = std::max(nbox_max, j.nbox);
@@ -269,15 +314,14 @@ int gram_launch(ithaca_b200* h)
 
     // split-K: about two waves of CTAs when there are several jobs, one CTA per SM for a single job;
     // every slab is a multiple of the stage depth and at least 64 stages long.
-    const long long Nd = h->Nd;
     int target = (njobs == 1) ? h->num_sms : 2 * h->num_sms;
     int nsplit = std::max(1, target / njobs);
     long long min_chunk = 64LL * GRAM_KT;
-    nsplit = (int)std::max(1LL, std::min<long long>(nsplit, (Nd + min_chunk - 1) / min_chunk));
-    long long kchunk = ((Nd + nsplit - 1) / nsplit + GRAM_KT - 1) / GRAM_KT * GRAM_KT;
-    nsplit = (int)((Nd + kchunk - 1) / kchunk);
+    nsplit = (int)std::max(1LL, std::min<long long>(nsplit, (K + min_chunk - 1) / min_chunk));
+    long long kchunk = ((K + nsplit - 1) / nsplit + GRAM_KT - 1) / GRAM_KT * GRAM_KT;
+    nsplit = (int)((K + kchunk - 1) / kchunk);
 
-    const size_t ws_need = (size_t)nsplit * m * m * sizeof(double);
+    const size_t ws_need = (size_t)nsplit * Ma * Nb * sizeof(double);
     if (ws_need > h->dWs_cap) {
         if (h->dWs) cudaFree(h->dWs);
         h->dWs = nullptr; h->dWs_cap = 0;
@@ -293,25 +337,32 @@ int gram_launch(ithaca_b200* h)
     }
     IB_CUDA(h, cudaMemcpyAsync(h->dJobs, jobs.data(), jb_need, cudaMemcpyHostToDevice, h->stream));
 
-    CUtensorMap tm;
-    int rc = make_tmap_2d(h, &tm, h->dS, (uint64_t)Nd, (uint64_t)m, (uint64_t)h->ld * 8, GRAM_KT,
-                          GRAM_BOXROWS, true);
+    CUtensorMap tmA, tmB;
+    int rc = make_tmap_2d(h, &tmA, A, (uint64_t)K, (uint64_t)Ma, (uint64_t)lda * 8, GRAM_KT, GRAM_BOXROWS, true);
+    if (rc) return rc;
+    rc = make_tmap_2d(h, &tmB, B, (uint64_t)K, (uint64_t)Nb, (uint64_t)ldb * 8, GRAM_KT, GRAM_BOXROWS, true);
     if (rc) return rc;
 
     IB_CUDA(h, cudaFuncSetAttribute(gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     Timer& tk = h->timers[T_GRAMK];
     IB_CUDA(h, cudaEventRecord(tk.a, h->stream));
     gram_kernel<<<njobs * nsplit, GRAM_THREADS, smem, h->stream>>>(
-        tm, h->dV, h->dim, Nd, m, (const GramJob*)h->dJobs, njobs, kchunk, nstages, stage_bytes, h->dWs);
+        tmA, tmB, V, dim, K, Ma, Nb, (const GramJob*)h->dJobs, njobs, kchunk, nstages, stage_bytes, h->dWs);
     IB_CUDA(h, cudaGetLastError());
     IB_CUDA(h, cudaEventRecord(tk.b, h->stream));
     tk.used = true;
     const int rb = 256;
-    const int rg = (int)std::min<size_t>(((size_t)m * m + rb - 1) / rb, 4 * (size_t)h->num_sms);
-    gram_reduce_kernel<<<rg, rb, 0, h->stream>>>(h->dWs, nsplit, m, h->dG);
+    const int rg = (int)std::min<size_t>(((size_t)Ma * Nb + rb - 1) / rb, 4 * (size_t)h->num_sms);
+    gram_reduce_kernel<<<rg, rb, 0, h->stream>>>(h->dWs, nsplit, Ma, Nb, symmetric, out, rs, cinner, cso, csi);
     IB_CUDA(h, cudaGetLastError());
     h->launches += 2;
     return IB200_OK;
+}
+
+// POD Gram: G = S^T diag(V) S, symmetric schedule, column-major m x m into h->dG.
+int gram_launch(ithaca_b200* h)
+{
+    return atvb_launch(h, h->dS, h->ld, h->m, h->dS, h->ld, h->m, h->Nd, h->dV, h->dim, 1, h->dG, 1, 0x7fffffff, 0, h->m);
 }
 
 }  // namespace ib200

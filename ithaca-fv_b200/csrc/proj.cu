@@ -1,0 +1,891 @@
+// K5-K9 -- Galerkin projection of the steadyNS / unsteadyNS operators on the POD basis.
+//
+// Replaces the term builders of src/ITHACA_FOMPROBLEMS/steadyNS/steadyNS.C:
+//   mass_term :1085-1108 (M), diffusive_term :883-907 (B), pressure_gradient_term :935-960 (K),
+//   divergence_term :1112-1137 (P), convective_term_tens :997-1036 / _cache :1038-1083 (C)
+// and the OpenFOAM fvc operators they call (Gauss linear grad/div/interpolate, Gauss linear corrected or
+// uncorrected laplacian), over OpenFOAM's own owner/neighbour face addressing.
+//
+// Structure (the reference evaluates one fvc operator and one domainIntegrate -> one MPI reduce per ENTRY;
+// here each distinct field is evaluated once and each operator is one contraction):
+//   K5 face_flux_kernel       phi_j(f) = (w U_j[own] + (1-w) U_j[nei]) . Sf      gather, face-parallel
+//   K6 div_phi_kernel         div(phi_j, U_k)(c)                                 gather over the cell's faces
+//   K7 grad_vec / laplacian   grad(U_j) tensor, then laplacian(1, U_j)           two gathers
+//   K8 grad_scalar / surface_integrate   grad(P_j), div(U_j)                     gather
+//   K9 atvb (gram.cu, DMMA)   X^T diag(V) Y for every operator                   one contraction per operator
+// Scatter is replaced by a cell -> face CSR (ascending face order, built on the device) so every cell sums its
+// own faces in OpenFOAM's order: no atomics on doubles, results are reproducible run to run.
+#include "../../include/ithaca_b200.h"
+#include "common.cuh"
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+namespace ib200 {
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct MeshDev {
+    long long nCells, nInt, nBnd;
+    const int *owner, *neigh;
+    const double *Sf, *magSf, *w, *dc, *dcB, *corr, *V;
+    const unsigned char* bmask;
+    const int *off, *ent, *other;
+};
+
+struct ProjState {
+    long long nCells = 0, nInt = 0, nBnd = 0;
+    bool have_mesh = false, corrected = false;
+    DevBuf owner, neigh, Sf, magSf, w, dc, dcB, corr, V, bmask, off, ent, other, cnt, blocksum;
+    int nU = 0, nP = 0;
+    long long ldU = 0, ldUb = 0, ldP = 0, ldPb = 0, ldF = 0;
+    DevBuf U, Ub, P, Pb;
+    DevBuf flux;   // nU columns of ldF doubles (all faces)
+    bool have_flux = false;
+    DevBuf work;   // operator fields, columns of ldU (vector) or ldP (scalar) doubles
+    DevBuf T;      // gradient tensors of a batch of fields, 9*nCells doubles each
+    DevBuf out;    // device copy of the projected operator
+    double ms[8] = {0};  // last timings: flux, div_phi, lap, grad, div, contraction
+};
+
+static int ensure(ithaca_b200* h, DevBuf& b, size_t bytes)
+{
+    if (bytes <= b.cap) return IB200_OK;
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr;
+    b.cap = 0;
+    IB_CUDA(h, cudaMalloc(&b.p, bytes));
+    b.cap = bytes;
+    return IB200_OK;
+}
+
+static int upload(ithaca_b200* h, DevBuf& b, const void* src, size_t bytes)
+{
+    int rc = ensure(h, b, std::max<size_t>(bytes, 16));
+    if (rc) return rc;
+    if (bytes) IB_CUDA(h, cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyDefault, h->stream));
+    return IB200_OK;
+}
+
+void proj_destroy(ithaca_b200* h)
+{
+    ProjState* s = h->proj;
+    if (!s) return;
+    for (DevBuf* b : {&s->owner, &s->neigh, &s->Sf, &s->magSf, &s->w, &s->dc, &s->dcB, &s->corr, &s->V, &s->bmask,
+                      &s->off, &s->ent, &s->other, &s->cnt, &s->blocksum, &s->U, &s->Ub, &s->P, &s->Pb, &s->flux,
+                      &s->work, &s->T, &s->out})
+        if (b->p) cudaFree(b->p);
+    delete s;
+    h->proj = nullptr;
+}
+
+static MeshDev mesh_dev(const ProjState* s)
+{
+    MeshDev m;
+    m.nCells = s->nCells; m.nInt = s->nInt; m.nBnd = s->nBnd;
+    m.owner = s->owner.as<int>(); m.neigh = s->neigh.as<int>();
+    m.Sf = s->Sf.as<double>(); m.magSf = s->magSf.as<double>(); m.w = s->w.as<double>();
+    m.dc = s->dc.as<double>(); m.dcB = s->dcB.as<double>();
+    m.corr = s->corrected ? s->corr.as<double>() : nullptr;
+    m.V = s->V.as<double>(); m.bmask = s->bmask.as<unsigned char>();
+    m.off = s->off.as<int>(); m.ent = s->ent.as<int>(); m.other = s->other.as<int>();
+    return m;
+}
+
+// ------------------------------------------------------------------------------------------------
+// cell -> face CSR, built on the device: count, exclusive scan, fill, per-cell sort by face index.
+// entry = +(f+1): the cell owns face f; -(f+1): it is the neighbour. other = cell across the face, or -(b+1)
+// for boundary face b. Ascending face order == primitiveMesh::cells() order == the oracle's fvo_cell_faces.
+// ------------------------------------------------------------------------------------------------
+__global__ void csr_count_kernel(const int* __restrict__ owner, const int* __restrict__ neigh, long long nInt,
+                                 long long nF, int* __restrict__ cnt)
+{
+    for (long long f = blockIdx.x * (long long)blockDim.x + threadIdx.x; f < nF; f += (long long)gridDim.x * blockDim.x) {
+        atomicAdd(&cnt[owner[f]], 1);
+        if (f < nInt) atomicAdd(&cnt[neigh[f]], 1);
+    }
+}
+
+constexpr int SCAN_B = 1024;
+// per-block exclusive scan of cnt -> off (block-local), block totals -> blocksum
+__global__ void __launch_bounds__(SCAN_B) scan_block_kernel(const int* __restrict__ cnt, long long n, int* __restrict__ off,
+                                                            int* __restrict__ blocksum)
+{
+    __shared__ int sh[SCAN_B];
+    const long long i = blockIdx.x * (long long)SCAN_B + threadIdx.x;
+    const int v = (i < n) ? cnt[i] : 0;
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 1; o < SCAN_B; o <<= 1) {
+        const int t = (threadIdx.x >= o) ? sh[threadIdx.x - o] : 0;
+        __syncthreads();
+        sh[threadIdx.x] += t;
+        __syncthreads();
+    }
+    if (i < n) off[i] = sh[threadIdx.x] - v;
+    if (threadIdx.x == SCAN_B - 1) blocksum[blockIdx.x] = sh[threadIdx.x];
+}
+// single block: exclusive scan of blocksum in place (nb can exceed the block size: serial chunks)
+__global__ void __launch_bounds__(SCAN_B) scan_sums_kernel(int* __restrict__ blocksum, int nb)
+{
+    __shared__ int sh[SCAN_B];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < nb; base += SCAN_B) {
+        const int i = base + threadIdx.x;
+        const int v = (i < nb) ? blocksum[i] : 0;
+        sh[threadIdx.x] = v;
+        __syncthreads();
+        for (int o = 1; o < SCAN_B; o <<= 1) {
+            const int t = (threadIdx.x >= o) ? sh[threadIdx.x - o] : 0;
+            __syncthreads();
+            sh[threadIdx.x] += t;
+            __syncthreads();
+        }
+        if (i < nb) blocksum[i] = carry + sh[threadIdx.x] - v;
+        __syncthreads();
+        if (threadIdx.x == SCAN_B - 1) carry += sh[threadIdx.x];
+        __syncthreads();
+    }
+}
+__global__ void scan_add_kernel(int* __restrict__ off, const int* __restrict__ blocksum, long long n, int* __restrict__ cursor,
+                                int total_slot)
+{
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i < n) {
+        const int v = off[i] + blocksum[i / SCAN_B];
+        off[i] = v;
+        cursor[i] = v;
+    }
+    (void)total_slot;
+}
+__global__ void csr_fill_kernel(const int* __restrict__ owner, const int* __restrict__ neigh, long long nInt, long long nF,
+                                int* __restrict__ cursor, int* __restrict__ ent, int* __restrict__ other)
+{
+    for (long long f = blockIdx.x * (long long)blockDim.x + threadIdx.x; f < nF; f += (long long)gridDim.x * blockDim.x) {
+        const int o = owner[f];
+        int p = atomicAdd(&cursor[o], 1);
+        ent[p] = (int)(f + 1);
+        other[p] = (f < nInt) ? neigh[f] : -(int)(f - nInt + 1);
+        if (f < nInt) {
+            const int n = neigh[f];
+            p = atomicAdd(&cursor[n], 1);
+            ent[p] = -(int)(f + 1);
+            other[p] = o;
+        }
+    }
+}
+// insertion sort of each cell's segment by face index (segments are short: the faces of one cell)
+__global__ void csr_sort_kernel(const int* __restrict__ off, long long nCells, int* __restrict__ ent, int* __restrict__ other)
+{
+    const long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (c >= nCells) return;
+    const int a = off[c], b = off[c + 1];
+    for (int i = a + 1; i < b; i++) {
+        const int e = ent[i], o = other[i], key = abs(e);
+        int j = i - 1;
+        while (j >= a && abs(ent[j]) > key) {
+            ent[j + 1] = ent[j];
+            other[j + 1] = other[j];
+            j--;
+        }
+        ent[j + 1] = e;
+        other[j + 1] = o;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5: face flux of nf fields. phi[j*ldF + f] = (w U_j[o] + (1-w) U_j[n]) . Sf(f); boundary: Ub_j(b) . Sf,
+// 0 on `empty` patches. Face geometry is loaded once per face and reused for FB fields.
+// ------------------------------------------------------------------------------------------------
+constexpr int PROJ_T = 256;
+constexpr int FB = 4;  // fields per thread in the gather kernels
+
+__global__ void __launch_bounds__(PROJ_T)
+face_flux_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const double* __restrict__ Ub, long long ldUb,
+                 int nf, double* __restrict__ phi, long long ldF)
+{
+    const long long f = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    const long long nF = m.nInt + m.nBnd;
+    if (f >= nF) return;
+    const int j0 = blockIdx.y * FB;
+    const double s0 = m.Sf[3 * f], s1 = m.Sf[3 * f + 1], s2 = m.Sf[3 * f + 2];
+    if (f < m.nInt) {
+        const int o = m.owner[f], n = m.neigh[f];
+        const double w = m.w[f], w1 = 1.0 - w;
+#pragma unroll
+        for (int jj = 0; jj < FB; jj++) {
+            const int j = j0 + jj;
+            if (j >= nf) break;
+            const double* u = U + (size_t)j * ldU;
+            double s = 0.0;
+            s += (w * u[3 * (size_t)o] + w1 * u[3 * (size_t)n]) * s0;
+            s += (w * u[3 * (size_t)o + 1] + w1 * u[3 * (size_t)n + 1]) * s1;
+            s += (w * u[3 * (size_t)o + 2] + w1 * u[3 * (size_t)n + 2]) * s2;
+            phi[(size_t)j * ldF + f] = s;
+        }
+    } else {
+        const long long b = f - m.nInt;
+        const bool on = m.bmask[b] != 0;
+#pragma unroll
+        for (int jj = 0; jj < FB; jj++) {
+            const int j = j0 + jj;
+            if (j >= nf) break;
+            const double* ub = Ub + (size_t)j * ldUb + 3 * b;
+            double s = 0.0;
+            if (on) { s += ub[0] * s0; s += ub[1] * s1; s += ub[2] * s2; }
+            phi[(size_t)j * ldF + f] = s;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K6: out_k = fvc::div(phi, U_k) = surfaceIntegrate(phi * linearInterpolate(U_k)), FB fields k per thread,
+// one thread per cell walking the cell's CSR segment (OpenFOAM's summation order, then / V).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(PROJ_T)
+div_phi_kernel(MeshDev m, const double* __restrict__ phi, const double* __restrict__ U, long long ldU,
+               const double* __restrict__ Ub, long long ldUb, int nk, double* __restrict__ out, long long ldo)
+{
+    const long long c = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    if (c >= m.nCells) return;
+    const int k0 = blockIdx.y * FB;
+    double uc[FB][3], acc[FB][3];
+#pragma unroll
+    for (int kk = 0; kk < FB; kk++) {
+        const int k = min(k0 + kk, nk - 1);
+#pragma unroll
+        for (int d = 0; d < 3; d++) { uc[kk][d] = U[(size_t)k * ldU + 3 * c + d]; acc[kk][d] = 0.0; }
+    }
+    const int e0 = m.off[c], e1 = m.off[c + 1];
+    for (int e = e0; e < e1; e++) {
+        const int en = m.ent[e], ot = m.other[e];
+        const long long f = abs(en) - 1;
+        const double ph = phi[f];
+        if (ot >= 0) {
+            const double w = m.w[f], w1 = 1.0 - w;
+            const bool own = en > 0;
+#pragma unroll
+            for (int kk = 0; kk < FB; kk++) {
+                const int k = min(k0 + kk, nk - 1);
+                const double* un = U + (size_t)k * ldU + 3 * (size_t)ot;
+#pragma unroll
+                for (int d = 0; d < 3; d++) {
+                    const double x = un[d];
+                    const double uf = own ? (w * uc[kk][d] + w1 * x) : (w * x + w1 * uc[kk][d]);
+                    const double v = ph * uf;
+                    acc[kk][d] += own ? v : -v;
+                }
+            }
+        } else {
+            const long long b = -(long long)ot - 1;
+            if (!m.bmask[b]) continue;
+#pragma unroll
+            for (int kk = 0; kk < FB; kk++) {
+                const int k = min(k0 + kk, nk - 1);
+                const double* ub = Ub + (size_t)k * ldUb + 3 * b;
+#pragma unroll
+                for (int d = 0; d < 3; d++) acc[kk][d] += ph * ub[d];
+            }
+        }
+    }
+    const double V = m.V[c];
+#pragma unroll
+    for (int kk = 0; kk < FB; kk++) {
+        const int k = k0 + kk;
+        if (k >= nk) break;
+#pragma unroll
+        for (int d = 0; d < 3; d++) out[(size_t)k * ldo + 3 * c + d] = acc[kk][d] / V;
+    }
+}
+
+// K8a: out_j = surfaceIntegrate(phi_j) = fvc::div(U_j) when phi_j is the face flux of U_j. Scalar output.
+__global__ void __launch_bounds__(PROJ_T)
+surface_integrate_kernel(MeshDev m, const double* __restrict__ phi, long long ldF, int nf, double* __restrict__ out, long long ldo)
+{
+    const long long c = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    if (c >= m.nCells) return;
+    const int j0 = blockIdx.y * FB;
+    double acc[FB];
+#pragma unroll
+    for (int jj = 0; jj < FB; jj++) acc[jj] = 0.0;
+    const int e0 = m.off[c], e1 = m.off[c + 1];
+    for (int e = e0; e < e1; e++) {
+        const int en = m.ent[e], ot = m.other[e];
+        const long long f = abs(en) - 1;
+        if (ot < 0 && !m.bmask[-(long long)ot - 1]) continue;
+#pragma unroll
+        for (int jj = 0; jj < FB; jj++) {
+            const int j = min(j0 + jj, nf - 1);
+            const double ph = phi[(size_t)j * ldF + f];
+            acc[jj] += (en > 0) ? ph : -ph;
+        }
+    }
+    const double V = m.V[c];
+#pragma unroll
+    for (int jj = 0; jj < FB; jj++)
+        if (j0 + jj < nf) out[(size_t)(j0 + jj) * ldo + c] = acc[jj] / V;
+}
+
+// K8b: out_j = fvc::grad(P_j), Gauss linear: sum_f +-Sf * (w p[o] + (1-w) p[n]) / V; boundary Sf * pb.
+__global__ void __launch_bounds__(PROJ_T)
+grad_scalar_kernel(MeshDev m, const double* __restrict__ P, long long ldP, const double* __restrict__ Pb, long long ldPb,
+                   int np, double* __restrict__ out, long long ldo)
+{
+    const long long c = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    if (c >= m.nCells) return;
+    const int j0 = blockIdx.y * FB;
+    double pc[FB], acc[FB][3];
+#pragma unroll
+    for (int jj = 0; jj < FB; jj++) {
+        pc[jj] = P[(size_t)min(j0 + jj, np - 1) * ldP + c];
+        acc[jj][0] = acc[jj][1] = acc[jj][2] = 0.0;
+    }
+    const int e0 = m.off[c], e1 = m.off[c + 1];
+    for (int e = e0; e < e1; e++) {
+        const int en = m.ent[e], ot = m.other[e];
+        const long long f = abs(en) - 1;
+        const double s[3] = {m.Sf[3 * f], m.Sf[3 * f + 1], m.Sf[3 * f + 2]};
+        if (ot >= 0) {
+            const double w = m.w[f], w1 = 1.0 - w;
+            const bool own = en > 0;
+#pragma unroll
+            for (int jj = 0; jj < FB; jj++) {
+                const double x = P[(size_t)min(j0 + jj, np - 1) * ldP + ot];
+                const double pf = own ? (w * pc[jj] + w1 * x) : (w * x + w1 * pc[jj]);
+#pragma unroll
+                for (int d = 0; d < 3; d++) {
+                    const double v = s[d] * pf;
+                    acc[jj][d] += own ? v : -v;
+                }
+            }
+        } else {
+            const long long b = -(long long)ot - 1;
+            if (!m.bmask[b]) continue;
+#pragma unroll
+            for (int jj = 0; jj < FB; jj++) {
+                const double pb = Pb[(size_t)min(j0 + jj, np - 1) * ldPb + b];
+#pragma unroll
+                for (int d = 0; d < 3; d++) acc[jj][d] += s[d] * pb;
+            }
+        }
+    }
+    const double V = m.V[c];
+#pragma unroll
+    for (int jj = 0; jj < FB; jj++)
+        if (j0 + jj < np)
+#pragma unroll
+            for (int d = 0; d < 3; d++) out[(size_t)(j0 + jj) * ldo + 3 * c + d] = acc[jj][d] / V;
+}
+
+// K7a: T_j = fvc::grad(U_j), Gauss linear: T[c][i][d] = sum_f +-Sf_i * Uf_d / V. One field per blockIdx.y.
+__global__ void __launch_bounds__(PROJ_T)
+grad_vec_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const double* __restrict__ Ub, long long ldUb,
+                int j0, double* __restrict__ T, long long ldT)
+{
+    const long long c = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    if (c >= m.nCells) return;
+    const int j = j0 + blockIdx.y;
+    const double* u = U + (size_t)j * ldU;
+    const double uc[3] = {u[3 * c], u[3 * c + 1], u[3 * c + 2]};
+    double acc[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) acc[i][0] = acc[i][1] = acc[i][2] = 0.0;
+    const int e0 = m.off[c], e1 = m.off[c + 1];
+    for (int e = e0; e < e1; e++) {
+        const int en = m.ent[e], ot = m.other[e];
+        const long long f = abs(en) - 1;
+        const double s[3] = {m.Sf[3 * f], m.Sf[3 * f + 1], m.Sf[3 * f + 2]};
+        if (ot >= 0) {
+            const double w = m.w[f], w1 = 1.0 - w;
+            const bool own = en > 0;
+#pragma unroll
+            for (int d = 0; d < 3; d++) {
+                const double x = u[3 * (size_t)ot + d];
+                const double uf = own ? (w * uc[d] + w1 * x) : (w * x + w1 * uc[d]);
+#pragma unroll
+                for (int i = 0; i < 3; i++) {
+                    const double v = s[i] * uf;
+                    acc[i][d] += own ? v : -v;
+                }
+            }
+        } else {
+            const long long b = -(long long)ot - 1;
+            if (!m.bmask[b]) continue;
+            const double* ub = Ub + (size_t)j * ldUb + 3 * b;
+#pragma unroll
+            for (int d = 0; d < 3; d++)
+#pragma unroll
+                for (int i = 0; i < 3; i++) acc[i][d] += s[i] * ub[d];
+        }
+    }
+    const double V = m.V[c];
+    double* t = T + (size_t)blockIdx.y * ldT + 9 * c;
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int d = 0; d < 3; d++) t[3 * i + d] = acc[i][d] / V;
+}
+
+// K7b: out_j = fvc::laplacian(1, U_j) = surfaceIntegrate(|Sf| snGrad(U_j)); snGrad = dc (U[n]-U[o])
+// (+ corr . (w T[o] + (1-w) T[n]) when corrected); boundary |Sf| dcB (Ub - U[c]). One field per blockIdx.y.
+__global__ void __launch_bounds__(PROJ_T)
+laplacian_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const double* __restrict__ Ub, long long ldUb,
+                 int j0, const double* __restrict__ T, long long ldT, double* __restrict__ out, long long ldo)
+{
+    const long long c = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    if (c >= m.nCells) return;
+    const int j = j0 + blockIdx.y;
+    const double* u = U + (size_t)j * ldU;
+    const double* t = T ? T + (size_t)blockIdx.y * ldT : nullptr;
+    const double uc[3] = {u[3 * c], u[3 * c + 1], u[3 * c + 2]};
+    double tc[9];
+    if (t)
+#pragma unroll
+        for (int k = 0; k < 9; k++) tc[k] = t[9 * c + k];
+    double acc[3] = {0.0, 0.0, 0.0};
+    const int e0 = m.off[c], e1 = m.off[c + 1];
+    for (int e = e0; e < e1; e++) {
+        const int en = m.ent[e], ot = m.other[e];
+        const long long f = abs(en) - 1;
+        const double ms = m.magSf[f];
+        if (ot >= 0) {
+            const bool own = en > 0;
+            const double dc = m.dc[f];
+            double cr[3] = {0.0, 0.0, 0.0};
+            if (t) {
+                const double w = m.w[f], w1 = 1.0 - w;
+                const double* tn = t + 9 * (size_t)ot;
+#pragma unroll
+                for (int i = 0; i < 3; i++) {
+                    const double k = m.corr[3 * f + i];
+#pragma unroll
+                    for (int d = 0; d < 3; d++) {
+                        const double x = tn[3 * i + d];
+                        cr[d] += k * (own ? (w * tc[3 * i + d] + w1 * x) : (w * x + w1 * tc[3 * i + d]));
+                    }
+                }
+            }
+#pragma unroll
+            for (int d = 0; d < 3; d++) {
+                const double x = u[3 * (size_t)ot + d];
+                double sn = own ? dc * (x - uc[d]) : dc * (uc[d] - x);
+                if (t) sn += cr[d];
+                const double v = ms * sn;
+                acc[d] += own ? v : -v;
+            }
+        } else {
+            const long long b = -(long long)ot - 1;
+            if (!m.bmask[b]) continue;
+            const double* ub = Ub + (size_t)j * ldUb + 3 * b;
+            const double dcb = m.dcB[b];
+#pragma unroll
+            for (int d = 0; d < 3; d++) acc[d] += ms * (dcb * (ub[d] - uc[d]));
+        }
+    }
+    const double V = m.V[c];
+#pragma unroll
+    for (int d = 0; d < 3; d++) out[(size_t)j * ldo + 3 * c + d] = acc[d] / V;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------------
+static inline long long pad16(long long n) { return (n + 15) / 16 * 16; }
+static inline unsigned gx(long long n) { return (unsigned)((n + PROJ_T - 1) / PROJ_T); }
+static inline unsigned gy(int n) { return (unsigned)((n + FB - 1) / FB); }
+
+struct StageTimer {
+    cudaEvent_t a, b;
+    cudaStream_t s;
+    double* acc;
+    StageTimer(cudaStream_t st, double* where) : s(st), acc(where)
+    {
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        cudaEventRecord(a, s);
+    }
+    void stop()
+    {
+        cudaEventRecord(b, s);
+        cudaEventSynchronize(b);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, a, b);
+        *acc += ms;
+        cudaEventDestroy(a);
+        cudaEventDestroy(b);
+    }
+};
+
+static int build_csr(ithaca_b200* h, ProjState* s)
+{
+    const long long nC = s->nCells, nF = s->nInt + s->nBnd, nnz = 2 * s->nInt + s->nBnd, n1 = nC + 1;
+    int rc;
+    if ((rc = ensure(h, s->cnt, n1 * sizeof(int)))) return rc;
+    if ((rc = ensure(h, s->off, n1 * sizeof(int)))) return rc;
+    if ((rc = ensure(h, s->ent, std::max<long long>(nnz, 1) * sizeof(int)))) return rc;
+    if ((rc = ensure(h, s->other, std::max<long long>(nnz, 1) * sizeof(int)))) return rc;
+    const int nb = (int)((n1 + SCAN_B - 1) / SCAN_B);
+    if ((rc = ensure(h, s->blocksum, (size_t)nb * sizeof(int)))) return rc;
+    IB_CUDA(h, cudaMemsetAsync(s->cnt.p, 0, n1 * sizeof(int), h->stream));
+    const int fg = (int)std::min<long long>((nF + 255) / 256, 64LL * h->num_sms);
+    csr_count_kernel<<<std::max(fg, 1), 256, 0, h->stream>>>(s->owner.as<int>(), s->neigh.as<int>(), s->nInt, nF, s->cnt.as<int>());
+    scan_block_kernel<<<nb, SCAN_B, 0, h->stream>>>(s->cnt.as<int>(), n1, s->off.as<int>(), s->blocksum.as<int>());
+    scan_sums_kernel<<<1, SCAN_B, 0, h->stream>>>(s->blocksum.as<int>(), nb);
+    scan_add_kernel<<<(unsigned)((n1 + 255) / 256), 256, 0, h->stream>>>(s->off.as<int>(), s->blocksum.as<int>(), n1, s->cnt.as<int>(), 0);
+    csr_fill_kernel<<<std::max(fg, 1), 256, 0, h->stream>>>(s->owner.as<int>(), s->neigh.as<int>(), s->nInt, nF, s->cnt.as<int>(),
+                                                            s->ent.as<int>(), s->other.as<int>());
+    csr_sort_kernel<<<(unsigned)((nC + 255) / 256), 256, 0, h->stream>>>(s->off.as<int>(), nC, s->ent.as<int>(), s->other.as<int>());
+    IB_CUDA(h, cudaGetLastError());
+    h->launches += 6;
+    return IB200_OK;
+}
+
+static int need_flux(ithaca_b200* h, ProjState* s)
+{
+    if (s->have_flux) return IB200_OK;
+    int rc = ensure(h, s->flux, (size_t)s->nU * s->ldF * sizeof(double));
+    if (rc) return rc;
+    StageTimer t(h->stream, &s->ms[0]);
+    face_flux_kernel<<<dim3(gx(s->nInt + s->nBnd), gy(s->nU)), PROJ_T, 0, h->stream>>>(
+        mesh_dev(s), s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb, s->nU, s->flux.as<double>(), s->ldF);
+    t.stop();
+    IB_CUDA(h, cudaGetLastError());
+    h->launches += 1;
+    s->have_flux = true;
+    return IB200_OK;
+}
+
+// laplacian(1, U_j) for j in [0, nU) into `out` (columns of ldU doubles)
+static int run_laplacians(ithaca_b200* h, ProjState* s, double* out)
+{
+    const MeshDev m = mesh_dev(s);
+    const int batch = 8;
+    const long long ldT = pad16(9 * s->nCells);
+    if (s->corrected) {
+        int rc = ensure(h, s->T, (size_t)batch * ldT * sizeof(double));
+        if (rc) return rc;
+    }
+    StageTimer t(h->stream, &s->ms[2]);
+    for (int j0 = 0; j0 < s->nU; j0 += batch) {
+        const int nb = std::min(batch, s->nU - j0);
+        if (s->corrected) {
+            grad_vec_kernel<<<dim3(gx(s->nCells), nb), PROJ_T, 0, h->stream>>>(m, s->U.as<double>(), s->ldU, s->Ub.as<double>(),
+                                                                                s->ldUb, j0, s->T.as<double>(), ldT);
+            h->launches += 1;
+        }
+        laplacian_kernel<<<dim3(gx(s->nCells), nb), PROJ_T, 0, h->stream>>>(m, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb,
+                                                                             j0, s->corrected ? s->T.as<double>() : nullptr, ldT, out, s->ldU);
+        h->launches += 1;
+    }
+    t.stop();
+    IB_CUDA(h, cudaGetLastError());
+    return IB200_OK;
+}
+
+}  // namespace ib200
+
+using namespace ib200;
+
+#define PROJ_REQUIRE(cond, msg)                 \
+    do {                                        \
+        if (!(cond)) {                          \
+            set_error(h, msg);                  \
+            return IB200_ERR_ARG;               \
+        }                                       \
+    } while (0)
+
+extern "C" {
+
+int ithaca_b200_mesh_upload(ithaca_b200_t* h, int64_t nCells, int64_t nIntFaces, int64_t nBndFaces, const int32_t* owner,
+                            const int32_t* neighbour, const double* Sf, const double* magSf, const double* weights,
+                            const double* nonOrthDeltaCoeffs, const double* bndDeltaCoeffs, const double* nonOrthCorrVec,
+                            const double* V, const unsigned char* bndMask)
+{
+    if (!h) return IB200_ERR_ARG;
+    PROJ_REQUIRE(nCells > 0 && nIntFaces >= 0 && nBndFaces >= 0 && owner && (neighbour || nIntFaces == 0) && Sf && magSf &&
+                     (weights || nIntFaces == 0) && (nonOrthDeltaCoeffs || nIntFaces == 0) && (bndDeltaCoeffs || nBndFaces == 0) && V,
+                 "mesh_upload: bad argument");
+    PROJ_REQUIRE(2 * nIntFaces + nBndFaces < 0x7fffffffLL && nCells < 0x7fffffffLL, "mesh_upload: mesh too large for 32-bit labels");
+    cudaSetDevice(h->device);
+    if (!h->proj) h->proj = new ProjState();
+    ProjState* s = h->proj;
+    s->have_mesh = false;
+    s->have_flux = false;
+    s->nCells = nCells; s->nInt = nIntFaces; s->nBnd = nBndFaces;
+    const long long nF = nIntFaces + nBndFaces;
+    int rc;
+    if ((rc = upload(h, s->owner, owner, nF * sizeof(int)))) return rc;
+    if ((rc = upload(h, s->neigh, neighbour, nIntFaces * sizeof(int)))) return rc;
+    if ((rc = upload(h, s->Sf, Sf, 3 * nF * sizeof(double)))) return rc;
+    if ((rc = upload(h, s->magSf, magSf, nF * sizeof(double)))) return rc;
+    if ((rc = upload(h, s->w, weights, nIntFaces * sizeof(double)))) return rc;
+    if ((rc = upload(h, s->dc, nonOrthDeltaCoeffs, nIntFaces * sizeof(double)))) return rc;
+    if ((rc = upload(h, s->dcB, bndDeltaCoeffs, nBndFaces * sizeof(double)))) return rc;
+    s->corrected = nonOrthCorrVec != nullptr;
+    if (s->corrected && (rc = upload(h, s->corr, nonOrthCorrVec, 3 * nIntFaces * sizeof(double)))) return rc;
+    if ((rc = upload(h, s->V, V, nCells * sizeof(double)))) return rc;
+    if ((rc = ensure(h, s->bmask, std::max<long long>(nBndFaces, 16)))) return rc;
+    if (bndMask) IB_CUDA(h, cudaMemcpyAsync(s->bmask.p, bndMask, nBndFaces, cudaMemcpyDefault, h->stream));
+    else IB_CUDA(h, cudaMemsetAsync(s->bmask.p, 1, std::max<long long>(nBndFaces, 16), h->stream));
+    if ((rc = build_csr(h, s))) return rc;
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    s->have_mesh = true;
+    s->nU = s->nP = 0;
+    return IB200_OK;
+}
+
+int ithaca_b200_mesh_addressing(ithaca_b200_t* h, int32_t* off, int32_t* ent, int32_t* other, uint64_t* digest)
+{
+    if (!h) return IB200_ERR_ARG;
+    ProjState* s = h->proj;
+    PROJ_REQUIRE(s && s->have_mesh, "mesh_addressing: call mesh_upload first");
+    cudaSetDevice(h->device);
+    const long long n1 = s->nCells + 1, nnz = 2 * s->nInt + s->nBnd;
+    std::vector<int> o(n1), e(nnz), t(nnz);
+    IB_CUDA(h, cudaMemcpyAsync(o.data(), s->off.p, n1 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaMemcpyAsync(e.data(), s->ent.p, nnz * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaMemcpyAsync(t.data(), s->other.p, nnz * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (off) memcpy(off, o.data(), n1 * sizeof(int));
+    if (ent) memcpy(ent, e.data(), nnz * sizeof(int));
+    if (other) memcpy(other, t.data(), nnz * sizeof(int));
+    if (digest) {  // FNV-1a over the three arrays
+        uint64_t d = 1469598103934665603ULL;
+        auto mix = [&](const std::vector<int>& v) {
+            const unsigned char* p = reinterpret_cast<const unsigned char*>(v.data());
+            for (size_t i = 0; i < v.size() * sizeof(int); i++) { d ^= p[i]; d *= 1099511628211ULL; }
+        };
+        mix(o); mix(e); mix(t);
+        *digest = d;
+    }
+    return IB200_OK;
+}
+
+int ithaca_b200_basis_upload(ithaca_b200_t* h, int which, const double* const* int_ptrs, const double* const* bnd_ptrs, int n)
+{
+    if (!h) return IB200_ERR_ARG;
+    ProjState* s = h->proj;
+    PROJ_REQUIRE(s && s->have_mesh, "basis_upload: call mesh_upload first");
+    PROJ_REQUIRE((which == 0 || which == 1) && n > 0 && int_ptrs && (bnd_ptrs || s->nBnd == 0), "basis_upload: bad argument");
+    cudaSetDevice(h->device);
+    const int dim = which == 0 ? 3 : 1;
+    const long long ld = pad16(dim * s->nCells), ldb = pad16(std::max<long long>(dim * s->nBnd, 1));
+    DevBuf& I = which == 0 ? s->U : s->P;
+    DevBuf& Bd = which == 0 ? s->Ub : s->Pb;
+    int rc;
+    if ((rc = ensure(h, I, (size_t)n * ld * sizeof(double)))) return rc;
+    if ((rc = ensure(h, Bd, (size_t)n * ldb * sizeof(double)))) return rc;
+    for (int j = 0; j < n; j++) {
+        PROJ_REQUIRE(int_ptrs[j] && (s->nBnd == 0 || bnd_ptrs[j]), "basis_upload: null field pointer");
+        IB_CUDA(h, cudaMemcpyAsync(I.as<double>() + (size_t)j * ld, int_ptrs[j], (size_t)dim * s->nCells * sizeof(double),
+                                   cudaMemcpyDefault, h->stream));
+        if (s->nBnd)
+            IB_CUDA(h, cudaMemcpyAsync(Bd.as<double>() + (size_t)j * ldb, bnd_ptrs[j], (size_t)dim * s->nBnd * sizeof(double),
+                                       cudaMemcpyDefault, h->stream));
+    }
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    if (which == 0) { s->nU = n; s->ldU = ld; s->ldUb = ldb; s->ldF = pad16(s->nInt + s->nBnd); s->have_flux = false; }
+    else { s->nP = n; s->ldP = ld; s->ldPb = ldb; }
+    return IB200_OK;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+// Materialised operator field of basis function j (and k), for the parity tests of K5-K8.
+int ithaca_b200_fvc_eval(ithaca_b200_t* h, int op, int j, int k, double* out)
+{
+    if (!h) return IB200_ERR_ARG;
+    ProjState* s = h->proj;
+    PROJ_REQUIRE(s && s->have_mesh && out, "fvc_eval: call mesh_upload and basis_upload first");
+    cudaSetDevice(h->device);
+    const MeshDev m = mesh_dev(s);
+    int rc;
+    size_t nout = 0;
+    switch (op) {
+    case IB200_FVC_FLUX: {
+        PROJ_REQUIRE(j >= 0 && j < s->nU, "fvc_eval: field index out of range");
+        if ((rc = need_flux(h, s))) return rc;
+        nout = (size_t)(s->nInt + s->nBnd);
+        IB_CUDA(h, cudaMemcpyAsync(out, s->flux.as<double>() + (size_t)j * s->ldF, nout * sizeof(double), cudaMemcpyDefault, h->stream));
+        break;
+    }
+    case IB200_FVC_DIV_PHI: {
+        PROJ_REQUIRE(j >= 0 && j < s->nU && k >= 0 && k < s->nU, "fvc_eval: field index out of range");
+        if ((rc = need_flux(h, s))) return rc;
+        if ((rc = ensure(h, s->work, (size_t)s->nU * s->ldU * sizeof(double)))) return rc;
+        div_phi_kernel<<<dim3(gx(s->nCells), gy(s->nU)), PROJ_T, 0, h->stream>>>(
+            m, s->flux.as<double>() + (size_t)j * s->ldF, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb, s->nU,
+            s->work.as<double>(), s->ldU);
+        h->launches += 1;
+        nout = (size_t)3 * s->nCells;
+        IB_CUDA(h, cudaMemcpyAsync(out, s->work.as<double>() + (size_t)k * s->ldU, nout * sizeof(double), cudaMemcpyDefault, h->stream));
+        break;
+    }
+    case IB200_FVC_LAPLACIAN: {
+        PROJ_REQUIRE(j >= 0 && j < s->nU, "fvc_eval: field index out of range");
+        if ((rc = ensure(h, s->work, (size_t)s->nU * s->ldU * sizeof(double)))) return rc;
+        if ((rc = run_laplacians(h, s, s->work.as<double>()))) return rc;
+        nout = (size_t)3 * s->nCells;
+        IB_CUDA(h, cudaMemcpyAsync(out, s->work.as<double>() + (size_t)j * s->ldU, nout * sizeof(double), cudaMemcpyDefault, h->stream));
+        break;
+    }
+    case IB200_FVC_GRAD_P: {
+        PROJ_REQUIRE(j >= 0 && j < s->nP, "fvc_eval: field index out of range");
+        const long long ldo = pad16(3 * s->nCells);
+        if ((rc = ensure(h, s->work, (size_t)s->nP * ldo * sizeof(double)))) return rc;
+        grad_scalar_kernel<<<dim3(gx(s->nCells), gy(s->nP)), PROJ_T, 0, h->stream>>>(m, s->P.as<double>(), s->ldP, s->Pb.as<double>(),
+                                                                                      s->ldPb, s->nP, s->work.as<double>(), ldo);
+        h->launches += 1;
+        nout = (size_t)3 * s->nCells;
+        IB_CUDA(h, cudaMemcpyAsync(out, s->work.as<double>() + (size_t)j * ldo, nout * sizeof(double), cudaMemcpyDefault, h->stream));
+        break;
+    }
+    case IB200_FVC_DIV_U: {
+        PROJ_REQUIRE(j >= 0 && j < s->nU, "fvc_eval: field index out of range");
+        if ((rc = need_flux(h, s))) return rc;
+        const long long ldo = pad16(s->nCells);
+        if ((rc = ensure(h, s->work, (size_t)s->nU * ldo * sizeof(double)))) return rc;
+        surface_integrate_kernel<<<dim3(gx(s->nCells), gy(s->nU)), PROJ_T, 0, h->stream>>>(m, s->flux.as<double>(), s->ldF, s->nU,
+                                                                                            s->work.as<double>(), ldo);
+        h->launches += 1;
+        nout = (size_t)s->nCells;
+        IB_CUDA(h, cudaMemcpyAsync(out, s->work.as<double>() + (size_t)j * ldo, nout * sizeof(double), cudaMemcpyDefault, h->stream));
+        break;
+    }
+    default:
+        PROJ_REQUIRE(false, "fvc_eval: unknown operator");
+    }
+    IB_CUDA(h, cudaGetLastError());
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return IB200_OK;
+}
+
+// One projected operator. Output layouts are the reference's Eigen objects (column-major; C with i fastest).
+int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
+{
+    if (!h) return IB200_ERR_ARG;
+    ProjState* s = h->proj;
+    PROJ_REQUIRE(s && s->have_mesh && s->nU > 0, "project: call mesh_upload and basis_upload(U) first");
+    PROJ_REQUIRE(out, "project: null output");
+    PROJ_REQUIRE((op != IB200_OP_K && op != IB200_OP_P) || s->nP > 0, "project: K and P need basis_upload(P)");
+    cudaSetDevice(h->device);
+    const MeshDev m = mesh_dev(s);
+    const int N = s->nU, Np = s->nP, BIG = 0x7fffffff;
+    const long long K3 = 3 * s->nCells;
+    const double* U = s->U.as<double>();
+    const double* V = s->V.as<double>();
+    size_t nout = 0;
+    int rc;
+    for (double& x : s->ms) x = 0.0;
+    switch (op) {
+    case IB200_OP_M: {  // mass_term, steadyNS.C:1085-1108
+        nout = (size_t)N * N;
+        if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
+        StageTimer t(h->stream, &s->ms[5]);
+        rc = atvb_launch(h, U, s->ldU, N, U, s->ldU, N, K3, V, 3, 1, s->out.as<double>(), 1, BIG, 0, N);
+        t.stop();
+        if (rc) return rc;
+        break;
+    }
+    case IB200_OP_B: {  // diffusive_term, steadyNS.C:883-907
+        nout = (size_t)N * N;
+        if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
+        if ((rc = ensure(h, s->work, (size_t)N * s->ldU * sizeof(double)))) return rc;
+        if ((rc = run_laplacians(h, s, s->work.as<double>()))) return rc;
+        StageTimer t(h->stream, &s->ms[5]);
+        rc = atvb_launch(h, U, s->ldU, N, s->work.as<double>(), s->ldU, N, K3, V, 3, 0, s->out.as<double>(), 1, BIG, 0, N);
+        t.stop();
+        if (rc) return rc;
+        break;
+    }
+    case IB200_OP_K: {  // pressure_gradient_term, steadyNS.C:935-960: N x Np
+        nout = (size_t)N * Np;
+        if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
+        if ((rc = ensure(h, s->work, (size_t)Np * s->ldU * sizeof(double)))) return rc;
+        {
+            StageTimer t(h->stream, &s->ms[3]);
+            grad_scalar_kernel<<<dim3(gx(s->nCells), gy(Np)), PROJ_T, 0, h->stream>>>(m, s->P.as<double>(), s->ldP, s->Pb.as<double>(),
+                                                                                       s->ldPb, Np, s->work.as<double>(), s->ldU);
+            t.stop();
+            h->launches += 1;
+        }
+        StageTimer t(h->stream, &s->ms[5]);
+        rc = atvb_launch(h, U, s->ldU, N, s->work.as<double>(), s->ldU, Np, K3, V, 3, 0, s->out.as<double>(), 1, BIG, 0, N);
+        t.stop();
+        if (rc) return rc;
+        break;
+    }
+    case IB200_OP_P: {  // divergence_term, steadyNS.C:1112-1137: Np x N
+        nout = (size_t)Np * N;
+        if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
+        if ((rc = need_flux(h, s))) return rc;
+        if ((rc = ensure(h, s->work, (size_t)N * s->ldP * sizeof(double)))) return rc;
+        {
+            StageTimer t(h->stream, &s->ms[4]);
+            surface_integrate_kernel<<<dim3(gx(s->nCells), gy(N)), PROJ_T, 0, h->stream>>>(m, s->flux.as<double>(), s->ldF, N,
+                                                                                            s->work.as<double>(), s->ldP);
+            t.stop();
+            h->launches += 1;
+        }
+        StageTimer t(h->stream, &s->ms[5]);
+        rc = atvb_launch(h, s->P.as<double>(), s->ldP, Np, s->work.as<double>(), s->ldP, N, s->nCells, V, 1, 0, s->out.as<double>(), 1,
+                         BIG, 0, Np);
+        t.stop();
+        if (rc) return rc;
+        break;
+    }
+    case IB200_OP_C: {  // convective_term_tens (== _cache), steadyNS.C:997-1083: C(i,j,k) at i + N*(j + N*k)
+        nout = (size_t)N * N * N;
+        if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
+        if ((rc = need_flux(h, s))) return rc;
+        const size_t percol = (size_t)s->ldU * sizeof(double);
+        int jb = (int)std::max<size_t>(1, std::min<size_t>({(size_t)N, 8, (size_t)12e9 / (percol * N)}));
+        if ((rc = ensure(h, s->work, (size_t)jb * N * percol))) return rc;
+        for (int j0 = 0; j0 < N; j0 += jb) {
+            const int nj = std::min(jb, N - j0);
+            {
+                StageTimer t(h->stream, &s->ms[1]);
+                for (int jj = 0; jj < nj; jj++) {
+                    div_phi_kernel<<<dim3(gx(s->nCells), gy(N)), PROJ_T, 0, h->stream>>>(
+                        m, s->flux.as<double>() + (size_t)(j0 + jj) * s->ldF, U, s->ldU, s->Ub.as<double>(), s->ldUb, N,
+                        s->work.as<double>() + (size_t)jj * N * s->ldU, s->ldU);
+                    h->launches += 1;
+                }
+                t.stop();
+            }
+            StageTimer t(h->stream, &s->ms[5]);
+            // column jj*N + k of the work matrix = div(phi_{j0+jj}, U_k)  ->  C(i, j0+jj, k)
+            rc = atvb_launch(h, U, s->ldU, N, s->work.as<double>(), s->ldU, nj * N, K3, V, 3, 0,
+                             s->out.as<double>() + (size_t)N * j0, 1, N, N, (long long)N * N);
+            t.stop();
+            if (rc) return rc;
+        }
+        break;
+    }
+    default:
+        PROJ_REQUIRE(false, "project: unknown operator");
+    }
+    IB_CUDA(h, cudaGetLastError());
+    IB_CUDA(h, cudaMemcpyAsync(out, s->out.p, nout * sizeof(double), cudaMemcpyDefault, h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return IB200_OK;
+}
+
+// Device times (ms) of the last ithaca_b200_project call: out[0]=face flux out[1]=div(phi,U) out[2]=laplacian (+grad tensor)
+// out[3]=grad(p) out[4]=div(U) out[5]=contraction (DMMA).
+int ithaca_b200_proj_timings(ithaca_b200_t* h, double* out, int n)
+{
+    if (!h || !out || !h->proj) return IB200_ERR_ARG;
+    for (int i = 0; i < n; i++) out[i] = (i < 8) ? h->proj->ms[i] : 0.0;
+    return IB200_OK;
+}
+
+}  // extern "C"
