@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-projection", action="store_true", help="skip the C4 Galerkin-projection leg")
+    ap.add_argument("--projection", default="c4", choices=["c4", "c4small"])
     return ap.parse_args()
 
 
@@ -372,6 +374,15 @@ def run_b200(args, wl, rank, local_rank, world):
         "gram_tflops_total": achieved * world,
         "stages_ms": stages, "gpu_launches": int(launches), "clocks": clk, "e2e": e2e,
     }
+    if not args.no_projection and world == 1:
+        import bench_proj
+        del S, snaps_dev
+        torch.cuda.empty_cache()
+        try:
+            pj, _, _, _ = bench_proj.run(pod, torch, dev, args.projection, hbm_peak=hbm_peak, dmma_peak=peak_dmma)
+            line["projection"] = pj
+        except Exception as ex:  # never lose the POD line
+            line["projection"] = {"error": str(ex)[:200]}
     if not args.no_cpu_baseline and world >= 1:
         threads = 1
         rows = max(256, min(cells, int(2.0e10 / (2.0 * m * m * dim))))  # ~10-20 s of single-core Gram

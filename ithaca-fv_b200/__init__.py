@@ -65,7 +65,7 @@ def lib():
         L.ithaca_b200_pod_lift.argtypes = [P, I, I, P, P]
         L.ithaca_b200_pod_lift_patch.argtypes = [P, P, L64, P]
         L.ithaca_b200_dmma_peak.argtypes = [I, ctypes.POINTER(D)]
-        L.ithaca_b200_mesh_upload.argtypes = [P, L64, L64, L64] + [P] * 11
+        L.ithaca_b200_mesh_upload.argtypes = [P, L64, L64, L64] + [P] * 10
         L.ithaca_b200_mesh_addressing.argtypes = [P, P, P, P, ctypes.POINTER(ctypes.c_uint64)]
         L.ithaca_b200_basis_upload.argtypes = [P, I, P, P, I]
         L.ithaca_b200_project.argtypes = [P, I, P]
