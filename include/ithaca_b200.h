@@ -143,14 +143,17 @@ int ithaca_b200_mesh_addressing(ithaca_b200_t* h, int32_t* off, int32_t* ent, in
 int ithaca_b200_basis_upload(ithaca_b200_t* h, int which, const double* const* int_ptrs,
                              const double* const* bnd_ptrs, int n);
 
-enum { IB200_OP_M = 0, IB200_OP_B = 1, IB200_OP_K = 2, IB200_OP_P = 3, IB200_OP_C = 4 };
+enum { IB200_OP_M = 0, IB200_OP_B = 1, IB200_OP_K = 2, IB200_OP_P = 3, IB200_OP_C = 4, IB200_OP_C_MATERIALISED = 5 };
 /* One projected operator, laid out as the reference's Eigen object (column-major):
  *   IB200_OP_M  mass_term              steadyNS.C:1085-1108   N x N        M(i,j) = int U_i . U_j
  *   IB200_OP_B  diffusive_term         steadyNS.C:883-907     N x N        B(i,j) = int U_i . laplacian(1, U_j)
  *   IB200_OP_K  pressure_gradient_term steadyNS.C:935-960     N x Np       K(i,j) = int U_i . grad(P_j)
  *   IB200_OP_P  divergence_term        steadyNS.C:1112-1137   Np x N       P(i,j) = int P_i div(U_j)
  *   IB200_OP_C  convective_term_tens   steadyNS.C:997-1036    N x N x N    C(i,j,k) = int U_i . div(interpolate(U_j) & Sf, U_k),
- *               (values identical to convective_term_tens_cache :1038-1083), stored with i fastest. */
+ *               (values identical to convective_term_tens_cache :1038-1083), stored with i fastest. Computed as one
+ *               face-based contraction sum_f flux_j(f) * (Uf_k(f) . (U_i[own] - U_i[nei])) without materialising div fields.
+ *   IB200_OP_C_MATERIALISED  the same tensor through N^2 materialised fvc::div(flux_j, U_k) fields (the reference's
+ *               convective_term_tens_cache structure); kept as a cross-check and for the HBM-roofline measurement. */
 int ithaca_b200_project(ithaca_b200_t* h, int op, double* out);
 
 enum { IB200_FVC_FLUX = 0, IB200_FVC_DIV_PHI = 1, IB200_FVC_LAPLACIAN = 2, IB200_FVC_GRAD_P = 3, IB200_FVC_DIV_U = 4 };
@@ -163,7 +166,7 @@ enum { IB200_FVC_FLUX = 0, IB200_FVC_DIV_PHI = 1, IB200_FVC_LAPLACIAN = 2, IB200
 int ithaca_b200_fvc_eval(ithaca_b200_t* h, int op, int j, int k, double* out);
 
 /* Device times (ms) of the last ithaca_b200_project call: out[0]=face flux, [1]=div(phi,U), [2]=laplacian (+grad tensor),
- * [3]=grad(p), [4]=div(U), [5]=contraction. */
+ * [3]=grad(p), [4]=div(U), [5]=contraction, [6]=per-face records of the fused C. */
 int ithaca_b200_proj_timings(ithaca_b200_t* h, double* out, int n);
 
 /* ---- measurement helpers -------------------------------------------------------------------- */

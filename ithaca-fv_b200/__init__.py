@@ -223,7 +223,7 @@ class Pod:
         return out
 
 
-OPS = {"M": 0, "B": 1, "K": 2, "P": 3, "C": 4}
+OPS = {"M": 0, "B": 1, "K": 2, "P": 3, "C": 4, "Cmat": 5}
 FVC = {"flux": 0, "div_phi": 1, "laplacian": 2, "grad_p": 3, "div_u": 4}
 
 
@@ -232,7 +232,7 @@ class Projector:
     (src/ITHACA_FOMPROBLEMS/steadyNS/steadyNS.C:883-1137). `mesh` is any object with the attributes of
     ithaca_b200_mesh_upload's arguments (nCells, nInt, nBnd, owner, neighbour, Sf, magSf, w, dc, dcB, corr, V, bmask)."""
 
-    TIMER_NAMES = ["flux", "div_phi", "laplacian", "grad_p", "div_u", "contraction"]
+    TIMER_NAMES = ["flux", "div_phi", "laplacian", "grad_p", "div_u", "contraction", "face_records"]
 
     def __init__(self, pod):
         self.pod, self.L, self.h = pod, pod.L, pod.h
@@ -273,7 +273,7 @@ class Projector:
 
     def project(self, op):
         N, Np = self.N, self.Np
-        shape = {"M": (N, N), "B": (N, N), "K": (N, Np), "P": (Np, N), "C": (N, N, N)}[op]
+        shape = {"M": (N, N), "B": (N, N), "K": (N, Np), "P": (Np, N), "C": (N, N, N), "Cmat": (N, N, N)}[op]
         out = np.zeros(shape, order="F")
         self.pod._chk(self.L.ithaca_b200_project(self.h, OPS[op], out.ctypes.data))
         return out
@@ -286,8 +286,8 @@ class Projector:
         return out
 
     def timings(self):
-        out = np.zeros(6)
-        self.pod._chk(self.L.ithaca_b200_proj_timings(self.h, out.ctypes.data, 6))
+        out = np.zeros(7)
+        self.pod._chk(self.L.ithaca_b200_proj_timings(self.h, out.ctypes.data, 7))
         return dict(zip(self.TIMER_NAMES, out.tolist()))
 
 

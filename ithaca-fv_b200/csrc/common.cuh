@@ -62,6 +62,12 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* t
         "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
         ::"r"(smem_u32(smem_dst)), "l"(tmap), "r"(c0), "r"(c1), "r"(smem_u32(bar)) : "memory");
 }
+// 1-D bulk copy global -> shared (bytes multiple of 16, both addresses 16-B aligned), completion on an mbarrier.
+__device__ __forceinline__ void bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tmap)
 {
     asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
@@ -94,6 +100,25 @@ struct ithaca_b200;
 namespace ib200 {
 struct ProjState;  // proj.cu
 void proj_destroy(ithaca_b200* h);
+// growable device buffer (proj.cu / conv.cu)
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+int dev_ensure(ithaca_b200* h, DevBuf& b, size_t bytes);
+// conv.cu: fused convective tensor
+struct ConvMesh {
+    long long nInt, nBnd;
+    const int *owner, *neigh;
+    const double *Sf, *w;
+    const unsigned char* bmask;
+};
+struct ConvBufs {
+    DevBuf Ucm, Ubcm, Aj, Bk, Dd, ws, chunks;
+};
+int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long nCells, const double* U, long long ldU,
+                      const double* Ub, long long ldUb, int N, double* dC, double* ms_prep, double* ms_contract);
 void set_error(ithaca_b200* h, const std::string& msg);
 
 // cuTensorMapEncodeTiled through cudaGetDriverEntryPoint (no link-time libcuda dependency).

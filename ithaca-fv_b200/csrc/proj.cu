@@ -23,12 +23,6 @@
 
 namespace ib200 {
 
-struct DevBuf {
-    void* p = nullptr;
-    size_t cap = 0;
-    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
-};
-
 struct MeshDev {
     long long nCells, nInt, nBnd;
     const int *owner, *neigh;
@@ -49,10 +43,11 @@ struct ProjState {
     DevBuf work;   // operator fields, columns of ldU (vector) or ldP (scalar) doubles
     DevBuf T;      // gradient tensors of a batch of fields, 9*nCells doubles each
     DevBuf out;    // device copy of the projected operator
+    ConvBufs conv; // fused convective tensor (conv.cu)
     double ms[8] = {0};  // last timings: flux, div_phi, lap, grad, div, contraction
 };
 
-static int ensure(ithaca_b200* h, DevBuf& b, size_t bytes)
+int dev_ensure(ithaca_b200* h, DevBuf& b, size_t bytes)
 {
     if (bytes <= b.cap) return IB200_OK;
     if (b.p) cudaFree(b.p);
@@ -62,6 +57,8 @@ static int ensure(ithaca_b200* h, DevBuf& b, size_t bytes)
     b.cap = bytes;
     return IB200_OK;
 }
+
+static int ensure(ithaca_b200* h, DevBuf& b, size_t bytes) { return dev_ensure(h, b, bytes); }
 
 static int upload(ithaca_b200* h, DevBuf& b, const void* src, size_t bytes)
 {
@@ -77,7 +74,8 @@ void proj_destroy(ithaca_b200* h)
     if (!s) return;
     for (DevBuf* b : {&s->owner, &s->neigh, &s->Sf, &s->magSf, &s->w, &s->dc, &s->dcB, &s->corr, &s->V, &s->bmask,
                       &s->off, &s->ent, &s->other, &s->cnt, &s->blocksum, &s->U, &s->Ub, &s->P, &s->Pb, &s->flux,
-                      &s->work, &s->T, &s->out})
+                      &s->work, &s->T, &s->out, &s->conv.Ucm, &s->conv.Ubcm, &s->conv.Aj, &s->conv.Bk, &s->conv.Dd,
+                      &s->conv.ws, &s->conv.chunks})
         if (b->p) cudaFree(b->p);
     delete s;
     h->proj = nullptr;
@@ -842,7 +840,17 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
         if (rc) return rc;
         break;
     }
-    case IB200_OP_C: {  // convective_term_tens (== _cache), steadyNS.C:997-1083: C(i,j,k) at i + N*(j + N*k)
+    case IB200_OP_C: {  // convective_term_tens (== _cache), steadyNS.C:997-1083, fused face-based contraction (conv.cu)
+        nout = (size_t)N * N * N;
+        if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
+        ConvMesh cm;
+        cm.nInt = s->nInt; cm.nBnd = s->nBnd; cm.owner = m.owner; cm.neigh = m.neigh; cm.Sf = m.Sf; cm.w = m.w; cm.bmask = m.bmask;
+        rc = conv_fused_launch(h, &s->conv, cm, s->nCells, U, s->ldU, s->Ub.as<double>(), s->ldUb, N, s->out.as<double>(), &s->ms[6],
+                               &s->ms[5]);
+        if (rc) return rc;
+        break;
+    }
+    case IB200_OP_C_MATERIALISED: {  // same tensor through materialised div(phi_j, U_k) fields + cell-based contraction
         nout = (size_t)N * N * N;
         if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
         if ((rc = need_flux(h, s))) return rc;
@@ -880,7 +888,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
 }
 
 // Device times (ms) of the last ithaca_b200_project call: out[0]=face flux out[1]=div(phi,U) out[2]=laplacian (+grad tensor)
-// out[3]=grad(p) out[4]=div(U) out[5]=contraction (DMMA).
+// out[3]=grad(p) out[4]=div(U) out[5]=contraction (DMMA) out[6]=face records of the fused C (transpose + gather).
 int ithaca_b200_proj_timings(ithaca_b200_t* h, double* out, int n)
 {
     if (!h || !out || !h->proj) return IB200_ERR_ARG;
