@@ -1,16 +1,22 @@
-// K2 -- symmetric eigensolve of the m x m Gram matrix by one-sided (Hestenes) Jacobi, FP64, single GPU.
+// K2 -- symmetric eigensolve of the m x m Gram matrix: Cholesky-preconditioned one-sided (Hestenes) Jacobi, FP64.
 //
-// Replaces Spectra::SymEigsSolver<DenseSymMatProd> (ncv = m, LargestAlge) and
-// Eigen::SelfAdjointEigenSolver at src/ITHACA_CORE/ITHACAPOD/ITHACAPOD.C:157-180.
+// Replaces Spectra::SymEigsSolver<DenseSymMatProd> (ncv = m, LargestAlge) and Eigen::SelfAdjointEigenSolver at
+// src/ITHACA_CORE/ITHACAPOD/ITHACAPOD.C:157-180.
 //
-// Method: W <- G, Q <- I; plane rotations from the right orthogonalise the columns of W while the same
-// rotations accumulate in Q, so W = G Q throughout. At convergence W = Q Lambda: lambda_i = q_i . w_i
-// (signed, so the reference's negative-eigenvalue branch ITHACAPOD.C:182-186 still sees negative values),
-// eigenvectors = columns of Q (orthonormal to working precision for ALL i, including the noise floor).
-// Pairs follow the round-robin tournament ordering: m/2 disjoint pairs per round, one warp per pair,
-// one grid-wide barrier per round (cooperative launch). Stop when a whole sweep applies no rotation,
-// i.e. every pair satisfies |w_i . w_j| <= tol * |w_i| |w_j| with tol = sqrt(m) * 2^-52 (LAPACK dgesvj's
-// criterion).
+// Method (Veselic-Hari / Drmac): G + sigma I = L L^T (blocked Cholesky on the device), then plane rotations from the
+// right orthogonalise the COLUMNS of X = L:  X V = U Sigma  =>  G = U (Sigma^2 - sigma I) U^T.
+//   eigenvalues  lambda_i = |x_i|^2 - sigma   (signed, so the reference's negative-shift branch ITHACAPOD.C:182-186
+//                still sees negative values), eigenvectors u_i = x_i / |x_i| -- no rotation accumulator is needed.
+// Working on the factor instead of on G converges in about half the sweeps (the iteration sees cond(G), not
+// cond(G)^2) and halves the work per rotation. sigma = 0 when G is numerically positive definite; when the
+// factorisation meets a non-positive pivot (exactly singular or indefinite input) it is repeated with a shift
+// (first a few ulps of the largest diagonal entry, then a Gershgorin bound), which leaves the eigenvectors unchanged.
+//
+// Parallel ordering: block-cyclic. Columns are cut into blocks of b; a tournament over the blocks gives nb-1 rounds
+// per sweep; in every round one CTA owns a block pair, keeps its 2b columns in shared memory and rotates all b^2 cross
+// pairs (b inner rounds of b disjoint pairs, one warp per pair); intra-block pairs are done once per sweep. One grid
+// barrier per block round (cooperative launch) instead of one per column-pair round.
+// Stop when a whole sweep applies no rotation: |x_i . x_j| <= tol |x_i| |x_j|, tol = sqrt(m) 2^-52 (LAPACK dgesvj).
 #include "../../include/ithaca_b200.h"
 #include "common.cuh"
 #include <cooperative_groups.h>
@@ -21,8 +27,8 @@ namespace cg = cooperative_groups;
 
 namespace ib200 {
 
-constexpr int EIG_THREADS = 256;
 constexpr int EIG_MAX_SWEEPS = 40;
+constexpr int CH_B = 32;  // Cholesky panel width
 
 __device__ __forceinline__ double warp_sum(double v)
 {
@@ -31,80 +37,224 @@ __device__ __forceinline__ double warp_sum(double v)
     return v;
 }
 
-__global__ void eig_init_kernel(const double* __restrict__ G, double* __restrict__ W, double* __restrict__ Q, int m)
+// X = lower(G) + sigma I, strict upper triangle = 0 (column-major m x m)
+__global__ void eig_init_kernel(const double* __restrict__ G, double* __restrict__ X, int m, double sigma)
 {
     const size_t mm = (size_t)m * m;
     for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < mm; idx += (size_t)gridDim.x * blockDim.x) {
-        W[idx] = G[idx];
-        Q[idx] = ((int)(idx / m) == (int)(idx % m)) ? 1.0 : 0.0;
+        const int i = (int)(idx % m), j = (int)(idx / m);
+        X[idx] = (i > j) ? G[idx] : (i == j ? G[idx] + sigma : 0.0);
     }
 }
 
-// flags[0..EIG_MAX_SWEEPS): number of rotations applied in each sweep; flags[EIG_MAX_SWEEPS] = sweeps done.
-__global__ void __launch_bounds__(EIG_THREADS)
-eig_jacobi_kernel(double* W, double* Q, int m, double tol, int* flags)
+// max diagonal entry and Gershgorin bound max_i (sum_{j != i} |G_ij| - G_ii): out[0], out[1]. One block.
+__global__ void eig_bounds_kernel(const double* __restrict__ G, int m, double* __restrict__ out)
+{
+    __shared__ double sd[32], sg[32];
+    double dmax = -1e300, gmax = -1e300;
+    for (int i = threadIdx.x; i < m; i += blockDim.x) {
+        double s = 0.0;
+        for (int j = 0; j < m; j++) if (j != i) s += fabs(G[(size_t)i + (size_t)j * m]);
+        const double d = G[(size_t)i + (size_t)i * m];
+        dmax = fmax(dmax, fabs(d));
+        gmax = fmax(gmax, s - d);
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        dmax = fmax(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
+        gmax = fmax(gmax, __shfl_xor_sync(0xffffffffu, gmax, o));
+    }
+    if ((threadIdx.x & 31) == 0) { sd[threadIdx.x >> 5] = dmax; sg[threadIdx.x >> 5] = gmax; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < (int)(blockDim.x >> 5); w++) { sd[0] = fmax(sd[0], sd[w]); sg[0] = fmax(sg[0], sg[w]); }
+        out[0] = sd[0];
+        out[1] = sg[0];
+    }
+}
+
+// ---- blocked right-looking Cholesky, panel width CH_B ------------------------------------------------------------
+// (1) diagonal block: unblocked Cholesky in shared memory; flag[0] = 1 on a non-positive (or NaN) pivot.
+__global__ void __launch_bounds__(CH_B * CH_B) chol_diag_kernel(double* __restrict__ X, int m, int k0, int* __restrict__ flag)
+{
+    __shared__ double a[CH_B][CH_B + 1];
+    const int nb = min(CH_B, m - k0);
+    const int r = threadIdx.x % CH_B, c = threadIdx.x / CH_B;
+    if (r < nb && c < nb) a[r][c] = X[(size_t)(k0 + r) + (size_t)(k0 + c) * m];
+    __syncthreads();
+    for (int k = 0; k < nb; k++) {
+        const double d = a[k][k];
+        __syncthreads();
+        if (!(d > 0.0)) { if (threadIdx.x == 0) flag[0] = 1; return; }
+        const double s = sqrt(d);
+        if (c == k && r >= k && r < nb) a[r][k] = (r == k) ? s : a[r][k] / s;
+        __syncthreads();
+        if (c > k && c < nb && r >= c && r < nb) a[r][c] -= a[r][k] * a[c][k];
+        __syncthreads();
+    }
+    if (r < nb && c < nb) X[(size_t)(k0 + r) + (size_t)(k0 + c) * m] = (r >= c) ? a[r][c] : 0.0;
+}
+
+// (2) panel: rows below the diagonal block, X[i, k0:k0+nb] <- X[i, k0:k0+nb] L_kk^{-T}. One thread per row.
+__global__ void __launch_bounds__(128) chol_panel_kernel(double* __restrict__ X, int m, int k0)
+{
+    __shared__ double l[CH_B][CH_B + 1];
+    const int nb = min(CH_B, m - k0);
+    for (int idx = threadIdx.x; idx < nb * nb; idx += blockDim.x) {
+        const int r = idx % nb, c = idx / nb;
+        l[r][c] = X[(size_t)(k0 + r) + (size_t)(k0 + c) * m];
+    }
+    __syncthreads();
+    const int i = k0 + nb + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    double x[CH_B];
+#pragma unroll
+    for (int c = 0; c < CH_B; c++) x[c] = (c < nb) ? X[(size_t)i + (size_t)(k0 + c) * m] : 0.0;
+#pragma unroll
+    for (int c = 0; c < CH_B; c++) {
+        if (c < nb) {
+            double s = x[c];
+#pragma unroll
+            for (int q = 0; q < CH_B; q++) if (q < c) s -= x[q] * l[c][q];
+            x[c] = s / l[c][c];
+        }
+    }
+#pragma unroll
+    for (int c = 0; c < CH_B; c++) if (c < nb) X[(size_t)i + (size_t)(k0 + c) * m] = x[c];
+}
+
+// (3) trailing update: X[i,j] -= sum_c L[i,k0+c] L[j,k0+c] for i >= j >= k0+nb. 32x32 tiles of the lower triangle.
+__global__ void __launch_bounds__(256) chol_update_kernel(double* __restrict__ X, int m, int k0)
+{
+    const int nb = min(CH_B, m - k0);
+    const int t0 = k0 + nb;
+    if (blockIdx.x > blockIdx.y) return;  // lower triangle of tiles: column tile <= row tile
+    const int i0 = t0 + blockIdx.y * 32, j0 = t0 + blockIdx.x * 32;
+    __shared__ double li[32][CH_B + 1], lj[32][CH_B + 1];
+    for (int idx = threadIdx.x; idx < 32 * CH_B; idx += 256) {
+        const int r = idx % 32, c = idx / 32;
+        li[r][c] = (i0 + r < m && c < nb) ? X[(size_t)(i0 + r) + (size_t)(k0 + c) * m] : 0.0;
+        lj[r][c] = (j0 + r < m && c < nb) ? X[(size_t)(j0 + r) + (size_t)(k0 + c) * m] : 0.0;
+    }
+    __syncthreads();
+    const int r = threadIdx.x % 32;
+    for (int cc = threadIdx.x / 32; cc < 32; cc += 8) {
+        const int i = i0 + r, j = j0 + cc;
+        if (i < m && j < m && i >= j) {
+            double s = 0.0;
+#pragma unroll
+            for (int c = 0; c < CH_B; c++) s += li[r][c] * lj[cc][c];
+            X[(size_t)i + (size_t)j * m] -= s;
+        }
+    }
+}
+
+// ---- block-cyclic one-sided Jacobi on the columns of X (m x m, column-major) -----------------------------------
+// One warp rotates one column pair held in shared memory. Returns 1 if a rotation was applied.
+__device__ __forceinline__ int rotate_pair(double* xi, double* xj, int m, int lane, double tol)
+{
+    double a = 0.0, b = 0.0, c = 0.0;
+    for (int k = lane; k < m; k += 32) {
+        const double x = xi[k], y = xj[k];
+        a += x * x; b += y * y; c += x * y;
+    }
+    a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
+    const double ab = a * b;
+    if (!(ab > 0.0) || fabs(c) <= tol * sqrt(ab)) return 0;
+    const double zeta = (b - a) / (2.0 * c);
+    const double tt = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
+    const double cs = 1.0 / sqrt(1.0 + tt * tt);
+    const double sn = cs * tt;
+    for (int k = lane; k < m; k += 32) {
+        const double x = xi[k], y = xj[k];
+        xi[k] = cs * x - sn * y;
+        xj[k] = sn * x + cs * y;
+    }
+    return 1;
+}
+
+// flags[0..EIG_MAX_SWEEPS): rotations applied in each sweep; flags[EIG_MAX_SWEEPS] = sweeps done.
+// b columns per block, nb blocks; blockDim = 32*b (one warp per pair of an inner round). smem: 2*b*m doubles.
+__global__ void eig_jacobi_block_kernel(double* X, int m, int b, int nb, double tol, int* flags)
 {
     cg::grid_group grid = cg::this_grid();
-    const int lane = threadIdx.x & 31;
-    const int gwarp = blockIdx.x * (EIG_THREADS / 32) + (threadIdx.x >> 5);
-    const int nwarps = gridDim.x * (EIG_THREADS / 32);
-    const int n = (m + 1) & ~1;  // players in the tournament (one dummy when m is odd)
-    const int npairs = n / 2;
+    extern __shared__ double sx[];  // 2b columns of m doubles
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nbp = (nb + 1) & ~1;       // tournament players (one dummy block when nb is odd)
+    const int npairs = nbp / 2;
+    auto ncols = [&](int blk) { return min(b, m - blk * b); };
 
     int sweep = 0;
     for (; sweep < EIG_MAX_SWEEPS; sweep++) {
-        for (int rd = 0; rd < n - 1; rd++) {
-            for (int p = gwarp; p < npairs; p += nwarps) {
-                int i, j;
-                if (p == 0) { i = n - 1; j = rd; }
-                else { i = (rd + p) % (n - 1); j = (rd - p + (n - 1)) % (n - 1); }
-                if (i >= m || j >= m) continue;  // dummy player
-                if (i > j) { int tmp = i; i = j; j = tmp; }
-                double* wi = W + (size_t)i * m;
-                double* wj = W + (size_t)j * m;
-                double a = 0.0, b = 0.0, c = 0.0;
-                for (int k = lane; k < m; k += 32) {
-                    const double x = wi[k], y = wj[k];
-                    a += x * x; b += y * y; c += x * y;
+        int rot = 0;
+        // ---- phase 0: pairs inside each block (tournament over the block's columns) ----
+        for (int blk = blockIdx.x; blk < nb; blk += gridDim.x) {
+            const int nc = ncols(blk);
+            double* g = X + (size_t)blk * b * m;
+            for (int idx = threadIdx.x; idx < nc * m; idx += blockDim.x) sx[idx] = g[idx];
+            __syncthreads();
+            const int n = (nc + 1) & ~1;
+            for (int rd = 0; rd < n - 1; rd++) {
+                if (warp < n / 2) {
+                    int i, j;
+                    if (warp == 0) { i = n - 1; j = rd; }
+                    else { i = (rd + warp) % (n - 1); j = (rd - warp + (n - 1)) % (n - 1); }
+                    if (i < nc && j < nc) {
+                        if (i > j) { const int t = i; i = j; j = t; }
+                        rot += rotate_pair(sx + (size_t)i * m, sx + (size_t)j * m, m, lane, tol);
+                    }
                 }
-                a = warp_sum(a); b = warp_sum(b); c = warp_sum(c);
-                const double ab = a * b;
-                if (!(ab > 0.0) || fabs(c) <= tol * sqrt(ab)) continue;
-                // rotation that zeroes w_i . w_j
-                const double zeta = (b - a) / (2.0 * c);
-                const double tt = copysign(1.0, zeta) / (fabs(zeta) + sqrt(1.0 + zeta * zeta));
-                const double cs = 1.0 / sqrt(1.0 + tt * tt);
-                const double sn = cs * tt;
-                double* qi = Q + (size_t)i * m;
-                double* qj = Q + (size_t)j * m;
-                for (int k = lane; k < m; k += 32) {
-                    const double x = wi[k], y = wj[k];
-                    wi[k] = cs * x - sn * y;
-                    wj[k] = sn * x + cs * y;
-                    const double u = qi[k], v = qj[k];
-                    qi[k] = cs * u - sn * v;
-                    qj[k] = sn * u + cs * v;
+                __syncthreads();
+            }
+            for (int idx = threadIdx.x; idx < nc * m; idx += blockDim.x) g[idx] = sx[idx];
+            __syncthreads();
+        }
+        grid.sync();
+        // ---- block tournament: nbp-1 rounds, each CTA owns block pairs (I,J) and rotates all cross pairs ----
+        for (int rd = 0; rd < nbp - 1; rd++) {
+            for (int p = blockIdx.x; p < npairs; p += gridDim.x) {
+                int I, J;
+                if (p == 0) { I = nbp - 1; J = rd; }
+                else { I = (rd + p) % (nbp - 1); J = (rd - p + (nbp - 1)) % (nbp - 1); }
+                if (I >= nb || J >= nb) continue;  // dummy block (uniform over the CTA)
+                if (I > J) { const int t = I; I = J; J = t; }
+                const int ni = ncols(I), nj = ncols(J);
+                double* gi = X + (size_t)I * b * m;
+                double* gj = X + (size_t)J * b * m;
+                double* sj = sx + (size_t)b * m;
+                for (int idx = threadIdx.x; idx < ni * m; idx += blockDim.x) sx[idx] = gi[idx];
+                for (int idx = threadIdx.x; idx < nj * m; idx += blockDim.x) sj[idx] = gj[idx];
+                __syncthreads();
+                for (int s = 0; s < b; s++) {
+                    const int i = warp, j = (warp + s) % b;
+                    if (i < ni && j < nj) rot += rotate_pair(sx + (size_t)i * m, sj + (size_t)j * m, m, lane, tol);
+                    __syncthreads();
                 }
-                if (lane == 0) atomicAdd(&flags[sweep], 1);
+                for (int idx = threadIdx.x; idx < ni * m; idx += blockDim.x) gi[idx] = sx[idx];
+                for (int idx = threadIdx.x; idx < nj * m; idx += blockDim.x) gj[idx] = sj[idx];
+                __syncthreads();
             }
             grid.sync();
         }
+        if (lane == 0 && rot) atomicAdd(&flags[sweep], rot);
+        grid.sync();
         if (*(volatile int*)&flags[sweep] == 0) { sweep++; break; }
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) flags[EIG_MAX_SWEEPS] = sweep;
 }
 
-// lambda_i = q_i . w_i, one warp per column.
-__global__ void eig_values_kernel(const double* __restrict__ W, const double* __restrict__ Q, int m,
-                                  double* __restrict__ lam)
+// lambda_i = |x_i|^2 - sigma, u_i = x_i / |x_i| (in place). One warp per column.
+__global__ void eig_finalize_kernel(double* __restrict__ X, int m, double sigma, double* __restrict__ lam)
 {
     const int lane = threadIdx.x & 31;
     const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     if (i >= m) return;
+    double* x = X + (size_t)i * m;
     double s = 0.0;
-    for (int k = lane; k < m; k += 32) s += Q[(size_t)i * m + k] * W[(size_t)i * m + k];
+    for (int k = lane; k < m; k += 32) s += x[k] * x[k];
     s = warp_sum(s);
-    if (lane == 0) lam[i] = s;
+    const double inv = s > 0.0 ? 1.0 / sqrt(s) : 0.0;
+    for (int k = lane; k < m; k += 32) x[k] *= inv;
+    if (lane == 0) lam[i] = s - sigma;
 }
 
 // Descending rank sort (stable) + column permutation with a deterministic sign (largest |component| > 0).
@@ -158,39 +308,92 @@ __global__ void eig_sort_permute_kernel(const double* __restrict__ lam, const do
     if (threadIdx.x == 0) lam_sorted[rank] = li;
 }
 
+static int cholesky(ithaca_b200* h, double* X, int m, int* flag_dev, bool* ok)
+{
+    IB_CUDA(h, cudaMemsetAsync(flag_dev, 0, sizeof(int), h->stream));
+    for (int k0 = 0; k0 < m; k0 += CH_B) {
+        const int nb = std::min(CH_B, m - k0), rest = m - k0 - nb;
+        chol_diag_kernel<<<1, CH_B * CH_B, 0, h->stream>>>(X, m, k0, flag_dev);
+        h->launches += 1;
+        if (rest > 0) {
+            chol_panel_kernel<<<(rest + 127) / 128, 128, 0, h->stream>>>(X, m, k0);
+            const int nt = (rest + 31) / 32;
+            chol_update_kernel<<<dim3(nt, nt), 256, 0, h->stream>>>(X, m, k0);
+            h->launches += 2;
+        }
+    }
+    IB_CUDA(h, cudaGetLastError());
+    int f = 0;
+    IB_CUDA(h, cudaMemcpyAsync(&f, flag_dev, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    *ok = (f == 0);
+    return IB200_OK;
+}
+
 int eig_launch(ithaca_b200* h, int* sweeps)
 {
     const int m = h->m;
-    // dQ doubles as the Jacobi accumulator; the sorted eigenvectors end in dW, then the two are swapped.
-    double* lam_tmp = nullptr;
-    IB_CUDA(h, cudaMalloc(&lam_tmp, (size_t)m * sizeof(double)));
-    IB_CUDA(h, cudaMemsetAsync(h->dFlags, 0, 64 * sizeof(int), h->stream));
+    const double eps = 2.220446049250313e-16;
+    double* lam_tmp = nullptr;   // m eigenvalues + 2 bounds
+    IB_CUDA(h, cudaMalloc(&lam_tmp, (size_t)(m + 2) * sizeof(double)));
+    auto fail = [&](int rc) { cudaFree(lam_tmp); return rc; };
+    int* flags = h->dFlags;       // [0..40] sweep counters, [48] Cholesky flag
+    eig_bounds_kernel<<<1, 256, 0, h->stream>>>(h->dG, m, lam_tmp + m);
+    double bounds[2] = {0.0, 0.0};
+    if (cudaMemcpyAsync(bounds, lam_tmp + m, 2 * sizeof(double), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
+        cudaStreamSynchronize(h->stream) != cudaSuccess) {
+        set_error(h, "eig: device failure");
+        return fail(IB200_ERR_CUDA);
+    }
+    h->launches += 1;
+    const double dmax = bounds[0], gersh = std::max(bounds[1], 0.0);
+    const double tiny = 16.0 * m * eps * dmax;
+    const double shifts[3] = {0.0, tiny, gersh * (1.0 + 1e-3) + tiny};
     const int ib = 256;
     const int ig = (int)std::min<size_t>(((size_t)m * m + ib - 1) / ib, 8 * (size_t)h->num_sms);
-    eig_init_kernel<<<ig, ib, 0, h->stream>>>(h->dG, h->dW, h->dQ, m);
+    double sigma = 0.0;
+    bool ok = false;
+    for (int attempt = 0; attempt < 3 && !ok; attempt++) {
+        sigma = shifts[attempt];
+        if (attempt > 0 && !(sigma > shifts[attempt - 1])) continue;
+        eig_init_kernel<<<ig, ib, 0, h->stream>>>(h->dG, h->dW, m, sigma);
+        h->launches += 1;
+        int rc = cholesky(h, h->dW, m, flags + 48, &ok);
+        if (rc) return fail(rc);
+    }
+    if (!ok) {
+        set_error(h, "The Eigenvalue Decomposition did not succeed (matrix is not finite)");
+        return fail(IB200_ERR_NOCONV);
+    }
 
-    const int npairs = (m + 1) / 2;
-    const int wpb = EIG_THREADS / 32;
+    // block size: 2b columns of m doubles must fit shared memory; one warp per pair of an inner round
+    int b = std::min({16, m, (int)((200 * 1024) / (16 * (size_t)m))});
+    if (b < 1) { set_error(h, "pod_eig: more than 12800 snapshots are not supported"); return fail(IB200_ERR_ARG); }
+    if (b < 2 && m >= 2) b = std::min(2, m);
+    const int nb = (m + b - 1) / b;
+    const int threads = std::max(64, 32 * b);
+    const size_t smem = (size_t)2 * b * m * sizeof(double);
+    if (smem > 227 * 1024) { set_error(h, "pod_eig: too many snapshots for the Jacobi block kernel"); return fail(IB200_ERR_ARG); }
+    IB_CUDA(h, cudaFuncSetAttribute(eig_jacobi_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int maxb = 0;
-    IB_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&maxb, eig_jacobi_kernel, EIG_THREADS, 0));
-    int nblocks = std::max(1, std::min((npairs + wpb - 1) / wpb, maxb * h->num_sms));
-    double tol = std::sqrt((double)m) * 2.220446049250313e-16;
-    double* W = h->dW;
-    double* Q = h->dQ;
-    int mm = m;
-    int* flags = h->dFlags;
-    void* args[] = {&W, &Q, &mm, &tol, &flags};
-    IB_CUDA(h, cudaLaunchCooperativeKernel((void*)eig_jacobi_kernel, dim3(nblocks), dim3(EIG_THREADS), args, 0, h->stream));
-    eig_values_kernel<<<(m + 7) / 8, 256, 0, h->stream>>>(h->dW, h->dQ, m, lam_tmp);
-    // sorted eigenvectors are written over W (no longer needed once lambda is known)
-    eig_sort_permute_kernel<<<m, 128, 0, h->stream>>>(lam_tmp, h->dQ, m, h->dEvals, h->dW);
+    IB_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&maxb, eig_jacobi_block_kernel, threads, smem));
+    if (maxb < 1) { set_error(h, "pod_eig: Jacobi kernel does not fit one SM"); return fail(IB200_ERR_CUDA); }
+    const int want = std::max((nb + 1) / 2, 1);
+    const int nblocks = std::max(1, std::min(want, maxb * h->num_sms));
+    IB_CUDA(h, cudaMemsetAsync(flags, 0, 48 * sizeof(int), h->stream));
+    double tol = std::sqrt((double)m) * eps;
+    double* X = h->dW;
+    int mm = m, bb = b, nbb = nb;
+    void* args[] = {&X, &mm, &bb, &nbb, &tol, &flags};
+    IB_CUDA(h, cudaLaunchCooperativeKernel((void*)eig_jacobi_block_kernel, dim3(nblocks), dim3(threads), args, smem, h->stream));
+    eig_finalize_kernel<<<(m + 7) / 8, 256, 0, h->stream>>>(h->dW, m, sigma, lam_tmp);
+    eig_sort_permute_kernel<<<m, 128, 0, h->stream>>>(lam_tmp, h->dW, m, h->dEvals, h->dQ);
     IB_CUDA(h, cudaGetLastError());
-    h->launches += 4;
+    h->launches += 3;
     int hflags[EIG_MAX_SWEEPS + 1];
-    IB_CUDA(h, cudaMemcpyAsync(hflags, h->dFlags, sizeof(hflags), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaMemcpyAsync(hflags, flags, sizeof(hflags), cudaMemcpyDeviceToHost, h->stream));
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
     cudaFree(lam_tmp);
-    std::swap(h->dQ, h->dW);
     const int done = hflags[EIG_MAX_SWEEPS];
     if (sweeps) *sweeps = done;
     if (done >= EIG_MAX_SWEEPS && hflags[EIG_MAX_SWEEPS - 1] != 0) {
