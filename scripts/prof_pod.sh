@@ -7,5 +7,5 @@ $CMD > gpurun_out/plain_$TAG.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --csv --log-file gpurun_out/launches_$TAG.csv $CMD > gpurun_out/ncu_launch_$TAG.log 2>&1
 $CMD > gpurun_out/plain2_$TAG.log 2>&1 &&
 ncu --set full --clock-control none --import-source on -k regex:'gram_kernel|lift_kernel|eig_' -c 6 -f -o gpurun_out/prof_${TAG}_pod $CMD > gpurun_out/ncu_full_$TAG.log 2>&1
-tail -3 gpurun_out/ncu_launch_$TAG.log gpurun_out/ncu_full_$TAG.log
+tail -n 3 gpurun_out/ncu_launch_$TAG.log gpurun_out/ncu_full_$TAG.log
 ls -la gpurun_out
