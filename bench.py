@@ -30,6 +30,8 @@ WORKLOADS = {
     "c1": dict(cells=10_000, dim=3, m=100, r=10, sharded=False, name="C1 10k cells x 100 vector snapshots, 10 modes"),
     "c2": dict(cells=2_000_000, dim=1, m=200, r=20, sharded=False,
                name="C2 2M cells x 200 scalar FP64 snapshots, 20 modes (per rank)"),
+    "c3r8": dict(cells=2_500_000, dim=3, m=1000, r=50, sharded=False,
+                 name="C3/8: one rank's shard of C3 at 8 GPUs, 2.5M cells x 1000 vector FP64 snapshots (60 GB), 50 modes (per rank)"),
     "c3": dict(cells=20_000_000, dim=3, m=1000, r=50, sharded=True,
                name="C3 20M cells x 1000 vector FP64 snapshots, 50 modes (cell-sharded over ranks)"),
 }
