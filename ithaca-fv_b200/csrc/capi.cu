@@ -210,7 +210,7 @@ int ithaca_b200_destroy(ithaca_b200_t* h)
     if (h->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->nccl_comm);
     for (void* p : {(void*)h->dV, (void*)h->dS, (void*)h->dG, (void*)h->dWs, (void*)h->dQ, (void*)h->dW,
                     (void*)h->dEvals, (void*)h->dQr, (void*)h->dPhi, (void*)h->dNormPart, (void*)h->dNorm,
-                    h->dJobs, (void*)h->dFlags})
+                    h->dJobs, (void*)h->dFlags, h->wexp[0].p, h->wexp[1].p})
         if (p) cudaFree(p);
     for (int i = 0; i < T_COUNT; i++) {
         cudaEventDestroy(h->timers[i].a);
@@ -296,6 +296,7 @@ int ithaca_b200_pod_set_volumes(ithaca_b200_t* h, const double* V, int64_t nCell
     IB_CUDA(h, cudaMemcpyAsync(h->dV, V, (size_t)nCells * sizeof(double), cudaMemcpyDefault, h->stream));
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
     h->nCells = nCells;
+    h->vol_gen++;
     h->have_gram = h->have_eig = h->have_lift = false;
     return IB200_OK;
 }

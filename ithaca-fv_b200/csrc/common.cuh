@@ -198,6 +198,14 @@ struct ithaca_b200 {
     bool have_lift = false;
     void* dJobs = nullptr;
     size_t dJobs_cap = 0;
+    // dim-times repeated weight vectors of the contraction kernel (gram.cu), keyed on (V, dim, K, vol_gen)
+    ib200::DevBuf wexp[2];
+    const double* wexp_V[2] = {nullptr, nullptr};
+    int wexp_dim[2] = {0, 0};
+    long long wexp_K[2] = {0, 0};
+    unsigned long long wexp_gen[2] = {0, 0};
+    unsigned long long vol_gen = 1;  // bumped whenever a volume vector on the device may have changed
+    int wexp_next = 0;
     int* dFlags = nullptr;
 
     // ---- projection state (proj.cu) ----

@@ -615,6 +615,7 @@ int ithaca_b200_mesh_upload(ithaca_b200_t* h, int64_t nCells, int64_t nIntFaces,
     ProjState* s = h->proj;
     s->have_mesh = false;
     s->have_flux = false;
+    h->vol_gen++;
     s->nCells = nCells; s->nInt = nIntFaces; s->nBnd = nBndFaces;
     const long long nF = nIntFaces + nBndFaces;
     int rc;
