@@ -23,6 +23,10 @@
 
 namespace ib200 {
 
+// renumber.cu
+void mesh_renumber(long long nCells, long long nInt, const int* owner, const int* neigh, std::vector<int>& old2new,
+                   std::vector<int>& fnew2old);
+
 struct MeshDev {
     long long nCells, nInt, nBnd;
     const int *owner, *neigh;
@@ -34,7 +38,12 @@ struct MeshDev {
 struct ProjState {
     long long nCells = 0, nInt = 0, nBnd = 0;
     bool have_mesh = false, corrected = false;
-    DevBuf owner, neigh, Sf, magSf, w, dc, dcB, corr, V, bmask, off, ent, other, cnt, blocksum;
+    DevBuf owner, neigh, Sf, magSf, w, dc, dcB, corr, V, bmask, off, ent, other, cnt, blocksum;   // renumbered mesh (renumber.cu)
+    DevBuf owner0, neigh0, off0, ent0, other0;   // the caller's addressing (mesh_addressing reports this one)
+    bool have_csr0 = false;
+    DevBuf perm;    // old2new cell label (int, nCells)
+    DevBuf fperm;   // original index of the internal face at each new position (int, nInt)
+    DevBuf stage;   // one field in the caller's order (upload / fvc_eval staging)
     int nU = 0, nP = 0;
     long long ldU = 0, ldUb = 0, ldP = 0, ldPb = 0, ldF = 0;
     DevBuf U, Ub, P, Pb;
@@ -74,6 +83,7 @@ void proj_destroy(ithaca_b200* h)
     if (!s) return;
     for (DevBuf* b : {&s->owner, &s->neigh, &s->Sf, &s->magSf, &s->w, &s->dc, &s->dcB, &s->corr, &s->V, &s->bmask,
                       &s->off, &s->ent, &s->other, &s->cnt, &s->blocksum, &s->U, &s->Ub, &s->P, &s->Pb, &s->flux,
+                      &s->owner0, &s->neigh0, &s->off0, &s->ent0, &s->other0, &s->perm, &s->fperm, &s->stage,
                       &s->work, &s->T, &s->out, &s->conv.Ucm, &s->conv.Ubcm, &s->conv.Aj, &s->conv.Bk, &s->conv.Dd,
                       &s->conv.ws, &s->conv.chunks})
         if (b->p) cudaFree(b->p);
@@ -195,6 +205,58 @@ __global__ void csr_sort_kernel(const int* __restrict__ off, long long nCells, i
         ent[j + 1] = e;
         other[j + 1] = o;
     }
+}
+
+// ------------------------------------------------------------------------------------------------
+// renumbered copy of the mesh (see renumber.cu): cells old -> perm[old], internal faces new -> fperm[new] (orientation
+// kept, so no sign or weight changes), boundary faces keep their order.
+// ------------------------------------------------------------------------------------------------
+struct MeshSrc {
+    const int *owner, *neigh;
+    const double *Sf, *magSf, *w, *dc, *corr;
+};
+__global__ void permute_faces_kernel(MeshSrc in, const int* __restrict__ perm, const int* __restrict__ fperm, long long nInt,
+                                     long long nF, int* __restrict__ owner, int* __restrict__ neigh, double* __restrict__ Sf,
+                                     double* __restrict__ magSf, double* __restrict__ w, double* __restrict__ dc,
+                                     double* __restrict__ corr)
+{
+    for (long long f = blockIdx.x * (long long)blockDim.x + threadIdx.x; f < nF; f += (long long)gridDim.x * blockDim.x) {
+        const long long g = (f < nInt) ? fperm[f] : f;
+        owner[f] = perm[in.owner[g]];
+        Sf[3 * f] = in.Sf[3 * g]; Sf[3 * f + 1] = in.Sf[3 * g + 1]; Sf[3 * f + 2] = in.Sf[3 * g + 2];
+        magSf[f] = in.magSf[g];
+        if (f < nInt) {
+            neigh[f] = perm[in.neigh[g]];
+            w[f] = in.w[g];
+            dc[f] = in.dc[g];
+            if (in.corr) { corr[3 * f] = in.corr[3 * g]; corr[3 * f + 1] = in.corr[3 * g + 1]; corr[3 * f + 2] = in.corr[3 * g + 2]; }
+        }
+    }
+}
+// out[dim*perm[c] + d] = in[dim*c + d]   (caller's order -> internal order)
+__global__ void permute_cells_kernel(const double* __restrict__ in, const int* __restrict__ perm, long long n, int dim,
+                                     double* __restrict__ out)
+{
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n * dim; i += (long long)gridDim.x * blockDim.x) {
+        const long long c = i / dim;
+        out[(long long)perm[c] * dim + (i - c * dim)] = in[i];
+    }
+}
+// out[dim*c + d] = in[dim*perm[c] + d]   (internal order -> caller's order)
+__global__ void unpermute_cells_kernel(const double* __restrict__ in, const int* __restrict__ perm, long long n, int dim,
+                                       double* __restrict__ out)
+{
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n * dim; i += (long long)gridDim.x * blockDim.x) {
+        const long long c = i / dim;
+        out[i] = in[(long long)perm[c] * dim + (i - c * dim)];
+    }
+}
+// face field back to the caller's face order
+__global__ void unpermute_faces_kernel(const double* __restrict__ in, const int* __restrict__ fperm, long long nInt, long long nF,
+                                       double* __restrict__ out)
+{
+    for (long long f = blockIdx.x * (long long)blockDim.x + threadIdx.x; f < nF; f += (long long)gridDim.x * blockDim.x)
+        out[(f < nInt) ? fperm[f] : f] = in[f];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -520,25 +582,24 @@ struct StageTimer {
     }
 };
 
-static int build_csr(ithaca_b200* h, ProjState* s)
+static int build_csr(ithaca_b200* h, ProjState* s, const int* owner, const int* neigh, DevBuf& off, DevBuf& ent, DevBuf& other)
 {
     const long long nC = s->nCells, nF = s->nInt + s->nBnd, nnz = 2 * s->nInt + s->nBnd, n1 = nC + 1;
     int rc;
     if ((rc = ensure(h, s->cnt, n1 * sizeof(int)))) return rc;
-    if ((rc = ensure(h, s->off, n1 * sizeof(int)))) return rc;
-    if ((rc = ensure(h, s->ent, std::max<long long>(nnz, 1) * sizeof(int)))) return rc;
-    if ((rc = ensure(h, s->other, std::max<long long>(nnz, 1) * sizeof(int)))) return rc;
+    if ((rc = ensure(h, off, n1 * sizeof(int)))) return rc;
+    if ((rc = ensure(h, ent, std::max<long long>(nnz, 1) * sizeof(int)))) return rc;
+    if ((rc = ensure(h, other, std::max<long long>(nnz, 1) * sizeof(int)))) return rc;
     const int nb = (int)((n1 + SCAN_B - 1) / SCAN_B);
     if ((rc = ensure(h, s->blocksum, (size_t)nb * sizeof(int)))) return rc;
     IB_CUDA(h, cudaMemsetAsync(s->cnt.p, 0, n1 * sizeof(int), h->stream));
     const int fg = (int)std::min<long long>((nF + 255) / 256, 64LL * h->num_sms);
-    csr_count_kernel<<<std::max(fg, 1), 256, 0, h->stream>>>(s->owner.as<int>(), s->neigh.as<int>(), s->nInt, nF, s->cnt.as<int>());
-    scan_block_kernel<<<nb, SCAN_B, 0, h->stream>>>(s->cnt.as<int>(), n1, s->off.as<int>(), s->blocksum.as<int>());
+    csr_count_kernel<<<std::max(fg, 1), 256, 0, h->stream>>>(owner, neigh, s->nInt, nF, s->cnt.as<int>());
+    scan_block_kernel<<<nb, SCAN_B, 0, h->stream>>>(s->cnt.as<int>(), n1, off.as<int>(), s->blocksum.as<int>());
     scan_sums_kernel<<<1, SCAN_B, 0, h->stream>>>(s->blocksum.as<int>(), nb);
-    scan_add_kernel<<<(unsigned)((n1 + 255) / 256), 256, 0, h->stream>>>(s->off.as<int>(), s->blocksum.as<int>(), n1, s->cnt.as<int>(), 0);
-    csr_fill_kernel<<<std::max(fg, 1), 256, 0, h->stream>>>(s->owner.as<int>(), s->neigh.as<int>(), s->nInt, nF, s->cnt.as<int>(),
-                                                            s->ent.as<int>(), s->other.as<int>());
-    csr_sort_kernel<<<(unsigned)((nC + 255) / 256), 256, 0, h->stream>>>(s->off.as<int>(), nC, s->ent.as<int>(), s->other.as<int>());
+    scan_add_kernel<<<(unsigned)((n1 + 255) / 256), 256, 0, h->stream>>>(off.as<int>(), s->blocksum.as<int>(), n1, s->cnt.as<int>(), 0);
+    csr_fill_kernel<<<std::max(fg, 1), 256, 0, h->stream>>>(owner, neigh, s->nInt, nF, s->cnt.as<int>(), ent.as<int>(), other.as<int>());
+    csr_sort_kernel<<<(unsigned)((nC + 255) / 256), 256, 0, h->stream>>>(off.as<int>(), nC, ent.as<int>(), other.as<int>());
     IB_CUDA(h, cudaGetLastError());
     h->launches += 6;
     return IB200_OK;
@@ -619,21 +680,76 @@ int ithaca_b200_mesh_upload(ithaca_b200_t* h, int64_t nCells, int64_t nIntFaces,
     s->nCells = nCells; s->nInt = nIntFaces; s->nBnd = nBndFaces;
     const long long nF = nIntFaces + nBndFaces;
     int rc;
-    if ((rc = upload(h, s->owner, owner, nF * sizeof(int)))) return rc;
-    if ((rc = upload(h, s->neigh, neighbour, nIntFaces * sizeof(int)))) return rc;
-    if ((rc = upload(h, s->Sf, Sf, 3 * nF * sizeof(double)))) return rc;
-    if ((rc = upload(h, s->magSf, magSf, nF * sizeof(double)))) return rc;
-    if ((rc = upload(h, s->w, weights, nIntFaces * sizeof(double)))) return rc;
-    if ((rc = upload(h, s->dc, nonOrthDeltaCoeffs, nIntFaces * sizeof(double)))) return rc;
-    if ((rc = upload(h, s->dcB, bndDeltaCoeffs, nBndFaces * sizeof(double)))) return rc;
+    // the caller's arrays: addressing is kept (mesh_addressing), geometry only until the renumbered copy is made
+    DevBuf Sf0, magSf0, w0, dc0, corr0, V0;
+    auto drop = [&]() { for (DevBuf* b : {&Sf0, &magSf0, &w0, &dc0, &corr0, &V0}) if (b->p) { cudaFree(b->p); b->p = nullptr; } };
     s->corrected = nonOrthCorrVec != nullptr;
-    if (s->corrected && (rc = upload(h, s->corr, nonOrthCorrVec, 3 * nIntFaces * sizeof(double)))) return rc;
-    if ((rc = upload(h, s->V, V, nCells * sizeof(double)))) return rc;
-    if ((rc = ensure(h, s->bmask, std::max<long long>(nBndFaces, 16)))) return rc;
+    s->have_csr0 = false;
+    if ((rc = upload(h, s->owner0, owner, nF * sizeof(int))) || (rc = upload(h, s->neigh0, neighbour, nIntFaces * sizeof(int))) ||
+        (rc = upload(h, Sf0, Sf, 3 * nF * sizeof(double))) || (rc = upload(h, magSf0, magSf, nF * sizeof(double))) ||
+        (rc = upload(h, w0, weights, nIntFaces * sizeof(double))) || (rc = upload(h, dc0, nonOrthDeltaCoeffs, nIntFaces * sizeof(double))) ||
+        (s->corrected && (rc = upload(h, corr0, nonOrthCorrVec, 3 * nIntFaces * sizeof(double)))) ||
+        (rc = upload(h, V0, V, nCells * sizeof(double))) || (rc = upload(h, s->dcB, bndDeltaCoeffs, nBndFaces * sizeof(double)))) {
+        drop();
+        return rc;
+    }
+    if ((rc = ensure(h, s->bmask, std::max<long long>(nBndFaces, 16)))) { drop(); return rc; }
     if (bndMask) IB_CUDA(h, cudaMemcpyAsync(s->bmask.p, bndMask, nBndFaces, cudaMemcpyDefault, h->stream));
     else IB_CUDA(h, cudaMemsetAsync(s->bmask.p, 1, std::max<long long>(nBndFaces, 16), h->stream));
-    if ((rc = build_csr(h, s))) return rc;
-    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+
+    // locality renumbering on the host (renumber.cu); ITHACA_B200_NO_RENUMBER=1 keeps the caller's labels
+    std::vector<int> old2new, fnew2old;
+    {
+        std::vector<int> ho((size_t)nIntFaces), hn((size_t)nIntFaces);
+        IB_CUDA(h, cudaMemcpyAsync(ho.data(), s->owner0.p, nIntFaces * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        IB_CUDA(h, cudaMemcpyAsync(hn.data(), s->neigh0.p, nIntFaces * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        IB_CUDA(h, cudaStreamSynchronize(h->stream));
+        bool bad = false;
+        for (long long f = 0; f < nIntFaces && !bad; f++)
+            bad = ho[f] < 0 || ho[f] >= nCells || hn[f] < 0 || hn[f] >= nCells;
+        if (bad) { drop(); set_error(h, "mesh_upload: owner/neighbour label out of range"); return IB200_ERR_ARG; }
+        const char* off_env = getenv("ITHACA_B200_NO_RENUMBER");
+        if (off_env && *off_env == '1') {
+            old2new.resize((size_t)nCells);
+            fnew2old.resize((size_t)nIntFaces);
+            for (long long c = 0; c < nCells; c++) old2new[c] = (int)c;
+            for (long long f = 0; f < nIntFaces; f++) fnew2old[f] = (int)f;
+        } else {
+            mesh_renumber(nCells, nIntFaces, ho.data(), hn.data(), old2new, fnew2old);
+        }
+    }
+    if ((rc = upload(h, s->perm, old2new.data(), nCells * sizeof(int))) ||
+        (rc = upload(h, s->fperm, fnew2old.data(), nIntFaces * sizeof(int))) ||
+        (rc = ensure(h, s->owner, nF * sizeof(int))) || (rc = ensure(h, s->neigh, std::max<long long>(nIntFaces, 4) * sizeof(int))) ||
+        (rc = ensure(h, s->Sf, 3 * nF * sizeof(double))) || (rc = ensure(h, s->magSf, nF * sizeof(double))) ||
+        (rc = ensure(h, s->w, std::max<long long>(nIntFaces, 2) * sizeof(double))) ||
+        (rc = ensure(h, s->dc, std::max<long long>(nIntFaces, 2) * sizeof(double))) ||
+        (s->corrected && (rc = ensure(h, s->corr, 3 * std::max<long long>(nIntFaces, 1) * sizeof(double)))) ||
+        (rc = ensure(h, s->V, nCells * sizeof(double))) ||
+        (rc = ensure(h, s->stage, (size_t)std::max<long long>(3 * nCells, nF) * sizeof(double)))) {
+        drop();
+        return rc;
+    }
+    {
+        MeshSrc src;
+        src.owner = s->owner0.as<int>(); src.neigh = s->neigh0.as<int>();
+        src.Sf = Sf0.as<double>(); src.magSf = magSf0.as<double>(); src.w = w0.as<double>(); src.dc = dc0.as<double>();
+        src.corr = s->corrected ? corr0.as<double>() : nullptr;
+        const int fg = (int)std::min<long long>((nF + 255) / 256, 64LL * h->num_sms);
+        permute_faces_kernel<<<std::max(fg, 1), 256, 0, h->stream>>>(src, s->perm.as<int>(), s->fperm.as<int>(), nIntFaces, nF,
+                                                                     s->owner.as<int>(), s->neigh.as<int>(), s->Sf.as<double>(),
+                                                                     s->magSf.as<double>(), s->w.as<double>(), s->dc.as<double>(),
+                                                                     s->corrected ? s->corr.as<double>() : nullptr);
+        const int cg = (int)std::min<long long>((nCells + 255) / 256, 64LL * h->num_sms);
+        permute_cells_kernel<<<std::max(cg, 1), 256, 0, h->stream>>>(V0.as<double>(), s->perm.as<int>(), nCells, 1, s->V.as<double>());
+        h->launches += 2;
+    }
+    rc = build_csr(h, s, s->owner.as<int>(), s->neigh.as<int>(), s->off, s->ent, s->other);
+    cudaError_t e = cudaStreamSynchronize(h->stream);
+    drop();
+    if (rc) return rc;
+    IB_CUDA(h, e);
+    IB_CUDA(h, cudaGetLastError());
     s->have_mesh = true;
     s->nU = s->nP = 0;
     return IB200_OK;
@@ -646,10 +762,15 @@ int ithaca_b200_mesh_addressing(ithaca_b200_t* h, int32_t* off, int32_t* ent, in
     PROJ_REQUIRE(s && s->have_mesh, "mesh_addressing: call mesh_upload first");
     cudaSetDevice(h->device);
     const long long n1 = s->nCells + 1, nnz = 2 * s->nInt + s->nBnd;
+    if (!s->have_csr0) {   // addressing of the caller's own arrays (the kernels run on the renumbered copy)
+        int rc = build_csr(h, s, s->owner0.as<int>(), s->neigh0.as<int>(), s->off0, s->ent0, s->other0);
+        if (rc) return rc;
+        s->have_csr0 = true;
+    }
     std::vector<int> o(n1), e(nnz), t(nnz);
-    IB_CUDA(h, cudaMemcpyAsync(o.data(), s->off.p, n1 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-    IB_CUDA(h, cudaMemcpyAsync(e.data(), s->ent.p, nnz * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-    IB_CUDA(h, cudaMemcpyAsync(t.data(), s->other.p, nnz * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaMemcpyAsync(o.data(), s->off0.p, n1 * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaMemcpyAsync(e.data(), s->ent0.p, nnz * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaMemcpyAsync(t.data(), s->other0.p, nnz * sizeof(int), cudaMemcpyDeviceToHost, h->stream));
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
     if (off) memcpy(off, o.data(), n1 * sizeof(int));
     if (ent) memcpy(ent, e.data(), nnz * sizeof(int));
@@ -682,8 +803,10 @@ int ithaca_b200_basis_upload(ithaca_b200_t* h, int which, const double* const* i
     if ((rc = ensure(h, Bd, (size_t)n * ldb * sizeof(double)))) return rc;
     for (int j = 0; j < n; j++) {
         PROJ_REQUIRE(int_ptrs[j] && (s->nBnd == 0 || bnd_ptrs[j]), "basis_upload: null field pointer");
-        IB_CUDA(h, cudaMemcpyAsync(I.as<double>() + (size_t)j * ld, int_ptrs[j], (size_t)dim * s->nCells * sizeof(double),
-                                   cudaMemcpyDefault, h->stream));
+        IB_CUDA(h, cudaMemcpyAsync(s->stage.p, int_ptrs[j], (size_t)dim * s->nCells * sizeof(double), cudaMemcpyDefault, h->stream));
+        permute_cells_kernel<<<(unsigned)std::min<long long>((dim * s->nCells + 255) / 256, 64LL * h->num_sms), 256, 0, h->stream>>>(
+            s->stage.as<double>(), s->perm.as<int>(), s->nCells, dim, I.as<double>() + (size_t)j * ld);
+        h->launches += 1;
         if (s->nBnd)
             IB_CUDA(h, cudaMemcpyAsync(Bd.as<double>() + (size_t)j * ldb, bnd_ptrs[j], (size_t)dim * s->nBnd * sizeof(double),
                                        cudaMemcpyDefault, h->stream));
@@ -708,12 +831,14 @@ int ithaca_b200_fvc_eval(ithaca_b200_t* h, int op, int j, int k, double* out)
     const MeshDev m = mesh_dev(s);
     int rc;
     size_t nout = 0;
+    auto ug = [&](size_t n) { return (unsigned)std::min<size_t>((n + 255) / 256, 64 * (size_t)h->num_sms); };
     switch (op) {
     case IB200_FVC_FLUX: {
         PROJ_REQUIRE(j >= 0 && j < s->nU, "fvc_eval: field index out of range");
         if ((rc = need_flux(h, s))) return rc;
         nout = (size_t)(s->nInt + s->nBnd);
-        IB_CUDA(h, cudaMemcpyAsync(out, s->flux.as<double>() + (size_t)j * s->ldF, nout * sizeof(double), cudaMemcpyDefault, h->stream));
+        unpermute_faces_kernel<<<ug(nout), 256, 0, h->stream>>>(s->flux.as<double>() + (size_t)j * s->ldF, s->fperm.as<int>(), s->nInt,
+                                                                 s->nInt + s->nBnd, s->stage.as<double>());
         break;
     }
     case IB200_FVC_DIV_PHI: {
@@ -725,7 +850,8 @@ int ithaca_b200_fvc_eval(ithaca_b200_t* h, int op, int j, int k, double* out)
             s->work.as<double>(), s->ldU);
         h->launches += 1;
         nout = (size_t)3 * s->nCells;
-        IB_CUDA(h, cudaMemcpyAsync(out, s->work.as<double>() + (size_t)k * s->ldU, nout * sizeof(double), cudaMemcpyDefault, h->stream));
+        unpermute_cells_kernel<<<ug(nout), 256, 0, h->stream>>>(s->work.as<double>() + (size_t)k * s->ldU, s->perm.as<int>(), s->nCells, 3,
+                                                                 s->stage.as<double>());
         break;
     }
     case IB200_FVC_LAPLACIAN: {
@@ -733,7 +859,8 @@ int ithaca_b200_fvc_eval(ithaca_b200_t* h, int op, int j, int k, double* out)
         if ((rc = ensure(h, s->work, (size_t)s->nU * s->ldU * sizeof(double)))) return rc;
         if ((rc = run_laplacians(h, s, s->work.as<double>()))) return rc;
         nout = (size_t)3 * s->nCells;
-        IB_CUDA(h, cudaMemcpyAsync(out, s->work.as<double>() + (size_t)j * s->ldU, nout * sizeof(double), cudaMemcpyDefault, h->stream));
+        unpermute_cells_kernel<<<ug(nout), 256, 0, h->stream>>>(s->work.as<double>() + (size_t)j * s->ldU, s->perm.as<int>(), s->nCells, 3,
+                                                                 s->stage.as<double>());
         break;
     }
     case IB200_FVC_GRAD_P: {
@@ -744,7 +871,8 @@ int ithaca_b200_fvc_eval(ithaca_b200_t* h, int op, int j, int k, double* out)
                                                                                       s->ldPb, s->nP, s->work.as<double>(), ldo);
         h->launches += 1;
         nout = (size_t)3 * s->nCells;
-        IB_CUDA(h, cudaMemcpyAsync(out, s->work.as<double>() + (size_t)j * ldo, nout * sizeof(double), cudaMemcpyDefault, h->stream));
+        unpermute_cells_kernel<<<ug(nout), 256, 0, h->stream>>>(s->work.as<double>() + (size_t)j * ldo, s->perm.as<int>(), s->nCells, 3,
+                                                                 s->stage.as<double>());
         break;
     }
     case IB200_FVC_DIV_U: {
@@ -756,13 +884,17 @@ int ithaca_b200_fvc_eval(ithaca_b200_t* h, int op, int j, int k, double* out)
                                                                                             s->work.as<double>(), ldo);
         h->launches += 1;
         nout = (size_t)s->nCells;
-        IB_CUDA(h, cudaMemcpyAsync(out, s->work.as<double>() + (size_t)j * ldo, nout * sizeof(double), cudaMemcpyDefault, h->stream));
+        unpermute_cells_kernel<<<ug(nout), 256, 0, h->stream>>>(s->work.as<double>() + (size_t)j * ldo, s->perm.as<int>(), s->nCells, 1,
+                                                                 s->stage.as<double>());
         break;
     }
     default:
         PROJ_REQUIRE(false, "fvc_eval: unknown operator");
     }
     IB_CUDA(h, cudaGetLastError());
+    h->launches += 1;
+    // the field was gathered back to the caller's cell / face order into the staging buffer
+    IB_CUDA(h, cudaMemcpyAsync(out, s->stage.p, nout * sizeof(double), cudaMemcpyDefault, h->stream));
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
     return IB200_OK;
 }
