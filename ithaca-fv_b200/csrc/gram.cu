@@ -11,17 +11,16 @@
 // Data path: operands are column-contiguous ([cols][ld] doubles, K contiguous = OpenFOAM's own field storage), so both
 // MMA operands are K-contiguous. A TMA box is {16 cells (128 B) x 40 columns}, written with the 128-B swizzle;
 // fragments are read with a K permutation that makes every LDS.64 bank-conflict free. The 16 cell weights of a stage
-// arrive with a bulk copy from a dim-times repeated copy of V (built once per volume vector). 16 MMA warps (4 per SM
-// sub-partition) each own one <= 5x5-fragment output tile in registers; the tile shape is a template parameter
+// arrive with a bulk copy from a dim-times repeated copy of V (built once per volume vector). 15 MMA warps (4,4,4,3 per
+// SM sub-partition) each own one <= 5x5-fragment output tile in registers; the tile shape is a template parameter
 // (rectangular NR x NC, or rows [I0, I0+NR) of a lower-triangular diagonal tile), so the inner loop carries no masks.
-// Refilling the TMA/mbarrier ring is a rotating duty of one lane (warp it % 16 refills the slot released one
-// iteration earlier), so no warp and no registers are set aside for a producer.
+// One lane of a 16th warp keeps the TMA/mbarrier ring full.
 //
-// Schedule (host): the output is cut into 5x5-fragment tiles; tiles are packed into jobs of <= 16 tiles sharing <= 10
-// boxes (4x4 super-tiles off the diagonal, triangles on it), heavy tiles are split by fragment rows when warps are
-// spare, and tiles go to warps so that the four sub-partitions carry equal DMMA counts. The K range of all jobs is
-// then laid end to end, weighted by each job's critical-path cost, and cut into one equal share per SM (stream-K): a
-// CTA runs one to a few (job, K slab) segments back to back through the same pipeline.
+// Schedule (host): the output is cut into 5x5-fragment tiles; tiles are packed into jobs of <= 15 tiles sharing <= 10
+// boxes (4x3 / 3x4 super-tiles off the diagonal, triangles on it, the whole triangle for m <= 200), heavy tiles are
+// split by fragment rows when warps are spare, and tiles go to warps so that the four sub-partitions carry equal DMMA
+// counts. The K range of all jobs is then laid end to end, weighted by each job's measured stage time, and cut into
+// one equal share per SM (stream-K): a CTA runs one to a few (job, K slab) segments back to back through one ring.
 #include "../../include/ithaca_b200.h"
 #include "common.cuh"
 #include <algorithm>
