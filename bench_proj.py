@@ -111,6 +111,10 @@ def run(pod, torch, dev, which="c4", N=50, Np=10, reps=2, hbm_peak=6540.0, dmma_
     fused["face_records_frac_hbm_measured"] = fused["face_records_GBps"] / hbm_peak
     fused["contraction_frac_dmma"] = fused["contraction_TFLOPs"] / dmma_peak
     total_ms = sum(res[o]["wall_ms"] for o in res if o != "Cmat")
+    prod = [stages[k] for k in ("flux", "laplacian", "grad_p", "div_u")]
+    agg_bytes = sum(x["bytes"] for x in prod) + rec_bytes
+    agg_ms = sum(x["ms"] for x in prod) + tF["face_records"]
+    agg_gbps = agg_bytes / (agg_ms * 1e-3) / 1e9
     out = {
         "workload": "C4 projection: N=%d U basis functions (+%d p modes), %d-cell unstructured cylinder O-grid "
                     "(%d internal / %d boundary faces), Gauss linear + corrected laplacian" % (N, Np, nC, nI, nB),
@@ -119,8 +123,11 @@ def run(pod, torch, dev, which="c4", N=50, Np=10, reps=2, hbm_peak=6540.0, dmma_
         "time_all_operators_ms": total_ms,
         "per_operator_ms": {o: res[o]["wall_ms"] for o in res},
         "fused_C": fused, "stages": stages, "materialised_contraction": contraction,
-        "projection_GBps": stages["div_phi"]["GBps"], "projection_frac_hbm_measured": stages["div_phi"]["frac_hbm_measured"],
-        "projection_frac_hbm_8TBps": stages["div_phi"]["frac_hbm_8TBps"],
+        "projection_GBps": agg_gbps, "projection_frac_hbm_measured": agg_gbps / hbm_peak,
+        "projection_frac_hbm_8TBps": agg_gbps / 8000.0,
+        "projection_GBps_definition": "product path (M,B,K,P + fused C): algorithmic bytes of flux + laplacian + grad_p + div_u + "
+                                      "per-face records, divided by the summed device time of those gather stages; the materialised "
+                                      "div(phi,U) stage (cross-check path) is reported separately under stages.div_phi",
         "gpu_launches": int(launches), "host_mesh_generation_s": t_mesh, "mesh_upload_csr_s": t_upload,
     }
     if check:  # size-independent properties (the oracle parity proper is tests/test_proj_gpu.py)

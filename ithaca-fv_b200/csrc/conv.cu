@@ -16,11 +16,12 @@
 #include "../../include/ithaca_b200.h"
 #include "common.cuh"
 #include <algorithm>
+#include <cstdlib>
 #include <vector>
 
 namespace ib200 {
 
-constexpr int CV_KT = 16;      // faces per pipeline stage (4 DMMA k-steps)
+constexpr int CV_KTMAX = 32;   // faces per pipeline stage: template parameter KT = 16 or 32 (4 / 8 DMMA k-steps)
 constexpr int CV_ROWS = 240;   // output rows (k,i) per CTA
 constexpr int CV_KC = 7;       // distinct k per CTA: the b box is 4*CV_KC doubles per face (pitch 28 = 12 mod 16)
 constexpr int CV_WARPS = 15;   // MMA warps, two row fragments (16 rows) each; + 1 producer warp = 512 threads
@@ -101,13 +102,43 @@ conv_face_prep_kernel(ConvMesh m, const double* __restrict__ Ucm, const double* 
 struct ConvChunk { int r_lo, r_hi, k_lo, pad; };  // output rows [r_lo, r_hi) of the flattened (k,i) index, first k
 
 // grid: blockIdx.x = chunk + nchunks * (jblk + njblk * slab). Stage layout in smem: [A: KT x NP][B: KT x bp][D: KT x 3NP].
+// DMMA without `volatile` (see gram.cu)
+__device__ __forceinline__ void conv_dmma(double& c0, double& c1, double a, double b)
+{
+    asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+// one pipeline stage of one MMA warp with NR active row fragments: E = b_k . d_i in registers, 7 DMMAs per fragment row
+template <int KT, int NR>
+__device__ __forceinline__ void conv_stage(double (&acc)[2][CV_JF][2], const double* As, const double* Bs, const double* Ds, int NP,
+                                           int bp, int j0g, int t, const int (&boff)[2], const int (&doff)[2])
+{
+#pragma unroll
+    for (int ks = 0; ks < KT / 4; ks++) {
+        const int fa = 4 * ks + t;
+        const double* ap = As + fa * NP + j0g;
+        double bj[CV_JF];
+#pragma unroll
+        for (int jf = 0; jf < CV_JF; jf++) bj[jf] = ap[8 * jf];
+#pragma unroll
+        for (int r = 0; r < NR; r++) {
+            const double* bq = Bs + fa * bp + boff[r];
+            const double* dq = Ds + fa * 3 * NP + doff[r];
+            const double e = bq[0] * dq[0] + bq[1] * dq[NP] + bq[2] * dq[2 * NP];
+#pragma unroll
+            for (int jf = 0; jf < CV_JF; jf++) conv_dmma(acc[r][jf][0], acc[r][jf][1], e, bj[jf]);
+        }
+    }
+}
+
+template <int KT>
 __global__ void __launch_bounds__(CV_THREADS, 1)
 conv_contract_kernel(const __grid_constant__ CUtensorMap tmB, const double* __restrict__ Aj, const double* __restrict__ Dd,
                      const ConvChunk* __restrict__ chunks, int nchunks, int njblk, int N, int NP, int bp, int Jpad,
                      long long tiles_per_slab, long long ntiles, int nstages, double* __restrict__ ws)
 {
     extern __shared__ __align__(1024) unsigned char smem[];
-    const int a_bytes = CV_KT * NP * 8, b_bytes = CV_KT * bp * 8, d_bytes = CV_KT * 3 * NP * 8;
+    const int a_bytes = KT * NP * 8, b_bytes = KT * bp * 8, d_bytes = KT * 3 * NP * 8;
     const int stage_bytes = a_bytes + b_bytes + d_bytes;
     uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)nstages * stage_bytes);
     uint64_t* empty = full + nstages;
@@ -134,7 +165,7 @@ conv_contract_kernel(const __grid_constant__ CUtensorMap tmB, const double* __re
             for (int it = 0; it < niter; it++) {
                 const int s = it % nstages;
                 if (it >= nstages) mbar_wait(&empty[s], ((it / nstages) - 1) & 1);
-                const long long f0 = (t_begin + it) * CV_KT;
+                const long long f0 = (t_begin + it) * KT;
                 unsigned char* dst = smem + (size_t)s * stage_bytes;
                 mbar_arrive_expect_tx(&full[s], (uint32_t)stage_bytes);
                 bulk_load_1d(dst, Aj + (size_t)f0 * NP, (uint32_t)a_bytes, &full[s]);
@@ -159,6 +190,7 @@ conv_contract_kernel(const __grid_constant__ CUtensorMap tmB, const double* __re
         doff[r] = i;
     }
     const int j0 = jblk * (8 * CV_JF);
+    const int nact = (act[0] ? 1 : 0) + (act[1] ? 1 : 0);   // warp-uniform; act[1] implies act[0]
     double acc[2][CV_JF][2];
 #pragma unroll
     for (int r = 0; r < 2; r++)
@@ -169,27 +201,10 @@ conv_contract_kernel(const __grid_constant__ CUtensorMap tmB, const double* __re
         const int s = it % nstages;
         mbar_wait(&full[s], (it / nstages) & 1);
         const double* As = reinterpret_cast<const double*>(smem + (size_t)s * stage_bytes);
-        const double* Bs = As + CV_KT * NP;
-        const double* Ds = Bs + CV_KT * bp;
-        if (act[0]) {
-#pragma unroll
-            for (int ks = 0; ks < CV_KT / 4; ks++) {
-                const int fa = 4 * ks + t;
-                const double* ap = As + fa * NP + j0 + g;
-                double bj[CV_JF];
-#pragma unroll
-                for (int jf = 0; jf < CV_JF; jf++) bj[jf] = ap[8 * jf];
-#pragma unroll
-                for (int r = 0; r < 2; r++) {
-                    if (r == 1 && !act[1]) break;
-                    const double* bq = Bs + fa * bp + boff[r];
-                    const double* dq = Ds + fa * 3 * NP + doff[r];
-                    const double e = bq[0] * dq[0] + bq[1] * dq[NP] + bq[2] * dq[2 * NP];
-#pragma unroll
-                    for (int jf = 0; jf < CV_JF; jf++) dmma884(acc[r][jf][0], acc[r][jf][1], e, bj[jf]);
-                }
-            }
-        }
+        const double* Bs = As + KT * NP;
+        const double* Ds = Bs + KT * bp;
+        if (nact == 2) conv_stage<KT, 2>(acc, As, Bs, Ds, NP, bp, j0 + g, t, boff, doff);
+        else if (nact == 1) conv_stage<KT, 1>(acc, As, Bs, Ds, NP, bp, j0 + g, t, boff, doff);
         __syncwarp();
         if (lane == 0) mbar_arrive(&empty[s]);
     }
@@ -230,6 +245,8 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
 {
     const int NP = (N + 3) / 8 * 8 + 4;  // smallest NP >= N with NP = 4 (mod 8): conflict-free smem pitches
     const long long nF = m.nInt + m.nBnd;
+    int CV_KT = 32;   // faces per stage (ITHACA_B200_CONV_KT=16 selects the shorter stage)
+    if (const char* e = getenv("ITHACA_B200_CONV_KT")) CV_KT = (atoi(e) == 16) ? 16 : 32;
     const long long ntiles = (nF + CV_KT - 1) / CV_KT, nFpad = ntiles * CV_KT;
     const int Jpad = (N + 7) / 8 * 8;
     const int njblk = (Jpad + 8 * CV_JF - 1) / (8 * CV_JF);
@@ -281,8 +298,9 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
     int nstages = std::min(8, (226 * 1024 - 256) / (stage_bytes + 16));
     if (nstages < 2) { set_error(h, "project(C): too many modes for one pipeline stage"); return IB200_ERR_ARG; }
     const size_t smem = (size_t)nstages * (stage_bytes + 16) + 64;
-    IB_CUDA(h, cudaFuncSetAttribute(conv_contract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    conv_contract_kernel<<<nchunks * njblk * nslabs, CV_THREADS, smem, h->stream>>>(
+    auto kern = (CV_KT == 16) ? conv_contract_kernel<16> : conv_contract_kernel<32>;
+    IB_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<nchunks * njblk * nslabs, CV_THREADS, smem, h->stream>>>(
         tmB, cb->Aj.as<double>(), cb->Dd.as<double>(), cb->chunks.as<ConvChunk>(), nchunks, njblk, N, NP, bp, Jpad, tps, ntiles,
         nstages, cb->ws.as<double>());
     IB_CUDA(h, cudaGetLastError());

@@ -22,6 +22,8 @@
 #include <cooperative_groups.h>
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
+#include <cstring>
 
 namespace cg = cooperative_groups;
 
@@ -37,13 +39,13 @@ __device__ __forceinline__ double warp_sum(double v)
     return v;
 }
 
-// X = lower(G) + sigma I, strict upper triangle = 0 (column-major m x m)
-__global__ void eig_init_kernel(const double* __restrict__ G, double* __restrict__ X, int m, double sigma)
+// X = lower(scale G) + sigma I, strict upper triangle = 0 (column-major m x m). scale is a power of two (exact).
+__global__ void eig_init_kernel(const double* __restrict__ G, double* __restrict__ X, int m, double sigma, double scale)
 {
     const size_t mm = (size_t)m * m;
     for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < mm; idx += (size_t)gridDim.x * blockDim.x) {
         const int i = (int)(idx % m), j = (int)(idx / m);
-        X[idx] = (i > j) ? G[idx] : (i == j ? G[idx] + sigma : 0.0);
+        X[idx] = (i > j) ? scale * G[idx] : (i == j ? scale * G[idx] + sigma : 0.0);
     }
 }
 
@@ -242,8 +244,155 @@ __global__ void eig_jacobi_block_kernel(double* X, int m, int b, int nb, double 
     if (blockIdx.x == 0 && threadIdx.x == 0) flags[EIG_MAX_SWEEPS] = sweep;
 }
 
-// lambda_i = |x_i|^2 - sigma, u_i = x_i / |x_i| (in place). One warp per column.
-__global__ void eig_finalize_kernel(double* __restrict__ X, int m, double sigma, double* __restrict__ lam)
+// ---- register-resident variant for m <= 32*NE <= 1024 -------------------------------------------------------------
+// Same ordering as eig_jacobi_block_kernel, but in a block pair (I, J) warp i keeps column i of block I in REGISTERS for
+// all b inner rounds (it meets columns i, i+1, ... of block J in turn), only block J lives in shared memory (padded to
+// 32*NE doubles per column, so the hot loop has no bounds checks), and the squared norms travel with the columns and
+// are updated by the rotation (|x'|^2 = a - t c, |y'|^2 = b + t c; recomputed from scratch at every block-pair visit),
+// so a rotation costs ONE warp reduction (the dot product) instead of three.
+template <int NE>
+__global__ void __launch_bounds__(NE > 16 ? 320 : 512, 1) eig_jacobi_reg_kernel(double* X, int m, int b, int nb, double tol, int* flags)
+{
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ double sx[];           // b columns of LDC doubles | b squared norms
+    constexpr int LDC = 32 * NE;
+    double* nrm = sx + (size_t)b * LDC;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nbp = (nb + 1) & ~1;
+    const int npairs = nbp / 2;
+    auto ncols = [&](int blk) { return min(b, m - blk * b); };
+    // block `blk` -> shared memory (zero padded), squared norms by the owning warps
+    auto load_block = [&](int blk, int nc) {
+        const double* g = X + (size_t)blk * b * m;
+        for (int c = warp; c < b; c += (blockDim.x >> 5)) {
+            double s2 = 0.0;
+#pragma unroll
+            for (int e = 0; e < NE; e++) {
+                const int k = lane + 32 * e;
+                const double v = (c < nc && k < m) ? g[(size_t)c * m + k] : 0.0;
+                sx[(size_t)c * LDC + k] = v;
+                s2 += v * v;
+            }
+            s2 = warp_sum(s2);
+            if (lane == 0) nrm[c] = s2;
+        }
+    };
+    auto store_block = [&](int blk, int nc) {
+        double* g = X + (size_t)blk * b * m;
+        for (int c = warp; c < nc; c += (blockDim.x >> 5))
+#pragma unroll
+            for (int e = 0; e < NE; e++) {
+                const int k = lane + 32 * e;
+                if (k < m) g[(size_t)c * m + k] = sx[(size_t)c * LDC + k];
+            }
+    };
+
+    int sweep = 0;
+    for (; sweep < EIG_MAX_SWEEPS; sweep++) {
+        int rot = 0;
+        // ---- phase 0: pairs inside each block (tournament over the block's columns, in shared memory) ----
+        for (int blk = blockIdx.x; blk < nb; blk += gridDim.x) {
+            const int nc = ncols(blk);
+            load_block(blk, nc);
+            __syncthreads();
+            const int n = (nc + 1) & ~1;
+            for (int rd = 0; rd < n - 1; rd++) {
+                if (warp < n / 2) {
+                    int i, j;
+                    if (warp == 0) { i = n - 1; j = rd; }
+                    else { i = (rd + warp) % (n - 1); j = (rd - warp + (n - 1)) % (n - 1); }
+                    if (i < nc && j < nc) {
+                        if (i > j) { const int t = i; i = j; j = t; }
+                        rot += rotate_pair(sx + (size_t)i * LDC, sx + (size_t)j * LDC, m, lane, tol);
+                    }
+                }
+                __syncthreads();
+            }
+            store_block(blk, nc);
+            __syncthreads();
+        }
+        grid.sync();
+        // ---- block tournament ----
+        for (int rd = 0; rd < nbp - 1; rd++) {
+            for (int p = blockIdx.x; p < npairs; p += gridDim.x) {
+                int I, J;
+                if (p == 0) { I = nbp - 1; J = rd; }
+                else { I = (rd + p) % (nbp - 1); J = (rd - p + (nbp - 1)) % (nbp - 1); }
+                if (I >= nb || J >= nb) continue;  // dummy block (uniform over the CTA)
+                if (I > J) { const int t = I; I = J; J = t; }
+                const int ni = ncols(I), nj = ncols(J);
+                // my column of block I -> registers
+                double xr[NE];
+                double a = 0.0;
+                double* gi = X + ((size_t)I * b + warp) * m;
+                if (warp < ni) {
+#pragma unroll
+                    for (int e = 0; e < NE; e++) {
+                        const int k = lane + 32 * e;
+                        xr[e] = (k < m) ? gi[k] : 0.0;
+                        a += xr[e] * xr[e];
+                    }
+                    a = warp_sum(a);
+                } else {
+#pragma unroll
+                    for (int e = 0; e < NE; e++) xr[e] = 0.0;
+                }
+                load_block(J, nj);
+                __syncthreads();
+                for (int s = 0; s < b; s++) {
+                    const int j = (warp + s) % b;
+                    if (warp < ni && j < nj) {
+                        double* y = sx + (size_t)j * LDC + lane;
+                        double yr[NE];
+                        double c0 = 0.0, c1 = 0.0;
+#pragma unroll
+                        for (int e = 0; e < NE; e++) {
+                            yr[e] = y[32 * e];
+                            if (e & 1) c1 += xr[e] * yr[e]; else c0 += xr[e] * yr[e];
+                        }
+                        const double c = warp_sum(c0 + c1);
+                        const double bn = nrm[j];
+                        const double ab = a * bn;
+                        if (ab > 0.0 && c * c > tol * tol * ab) {
+                            // t = tan(theta) of the smaller rotation angle: 2c / (d + sign(d) sqrt(d^2 + 4c^2)), d = |y|^2 - |x|^2
+                            const double d = bn - a;
+                            const double tt = 2.0 * c / (d + copysign(sqrt(d * d + 4.0 * c * c), d));
+                            const double cs = rsqrt(1.0 + tt * tt);
+                            const double sn = cs * tt;
+#pragma unroll
+                            for (int e = 0; e < NE; e++) {
+                                const double xv = xr[e];
+                                xr[e] = cs * xv - sn * yr[e];
+                                y[32 * e] = sn * xv + cs * yr[e];
+                            }
+                            a -= tt * c;
+                            if (lane == 0) nrm[j] = bn + tt * c;
+                            rot++;
+                        }
+                    }
+                    __syncthreads();
+                }
+                if (warp < ni) {
+#pragma unroll
+                    for (int e = 0; e < NE; e++) {
+                        const int k = lane + 32 * e;
+                        if (k < m) gi[k] = xr[e];
+                    }
+                }
+                store_block(J, nj);
+                __syncthreads();
+            }
+            grid.sync();
+        }
+        if (lane == 0 && rot) atomicAdd(&flags[sweep], rot);
+        grid.sync();
+        if (*(volatile int*)&flags[sweep] == 0) { sweep++; break; }
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) flags[EIG_MAX_SWEEPS] = sweep;
+}
+
+// lambda_i = (|x_i|^2 - sigma) / scale, u_i = x_i / |x_i| (in place). One warp per column.
+__global__ void eig_finalize_kernel(double* __restrict__ X, int m, double sigma, double inv_scale, double* __restrict__ lam)
 {
     const int lane = threadIdx.x & 31;
     const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
@@ -254,7 +403,7 @@ __global__ void eig_finalize_kernel(double* __restrict__ X, int m, double sigma,
     s = warp_sum(s);
     const double inv = s > 0.0 ? 1.0 / sqrt(s) : 0.0;
     for (int k = lane; k < m; k += 32) x[k] *= inv;
-    if (lane == 0) lam[i] = s - sigma;
+    if (lane == 0) lam[i] = (s - sigma) * inv_scale;
 }
 
 // Descending rank sort (stable) + column permutation with a deterministic sign (largest |component| > 0).
@@ -346,7 +495,10 @@ int eig_launch(ithaca_b200* h, int* sweeps)
         return fail(IB200_ERR_CUDA);
     }
     h->launches += 1;
-    const double dmax = bounds[0], gersh = std::max(bounds[1], 0.0);
+    // power-of-two scaling to max |G_ii| in [1, 2): exact, and keeps the squared quantities of the rotation test in range
+    double scale = 1.0;
+    if (bounds[0] > 0.0 && std::isfinite(bounds[0])) { int ex = 0; std::frexp(bounds[0], &ex); scale = std::ldexp(1.0, 1 - ex); }
+    const double dmax = bounds[0] * scale, gersh = std::max(bounds[1], 0.0) * scale;
     const double tiny = 16.0 * m * eps * dmax;
     const double shifts[3] = {0.0, tiny, gersh * (1.0 + 1e-3) + tiny};
     const int ib = 256;
@@ -356,7 +508,7 @@ int eig_launch(ithaca_b200* h, int* sweeps)
     for (int attempt = 0; attempt < 3 && !ok; attempt++) {
         sigma = shifts[attempt];
         if (attempt > 0 && !(sigma > shifts[attempt - 1])) continue;
-        eig_init_kernel<<<ig, ib, 0, h->stream>>>(h->dG, h->dW, m, sigma);
+        eig_init_kernel<<<ig, ib, 0, h->stream>>>(h->dG, h->dW, m, sigma, scale);
         h->launches += 1;
         int rc = cholesky(h, h->dW, m, flags + 48, &ok);
         if (rc) return fail(rc);
@@ -366,27 +518,54 @@ int eig_launch(ithaca_b200* h, int* sweeps)
         return fail(IB200_ERR_NOCONV);
     }
 
-    // block size: 2b columns of m doubles must fit shared memory; one warp per pair of an inner round
-    int b = std::min({16, m, (int)((200 * 1024) / (16 * (size_t)m))});
-    if (b < 1) { set_error(h, "pod_eig: more than 12800 snapshots are not supported"); return fail(IB200_ERR_ARG); }
-    if (b < 2 && m >= 2) b = std::min(2, m);
-    const int nb = (m + b - 1) / b;
-    const int threads = std::max(64, 32 * b);
-    const size_t smem = (size_t)2 * b * m * sizeof(double);
-    if (smem > 227 * 1024) { set_error(h, "pod_eig: too many snapshots for the Jacobi block kernel"); return fail(IB200_ERR_ARG); }
-    IB_CUDA(h, cudaFuncSetAttribute(eig_jacobi_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int maxb = 0;
-    IB_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&maxb, eig_jacobi_block_kernel, threads, smem));
-    if (maxb < 1) { set_error(h, "pod_eig: Jacobi kernel does not fit one SM"); return fail(IB200_ERR_CUDA); }
-    const int want = std::max((nb + 1) / 2, 1);
-    const int nblocks = std::max(1, std::min(want, maxb * h->num_sms));
     IB_CUDA(h, cudaMemsetAsync(flags, 0, 48 * sizeof(int), h->stream));
     double tol = std::sqrt((double)m) * eps;
     double* X = h->dW;
+    const char* ev = getenv("ITHACA_B200_EIG");       // "block" selects the shared-memory kernel (A/B measurements)
+    const char* evb = getenv("ITHACA_B200_EIG_B");    // columns per block (tuning)
+    const bool use_reg = m <= 1024 && !(ev && strcmp(ev, "block") == 0);
+    int b, threads;
+    size_t smem;
+    void* kern = nullptr;
+    if (use_reg) {
+        // register-resident kernel: one block of b padded columns (+ b squared norms) in shared memory
+        int NE = 2;
+        while (32 * NE < m) NE *= 2;
+        const int bmax = NE > 16 ? 10 : 16;
+        b = std::min(8, m);   // measured (scripts/eig_bench.py): b = 8 beats 4, 12, 16 at m = 200 and m = 1000
+        if (evb) b = std::max(2, std::min({atoi(evb), bmax, m}));
+        if (b < 2 && m >= 2) b = 2;
+        threads = std::max(64, 32 * b);
+        smem = (size_t)b * (32 * NE + 1) * sizeof(double);
+        switch (NE) {
+            case 2: kern = (void*)eig_jacobi_reg_kernel<2>; break;
+            case 4: kern = (void*)eig_jacobi_reg_kernel<4>; break;
+            case 8: kern = (void*)eig_jacobi_reg_kernel<8>; break;
+            case 16: kern = (void*)eig_jacobi_reg_kernel<16>; break;
+            default: kern = (void*)eig_jacobi_reg_kernel<32>; break;
+        }
+    } else {
+        // block size: 2b columns of m doubles must fit shared memory; one warp per pair of an inner round
+        b = std::min({16, m, (int)((200 * 1024) / (16 * (size_t)m))});
+        if (b < 1) { set_error(h, "pod_eig: more than 12800 snapshots are not supported"); return fail(IB200_ERR_ARG); }
+        if (evb) b = std::max(1, std::min(atoi(evb), b));
+        if (b < 2 && m >= 2) b = std::min(2, m);
+        threads = std::max(64, 32 * b);
+        smem = (size_t)2 * b * m * sizeof(double);
+        kern = (void*)eig_jacobi_block_kernel;
+    }
+    const int nb = (m + b - 1) / b;
+    if (smem > 227 * 1024) { set_error(h, "pod_eig: too many snapshots for the Jacobi block kernel"); return fail(IB200_ERR_ARG); }
+    IB_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int maxb = 0;
+    IB_CUDA(h, cudaOccupancyMaxActiveBlocksPerMultiprocessorWithFlags(&maxb, kern, threads, smem, cudaOccupancyDefault));
+    if (maxb < 1) { set_error(h, "pod_eig: Jacobi kernel does not fit one SM"); return fail(IB200_ERR_CUDA); }
+    const int want = std::max((nb + 1) / 2, 1);
+    const int nblocks = std::max(1, std::min(want, maxb * h->num_sms));
     int mm = m, bb = b, nbb = nb;
     void* args[] = {&X, &mm, &bb, &nbb, &tol, &flags};
-    IB_CUDA(h, cudaLaunchCooperativeKernel((void*)eig_jacobi_block_kernel, dim3(nblocks), dim3(threads), args, smem, h->stream));
-    eig_finalize_kernel<<<(m + 7) / 8, 256, 0, h->stream>>>(h->dW, m, sigma, lam_tmp);
+    IB_CUDA(h, cudaLaunchCooperativeKernel(kern, dim3(nblocks), dim3(threads), args, smem, h->stream));
+    eig_finalize_kernel<<<(m + 7) / 8, 256, 0, h->stream>>>(h->dW, m, sigma, 1.0 / scale, lam_tmp);
     eig_sort_permute_kernel<<<m, 128, 0, h->stream>>>(lam_tmp, h->dW, m, h->dEvals, h->dQ);
     IB_CUDA(h, cudaGetLastError());
     h->launches += 3;
