@@ -335,6 +335,26 @@ def run_b200(args, wl, rank, local_rank, world):
         except RuntimeError as ex:  # not enough pinned host memory for this workload
             e2e = {"value": None, "unit": UNIT, "error": "host buffers (%.1f GB pinned) unavailable: %s" % (host_bytes / 1e9, str(ex)[:80])}
 
+    # ---------------- projection leg (C4): all ranks take part (cell-sharded with halo layers when N > 1) ----------------
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    projection = None
+    if not args.no_projection:
+        import bench_proj
+        del S, snaps_dev
+        torch.cuda.empty_cache()
+        try:
+            projection, _, _, _ = bench_proj.run(pod, torch, dev, args.projection, hbm_peak=hbm_peak, dmma_peak=peak_dmma,
+                                                 rank=rank, world=world, dist=dist if multi else None)
+        except Exception as ex:  # never lose the POD line
+            projection = {"error": str(ex)[:200]}
+        if multi:
+            barrier()
+
     if rank != 0:
         if multi:
             dist.destroy_process_group()
@@ -351,12 +371,6 @@ def run_b200(args, wl, rank, local_rank, world):
             traffic = json.load(open(tf)).get(args.workload)
         except Exception:
             traffic = None
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    hbm_peak = peaks.get("hbm_gbs", 6650.0)
     lift_bytes = 8.0 * Nd * (m + r)
     line = {
         "metric": METRIC, "value": ms_step / 1e3, "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -376,15 +390,8 @@ def run_b200(args, wl, rank, local_rank, world):
         "gram_tflops_total": achieved * world,
         "stages_ms": stages, "gpu_launches": int(launches), "clocks": clk, "e2e": e2e,
     }
-    if not args.no_projection and world == 1:
-        import bench_proj
-        del S, snaps_dev
-        torch.cuda.empty_cache()
-        try:
-            pj, _, _, _ = bench_proj.run(pod, torch, dev, args.projection, hbm_peak=hbm_peak, dmma_peak=peak_dmma)
-            line["projection"] = pj
-        except Exception as ex:  # never lose the POD line
-            line["projection"] = {"error": str(ex)[:200]}
+    if projection is not None:
+        line["projection"] = projection
     if not args.no_cpu_baseline and world >= 1:
         threads = 1
         rows = max(256, min(cells, int(2.0e10 / (2.0 * m * m * dim))))  # ~10-20 s of single-core Gram

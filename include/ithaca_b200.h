@@ -165,6 +165,46 @@ enum { IB200_FVC_FLUX = 0, IB200_FVC_DIV_PHI = 1, IB200_FVC_LAPLACIAN = 2, IB200
  *   DIV_U     fvc::div(U_j)                               nCells */
 int ithaca_b200_fvc_eval(ithaca_b200_t* h, int op, int j, int k, double* out);
 
+/* ---- cell-sharded projection ---------------------------------------------------------
+ * Rank g of G owns the contiguous cell range of ithaca_b200_cell_range (the rule POD uses) and works on a SHARD MESH:
+ * its owned cells followed by `halo_layers` layers of face-neighbour cells (1 layer is enough for Gauss linear
+ * div/grad/interpolate, 2 for the "corrected" laplacian, whose face gradient needs grad in the first layer).
+ * The addressing follows OpenFOAM's decomposition files as ITHACAparallel reads them
+ * (src/ITHACA_CORE/ITHACAparallel/ITHACAparallel.C:43-74, used at :133-165):
+ *   cellProcAddressing[nLocalCells]  global label of each shard cell: owned cells first (ascending), then halo cells
+ *                                    (ascending global label)
+ *   faceProcAddressing[nLocalFaces]  +-(global face + 1); the sign is negative when the shard face is FLIPPED with
+ *                                    respect to the global face (the shard cell is the global neighbour), exactly the
+ *                                    processor-face convention of decomposePar. Shard faces in this order:
+ *                                    [internal: both cells in the shard][boundary faces of shard cells][cut faces:
+ *                                    faces between the outermost halo layer and cells outside the shard]; ascending
+ *                                    global index inside each group. Cut faces are boundary faces of the shard mesh
+ *                                    with mask 0 (they only touch outer-halo cells, whose results are never used).
+ * Host code only (no GPU needed). sizes[5] = {nLocalCells, nOwned, nLocalInt, nLocalBnd (true boundary), nCut}. */
+typedef struct ithaca_b200_partition ithaca_b200_partition_t;
+int ithaca_b200_partition_create(ithaca_b200_partition_t** p, int64_t nCells, int64_t nIntFaces, int64_t nBndFaces,
+                                 const int32_t* owner, const int32_t* neighbour, int rank, int nranks, int halo_layers);
+int ithaca_b200_partition_destroy(ithaca_b200_partition_t* p);
+int ithaca_b200_partition_sizes(const ithaca_b200_partition_t* p, int64_t* sizes5);
+int ithaca_b200_partition_addressing(const ithaca_b200_partition_t* p, int32_t* cellProcAddressing,
+                                     int32_t* faceProcAddressing);
+/* Shard copy of a global field. kind 0: cell field (dim doubles per cell) -> nLocalCells*dim; kind 1: boundary-face
+ * field (dim per global boundary face) -> (nLocalBnd+nCut)*dim, zeros on cut faces. */
+int ithaca_b200_partition_gather(const ithaca_b200_partition_t* p, int kind, int dim, const double* global_field,
+                                 double* shard_field);
+/* ithaca_b200_mesh_upload of this rank's shard, from the GLOBAL mesh arrays (host pointers, same meaning as in
+ * ithaca_b200_mesh_upload). Marks the halo cells: they get integration weight 0 in every projected operator, and
+ * ithaca_b200_project all-reduces the operator over the communicator of ithaca_b200_comm_init (one
+ * ncclAllReduce per operator instead of the reference's one gSum per entry, fvc::domainIntegrate at steadyNS.C:896-897 et al.).
+ * After this call ithaca_b200_basis_upload expects SHARD fields (ithaca_b200_partition_gather). */
+int ithaca_b200_mesh_upload_shard(ithaca_b200_t* h, const ithaca_b200_partition_t* p, const int32_t* owner,
+                                  const int32_t* neighbour, const double* Sf, const double* magSf, const double* weights,
+                                  const double* nonOrthDeltaCoeffs, const double* bndDeltaCoeffs,
+                                  const double* nonOrthCorrVec, const double* V, const unsigned char* bndMask);
+/* Lower-level form of the above for callers that already hold a decomposed mesh with halo cells: the first nOwned
+ * cells (caller's order) of the uploaded mesh are owned, the rest are halo. nOwned = nCells restores the default. */
+int ithaca_b200_mesh_set_owned(ithaca_b200_t* h, int64_t nOwned);
+
 /* Device times (ms) of the last ithaca_b200_project call: out[0]=face flux, [1]=div(phi,U), [2]=laplacian (+grad tensor),
  * [3]=grad(p), [4]=div(U), [5]=contraction, [6]=per-face records of the fused C. */
 int ithaca_b200_proj_timings(ithaca_b200_t* h, double* out, int n);

@@ -25,6 +25,9 @@ SYMBOLS = [
     "ithaca_b200_dmma_peak",
     "ithaca_b200_mesh_upload", "ithaca_b200_mesh_addressing", "ithaca_b200_basis_upload", "ithaca_b200_project",
     "ithaca_b200_fvc_eval", "ithaca_b200_proj_timings",
+    "ithaca_b200_partition_create", "ithaca_b200_partition_destroy", "ithaca_b200_partition_sizes",
+    "ithaca_b200_partition_addressing", "ithaca_b200_partition_gather", "ithaca_b200_mesh_upload_shard",
+    "ithaca_b200_mesh_set_owned",
 ]
 
 _lib = None
@@ -71,6 +74,13 @@ def lib():
         L.ithaca_b200_project.argtypes = [P, I, P]
         L.ithaca_b200_fvc_eval.argtypes = [P, I, I, I, P]
         L.ithaca_b200_proj_timings.argtypes = [P, P, I]
+        L.ithaca_b200_partition_create.argtypes = [ctypes.POINTER(P), L64, L64, L64, P, P, I, I, I]
+        L.ithaca_b200_partition_destroy.argtypes = [P]
+        L.ithaca_b200_partition_sizes.argtypes = [P, P]
+        L.ithaca_b200_partition_addressing.argtypes = [P, P, P]
+        L.ithaca_b200_partition_gather.argtypes = [P, I, I, P, P]
+        L.ithaca_b200_mesh_upload_shard.argtypes = [P, P] + [P] * 10
+        L.ithaca_b200_mesh_set_owned.argtypes = [P, L64]
         _lib = L
     return _lib
 
@@ -223,6 +233,53 @@ class Pod:
         return out
 
 
+class Partition:
+    """One rank's shard of a mesh: contiguous owned cell range + halo layers (host code of the library, no GPU needed).
+    Addressing in the form of decomposePar's cellProcAddressing / faceProcAddressing
+    (src/ITHACA_CORE/ITHACAparallel/ITHACAparallel.C:43-74)."""
+
+    def __init__(self, mesh, rank, nranks, halo_layers=2):
+        self.L = lib()
+        self.p = ctypes.c_void_p()
+        self._own = np.ascontiguousarray(mesh.owner, dtype=np.int32)
+        self._nei = np.ascontiguousarray(mesh.neighbour, dtype=np.int32)
+        rc = self.L.ithaca_b200_partition_create(ctypes.byref(self.p), int(mesh.nCells), int(mesh.nInt), int(mesh.nBnd),
+                                                 _ptr(self._own), _ptr(self._nei), rank, nranks, halo_layers)
+        if rc:
+            raise IthacaB200Error("partition_create: bad argument (status %d)" % rc)
+        sz = np.zeros(5, dtype=np.int64)
+        self.L.ithaca_b200_partition_sizes(self.p, sz.ctypes.data)
+        self.nLocalCells, self.nOwned, self.nLocalInt, self.nLocalBnd, self.nCut = [int(x) for x in sz]
+        self.rank, self.nranks = rank, nranks
+
+    def addressing(self):
+        cpa = np.zeros(self.nLocalCells, dtype=np.int32)
+        fpa = np.zeros(self.nLocalInt + self.nLocalBnd + self.nCut, dtype=np.int32)
+        self.L.ithaca_b200_partition_addressing(self.p, cpa.ctypes.data, fpa.ctypes.data)
+        return cpa, fpa
+
+    def gather(self, field, kind, dim):
+        """Shard copy of a global cell field (kind 'cell') or boundary-face field (kind 'bnd')."""
+        g = np.ascontiguousarray(field, dtype=np.float64)
+        n = self.nLocalCells if kind == "cell" else self.nLocalBnd + self.nCut
+        out = np.zeros(n * dim)
+        rc = self.L.ithaca_b200_partition_gather(self.p, 0 if kind == "cell" else 1, dim, g.ctypes.data, out.ctypes.data)
+        if rc:
+            raise IthacaB200Error("partition_gather: bad argument")
+        return out
+
+    def close(self):
+        if self.p:
+            self.L.ithaca_b200_partition_destroy(self.p)
+            self.p = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 OPS = {"M": 0, "B": 1, "K": 2, "P": 3, "C": 4, "Cmat": 5}
 FVC = {"flux": 0, "div_phi": 1, "laplacian": 2, "grad_p": 3, "div_u": 4}
 
@@ -249,6 +306,16 @@ class Projector:
         self.pod._chk(self.L.ithaca_b200_mesh_upload(
             self.h, self.nCells, self.nInt, self.nBnd, _ptr(k["owner"]), _ptr(k["nei"]), _ptr(k["Sf"]), _ptr(k["magSf"]),
             _ptr(k["w"]), _ptr(k["dc"]), _ptr(k["dcB"]), _ptr(k["corr"]), _ptr(k["V"]), _ptr(k["bmask"])))
+
+    def set_mesh_shard(self, mesh, part, corrected=True):
+        """Upload `part`'s shard of the GLOBAL mesh; set_basis then takes shard fields (part.gather) and project()
+        all-reduces over the Pod's communicator."""
+        c = lambda a, dt: np.ascontiguousarray(a, dtype=dt)
+        k = [c(mesh.owner, np.int32), c(mesh.neighbour, np.int32), c(mesh.Sf, np.float64), c(mesh.magSf, np.float64),
+             c(mesh.w, np.float64), c(mesh.dc, np.float64), c(mesh.dcB, np.float64),
+             c(mesh.corr, np.float64) if corrected else None, c(mesh.V, np.float64), c(mesh.bmask, np.uint8)]
+        self.nCells, self.nInt, self.nBnd = part.nLocalCells, part.nLocalInt, part.nLocalBnd + part.nCut
+        self.pod._chk(self.L.ithaca_b200_mesh_upload_shard(self.h, part.p, *[_ptr(a) for a in k]))
 
     def addressing(self):
         nnz = 2 * self.nInt + self.nBnd

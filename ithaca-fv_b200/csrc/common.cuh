@@ -113,6 +113,7 @@ struct ConvMesh {
     const int *owner, *neigh;
     const double *Sf, *w;
     const unsigned char* bmask;
+    const unsigned char* cmask;   // per cell: 1 owned, 0 halo (null = all owned); scales U_i in d_i = U_i[own] - U_i[nei]
 };
 struct ConvBufs {
     DevBuf Ucm, Ubcm, Aj, Bk, Dd, ws, chunks;
@@ -148,6 +149,7 @@ int lift_patch_launch(ithaca_b200* h, const double* dSbc, int64_t rows, double* 
 // symmetric != 0: B == A, only the lower triangle is computed and mirrored. out(i,j) is written to
 // out[i*rs + (j / cinner)*cso + (j % cinner)*csi] (doubles), so the caller can scatter straight into a matrix
 // (cinner = INT_MAX, csi = column stride) or into slices of a tensor.
+int allreduce_sum(ithaca_b200* h, double* dbuf, size_t count);   // capi.cu: ncclAllReduce(sum, f64) on the handle stream, no-op for 1 rank
 int atvb_launch(ithaca_b200* h, const double* A, long long lda, int Ma, const double* B, long long ldb, int Nb,
                 long long K, const double* V, int dim, int symmetric, double* out, long long rs, int cinner,
                 long long cso, long long csi);

@@ -62,8 +62,11 @@ conv_face_prep_kernel(ConvMesh m, const double* __restrict__ Ucm, const double* 
     const double s0 = m.Sf[3 * f], s1 = m.Sf[3 * f + 1], s2 = m.Sf[3 * f + 2];
     const int o = m.owner[f];
     const double* uo = Ucm + (size_t)o * 3 * NP;
+    const double mo = (m.cmask && !m.cmask[o]) ? 0.0 : 1.0;   // halo cells of a shard take no part in the integral
     if (f < m.nInt) {
-        const double* un = Ucm + (size_t)m.neigh[f] * 3 * NP;
+        const int nn = m.neigh[f];
+        const double* un = Ucm + (size_t)nn * 3 * NP;
+        const double mn = (m.cmask && !m.cmask[nn]) ? 0.0 : 1.0;
         const double w = m.w[f], w1 = 1.0 - w;
         for (int j = threadIdx.x; j < NP; j += 64) {
             const double o0 = uo[j], o1 = uo[NP + j], o2 = uo[2 * NP + j];
@@ -73,7 +76,7 @@ conv_face_prep_kernel(ConvMesh m, const double* __restrict__ Ucm, const double* 
             a += b0 * s0; a += b1 * s1; a += b2 * s2;
             Aj[(size_t)f * NP + j] = a;
             double* d = Dd + (size_t)f * 3 * NP;
-            d[j] = o0 - n0; d[NP + j] = o1 - n1; d[2 * NP + j] = o2 - n2;
+            d[j] = mo * o0 - mn * n0; d[NP + j] = mo * o1 - mn * n1; d[2 * NP + j] = mo * o2 - mn * n2;
             if (j < N) {
                 double4* b = reinterpret_cast<double4*>(Bk + ((size_t)f * N + j) * 4);
                 *b = make_double4(b0, b1, b2, 0.0);
@@ -89,7 +92,7 @@ conv_face_prep_kernel(ConvMesh m, const double* __restrict__ Ucm, const double* 
             if (on) { a += b0 * s0; a += b1 * s1; a += b2 * s2; }
             Aj[(size_t)f * NP + j] = a;
             double* d = Dd + (size_t)f * 3 * NP;
-            d[j] = uo[j]; d[NP + j] = uo[NP + j]; d[2 * NP + j] = uo[2 * NP + j];
+            d[j] = mo * uo[j]; d[NP + j] = mo * uo[NP + j]; d[2 * NP + j] = mo * uo[2 * NP + j];
             if (j < N) {
                 double4* b = reinterpret_cast<double4*>(Bk + ((size_t)f * N + j) * 4);
                 *b = make_double4(b0, b1, b2, 0.0);

@@ -42,6 +42,8 @@ struct ProjState {
     DevBuf owner0, neigh0, off0, ent0, other0;   // the caller's addressing (mesh_addressing reports this one)
     bool have_csr0 = false;
     DevBuf perm;    // old2new cell label (int, nCells)
+    DevBuf Vw, cmask;   // shard: integration weights (V on owned cells, 0 on halo cells) and owned mask, internal order
+    long long nOwned = 0;   // == nCells unless mesh_set_owned marked halo cells
     DevBuf fperm;   // original index of the internal face at each new position (int, nInt)
     DevBuf stage;   // one field in the caller's order (upload / fvc_eval staging)
     int nU = 0, nP = 0;
@@ -83,7 +85,7 @@ void proj_destroy(ithaca_b200* h)
     if (!s) return;
     for (DevBuf* b : {&s->owner, &s->neigh, &s->Sf, &s->magSf, &s->w, &s->dc, &s->dcB, &s->corr, &s->V, &s->bmask,
                       &s->off, &s->ent, &s->other, &s->cnt, &s->blocksum, &s->U, &s->Ub, &s->P, &s->Pb, &s->flux,
-                      &s->owner0, &s->neigh0, &s->off0, &s->ent0, &s->other0, &s->perm, &s->fperm, &s->stage,
+                      &s->owner0, &s->neigh0, &s->off0, &s->ent0, &s->other0, &s->perm, &s->fperm, &s->stage, &s->Vw, &s->cmask,
                       &s->work, &s->T, &s->out, &s->conv.Ucm, &s->conv.Ubcm, &s->conv.Aj, &s->conv.Bk, &s->conv.Dd,
                       &s->conv.ws, &s->conv.chunks})
         if (b->p) cudaFree(b->p);
@@ -556,6 +558,18 @@ laplacian_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const d
 // ------------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------------
+// shard bookkeeping: caller-order cell c is owned iff c < nOwned. Internal order: cmask[perm[c]], Vw = V on owned cells else 0.
+__global__ void owned_mask_kernel(const int* __restrict__ perm, long long nCells, long long nOwned, const double* __restrict__ V,
+                                  double* __restrict__ Vw, unsigned char* __restrict__ cmask)
+{
+    for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < nCells; c += (long long)gridDim.x * blockDim.x) {
+        const int n = perm[c];
+        const bool own = c < nOwned;
+        cmask[n] = own ? 1 : 0;
+        Vw[n] = own ? V[n] : 0.0;
+    }
+}
+
 static inline long long pad16(long long n) { return (n + 15) / 16 * 16; }
 static inline unsigned gx(long long n) { return (unsigned)((n + PROJ_T - 1) / PROJ_T); }
 static inline unsigned gy(int n) { return (unsigned)((n + FB - 1) / FB); }
@@ -751,7 +765,29 @@ int ithaca_b200_mesh_upload(ithaca_b200_t* h, int64_t nCells, int64_t nIntFaces,
     IB_CUDA(h, e);
     IB_CUDA(h, cudaGetLastError());
     s->have_mesh = true;
+    s->nOwned = nCells;
     s->nU = s->nP = 0;
+    return IB200_OK;
+}
+
+int ithaca_b200_mesh_set_owned(ithaca_b200_t* h, int64_t nOwned)
+{
+    if (!h) return IB200_ERR_ARG;
+    ProjState* s = h->proj;
+    PROJ_REQUIRE(s && s->have_mesh, "mesh_set_owned: no mesh uploaded");
+    PROJ_REQUIRE(nOwned >= 0 && nOwned <= s->nCells, "mesh_set_owned: nOwned out of range");
+    cudaSetDevice(h->device);
+    s->nOwned = nOwned;
+    h->vol_gen++;
+    if (nOwned == s->nCells) return IB200_OK;
+    int rc;
+    if ((rc = ensure(h, s->Vw, s->nCells * sizeof(double))) || (rc = ensure(h, s->cmask, std::max<long long>(s->nCells, 16)))) return rc;
+    const int g = (int)std::min<long long>((s->nCells + 255) / 256, 64LL * h->num_sms);
+    owned_mask_kernel<<<std::max(g, 1), 256, 0, h->stream>>>(s->perm.as<int>(), s->nCells, nOwned, s->V.as<double>(), s->Vw.as<double>(),
+                                                             s->cmask.as<unsigned char>());
+    h->launches += 1;
+    IB_CUDA(h, cudaGetLastError());
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
     return IB200_OK;
 }
 
@@ -912,7 +948,8 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
     const int N = s->nU, Np = s->nP, BIG = 0x7fffffff;
     const long long K3 = 3 * s->nCells;
     const double* U = s->U.as<double>();
-    const double* V = s->V.as<double>();
+    const bool shard = s->nOwned < s->nCells;
+    const double* V = shard ? s->Vw.as<double>() : s->V.as<double>();   // integration weights (0 on halo cells)
     size_t nout = 0;
     int rc;
     for (double& x : s->ms) x = 0.0;
@@ -978,6 +1015,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
         if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
         ConvMesh cm;
         cm.nInt = s->nInt; cm.nBnd = s->nBnd; cm.owner = m.owner; cm.neigh = m.neigh; cm.Sf = m.Sf; cm.w = m.w; cm.bmask = m.bmask;
+        cm.cmask = shard ? s->cmask.as<unsigned char>() : nullptr;
         rc = conv_fused_launch(h, &s->conv, cm, s->nCells, U, s->ldU, s->Ub.as<double>(), s->ldUb, N, s->out.as<double>(), &s->ms[6],
                                &s->ms[5]);
         if (rc) return rc;
@@ -1015,6 +1053,13 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
         PROJ_REQUIRE(false, "project: unknown operator");
     }
     IB_CUDA(h, cudaGetLastError());
+    // cell-sharded run: one all-reduce of the whole operator (the reference: one gSum per entry inside domainIntegrate)
+    if (h->nccl_comm && h->nranks > 1) {
+        StageTimer t(h->stream, &s->ms[7]);
+        rc = allreduce_sum(h, s->out.as<double>(), nout);
+        t.stop();
+        if (rc) return rc;
+    }
     IB_CUDA(h, cudaMemcpyAsync(out, s->out.p, nout * sizeof(double), cudaMemcpyDefault, h->stream));
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
     return IB200_OK;

@@ -139,3 +139,32 @@ def test_projection_error_paths(pkg):
     with pytest.raises(pkg.IthacaB200Error):
         pr.project("K")  # no pressure basis
     p.close()
+
+
+@pytest.mark.parametrize("nranks,name", [(2, "tutorial04"), (3, "cyl")])
+def test_sharded_projection_sums_to_the_global_operators(pkg, pod, nranks, name):
+    """every rank projects on its shard mesh (owned cells + 2 halo layers, halo cells weigh 0); the sum
+    over ranks -- what the per-operator all-reduce forms -- equals the single-mesh operators to 1e-10."""
+    mesh = meshes()[name]()
+    N, Np = 6, 3
+    U, Ub, P, Pb = fvc.synthetic_basis(mesh, N, Np, seed=13)
+    orc = fvc.Oracle(mesh, corrected=True)
+    ref = {"M": orc.mass_term(U), "B": orc.diffusive_term(U, Ub), "K": orc.pressure_gradient_term(U, P, Pb),
+           "P": orc.divergence_term(U, Ub, P), "C": orc.convective_term_tens(U, Ub, cache=True)}
+    ref["Cmat"] = ref["C"]
+    acc = {k: np.zeros_like(v) for k, v in ref.items()}
+    pr = pkg.Projector(pod)
+    for rank in range(nranks):
+        part = pkg.Partition(mesh, rank, nranks, 2)
+        pr.set_mesh_shard(mesh, part, corrected=True)
+        pr.set_basis("U", [part.gather(u, "cell", 3) for u in U], [part.gather(u, "bnd", 3) for u in Ub])
+        pr.set_basis("P", [part.gather(p, "cell", 1) for p in P], [part.gather(p, "bnd", 1) for p in Pb])
+        for k in acc:
+            acc[k] += pr.project(k)
+        part.close()
+    for k in acc:
+        assert rel(acc[k], ref[k]) <= TOL, k
+    # a plain mesh_upload afterwards restores the unsharded behaviour
+    pr.set_mesh(mesh, corrected=True)
+    pr.set_basis("U", U, Ub)
+    assert rel(pr.project("C"), ref["C"]) <= TOL
