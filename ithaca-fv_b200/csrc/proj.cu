@@ -53,6 +53,7 @@ struct ProjState {
     bool have_flux = false;
     DevBuf work;   // operator fields, columns of ldU (vector) or ldP (scalar) doubles
     DevBuf T;      // gradient tensors of a batch of fields, 9*nCells doubles each
+    DevBuf Tcm, Lcm;   // cell-major gradient tensors [c][9][NP] and laplacians [c][3][NP] of all fields
     DevBuf out;    // device copy of the projected operator
     ConvBufs conv; // fused convective tensor (conv.cu)
     double ms[8] = {0};  // last timings: flux, div_phi, lap, grad, div, contraction
@@ -85,7 +86,7 @@ void proj_destroy(ithaca_b200* h)
     if (!s) return;
     for (DevBuf* b : {&s->owner, &s->neigh, &s->Sf, &s->magSf, &s->w, &s->dc, &s->dcB, &s->corr, &s->V, &s->bmask,
                       &s->off, &s->ent, &s->other, &s->cnt, &s->blocksum, &s->U, &s->Ub, &s->P, &s->Pb, &s->flux,
-                      &s->owner0, &s->neigh0, &s->off0, &s->ent0, &s->other0, &s->perm, &s->fperm, &s->stage, &s->Vw, &s->cmask,
+                      &s->owner0, &s->neigh0, &s->off0, &s->ent0, &s->other0, &s->perm, &s->fperm, &s->stage, &s->Vw, &s->cmask, &s->Tcm, &s->Lcm,
                       &s->work, &s->T, &s->out, &s->conv.Ucm, &s->conv.Ubcm, &s->conv.Aj, &s->conv.Bk, &s->conv.Dd,
                       &s->conv.ws, &s->conv.chunks})
         if (b->p) cudaFree(b->p);
@@ -445,14 +446,17 @@ grad_scalar_kernel(MeshDev m, const double* __restrict__ P, long long ldP, const
             for (int d = 0; d < 3; d++) out[(size_t)(j0 + jj) * ldo + 3 * c + d] = acc[jj][d] / V;
 }
 
-// K7a: T_j = fvc::grad(U_j), Gauss linear: T[c][i][d] = sum_f +-Sf_i * Uf_d / V. One field per blockIdx.y.
+// K7a: T_j = fvc::grad(U_j), Gauss linear: T[c][i][d] = sum_f +-Sf_i * Uf_d / V. One field per block.
 __global__ void __launch_bounds__(PROJ_T)
 grad_vec_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const double* __restrict__ Ub, long long ldUb,
-                int j0, double* __restrict__ T, long long ldT)
+                int j0, int nb, double* __restrict__ T, long long ldT)
 {
-    const long long c = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    // blockIdx.x = cell block * nb + field: the nb fields of one cell block run together, so the mesh arrays of the
+    // block are fetched from DRAM once and re-read from L2 by the other fields
+    const int jl = blockIdx.x % nb;
+    const long long c = (blockIdx.x / nb) * (long long)PROJ_T + threadIdx.x;
     if (c >= m.nCells) return;
-    const int j = j0 + blockIdx.y;
+    const int j = j0 + jl;
     const double* u = U + (size_t)j * ldU;
     const double uc[3] = {u[3 * c], u[3 * c + 1], u[3 * c + 2]};
     double acc[3][3];
@@ -487,29 +491,34 @@ grad_vec_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const do
         }
     }
     const double V = m.V[c];
-    double* t = T + (size_t)blockIdx.y * ldT + 9 * c;
+    // component-major within a field, T[j][3i+d][c] (ldc = ldT/9 cells per component): consecutive cells of a warp
+    // read and write consecutive doubles (the 72-byte cell-major records cost 3-4x the L1 sector accesses)
+    const long long ldc = ldT / 9;
+    double* t = T + (size_t)jl * ldT + c;
 #pragma unroll
     for (int i = 0; i < 3; i++)
 #pragma unroll
-        for (int d = 0; d < 3; d++) t[3 * i + d] = acc[i][d] / V;
+        for (int d = 0; d < 3; d++) t[(3 * i + d) * ldc] = acc[i][d] / V;
 }
 
 // K7b: out_j = fvc::laplacian(1, U_j) = surfaceIntegrate(|Sf| snGrad(U_j)); snGrad = dc (U[n]-U[o])
-// (+ corr . (w T[o] + (1-w) T[n]) when corrected); boundary |Sf| dcB (Ub - U[c]). One field per blockIdx.y.
+// (+ corr . (w T[o] + (1-w) T[n]) when corrected); boundary |Sf| dcB (Ub - U[c]). Grid as in grad_vec_kernel.
 __global__ void __launch_bounds__(PROJ_T)
 laplacian_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const double* __restrict__ Ub, long long ldUb,
-                 int j0, const double* __restrict__ T, long long ldT, double* __restrict__ out, long long ldo)
+                 int j0, int nb, const double* __restrict__ T, long long ldT, double* __restrict__ out, long long ldo)
 {
-    const long long c = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    const int jl = blockIdx.x % nb;
+    const long long c = (blockIdx.x / nb) * (long long)PROJ_T + threadIdx.x;
     if (c >= m.nCells) return;
-    const int j = j0 + blockIdx.y;
+    const int j = j0 + jl;
     const double* u = U + (size_t)j * ldU;
-    const double* t = T ? T + (size_t)blockIdx.y * ldT : nullptr;
+    const double* t = T ? T + (size_t)jl * ldT : nullptr;
     const double uc[3] = {u[3 * c], u[3 * c + 1], u[3 * c + 2]};
+    const long long ldc = ldT / 9;
     double tc[9];
     if (t)
 #pragma unroll
-        for (int k = 0; k < 9; k++) tc[k] = t[9 * c + k];
+        for (int k = 0; k < 9; k++) tc[k] = t[k * ldc + c];
     double acc[3] = {0.0, 0.0, 0.0};
     const int e0 = m.off[c], e1 = m.off[c + 1];
     for (int e = e0; e < e1; e++) {
@@ -522,13 +531,13 @@ laplacian_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const d
             double cr[3] = {0.0, 0.0, 0.0};
             if (t) {
                 const double w = m.w[f], w1 = 1.0 - w;
-                const double* tn = t + 9 * (size_t)ot;
+                const double* tn = t + (size_t)ot;
 #pragma unroll
                 for (int i = 0; i < 3; i++) {
                     const double k = m.corr[3 * f + i];
 #pragma unroll
                     for (int d = 0; d < 3; d++) {
-                        const double x = tn[3 * i + d];
+                        const double x = tn[(3 * i + d) * ldc];
                         cr[d] += k * (own ? (w * tc[3 * i + d] + w1 * x) : (w * x + w1 * tc[3 * i + d]));
                     }
                 }
@@ -553,6 +562,173 @@ laplacian_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const d
     const double V = m.V[c];
 #pragma unroll
     for (int d = 0; d < 3; d++) out[(size_t)j * ldo + 3 * c + d] = acc[d] / V;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K7 cell-major: all N laplacians in one pass over the mesh. The basis is held cell-major, Ucm[c][d][NP] (fields
+// innermost, the layout of conv.cu), one thread = (cell, field): the lanes of a warp read 8*NP-byte rows (coalesced)
+// and share every mesh scalar (one broadcast load), so the addressing and geometry are fetched once per cell for all
+// fields instead of once per field. Same arithmetic, in the same order, as grad_vec_kernel / laplacian_kernel.
+// ------------------------------------------------------------------------------------------------
+constexpr int CM_CELLS = 4;   // cells per block (threadIdx.y); threadIdx.x = 64 lanes over the fields
+
+// out[r*NP + j] = in[j*ld + r] (j < N, else 0): field-major columns -> cell-major rows. Block (32, 8), 32x32 tiles.
+__global__ void __launch_bounds__(256)
+tr_fm2cm_kernel(const double* __restrict__ in, long long ld, long long rows, int N, int NP, double* __restrict__ out)
+{
+    __shared__ double tile[32][33];
+    const long long r0 = (long long)blockIdx.x * 32;
+    for (int j0 = 0; j0 < NP; j0 += 32) {
+        for (int jj = threadIdx.y; jj < 32; jj += 8) {
+            const int j = j0 + jj;
+            const long long r = r0 + threadIdx.x;
+            tile[jj][threadIdx.x] = (j < N && r < rows) ? in[(size_t)j * ld + r] : 0.0;
+        }
+        __syncthreads();
+        for (int rr = threadIdx.y; rr < 32; rr += 8) {
+            const int j = j0 + threadIdx.x;
+            const long long r = r0 + rr;
+            if (j < NP && r < rows) out[(size_t)r * NP + j] = tile[threadIdx.x][rr];
+        }
+        __syncthreads();
+    }
+}
+// out[j*ldo + r] = in[r*NP + j] for j < N: cell-major rows -> field-major columns.
+__global__ void __launch_bounds__(256)
+tr_cm2fm_kernel(const double* __restrict__ in, long long rows, int NP, int N, double* __restrict__ out, long long ldo)
+{
+    __shared__ double tile[32][33];
+    const long long r0 = (long long)blockIdx.x * 32;
+    for (int j0 = 0; j0 < N; j0 += 32) {
+        for (int rr = threadIdx.y; rr < 32; rr += 8) {
+            const int j = j0 + threadIdx.x;
+            const long long r = r0 + rr;
+            tile[rr][threadIdx.x] = (j < NP && r < rows) ? in[(size_t)r * NP + j] : 0.0;
+        }
+        __syncthreads();
+        for (int jj = threadIdx.y; jj < 32; jj += 8) {
+            const int j = j0 + jj;
+            const long long r = r0 + threadIdx.x;
+            if (j < N && r < rows) out[(size_t)j * ldo + r] = tile[threadIdx.x][jj];
+        }
+        __syncthreads();
+    }
+}
+
+// Tcm[c][3i+d][NP] = fvc::grad(U_j)[c][i][d] for every field j (lane)
+__global__ void __launch_bounds__(64 * CM_CELLS)
+grad_cm_kernel(MeshDev m, const double* __restrict__ Ucm, const double* __restrict__ Ubcm, int NP, double* __restrict__ Tcm)
+{
+    const long long c = (long long)blockIdx.x * CM_CELLS + threadIdx.y;
+    if (c >= m.nCells) return;
+    const int e0 = m.off[c], e1 = m.off[c + 1];
+    const double V = m.V[c];
+    for (int j = threadIdx.x; j < NP; j += 64) {
+        const double* uo = Ucm + (size_t)c * 3 * NP + j;
+        const double uc[3] = {uo[0], uo[NP], uo[2 * NP]};
+        double acc[3][3];
+#pragma unroll
+        for (int i = 0; i < 3; i++) acc[i][0] = acc[i][1] = acc[i][2] = 0.0;
+        for (int e = e0; e < e1; e++) {
+            const int en = m.ent[e], ot = m.other[e];
+            const long long f = abs(en) - 1;
+            const double s[3] = {m.Sf[3 * f], m.Sf[3 * f + 1], m.Sf[3 * f + 2]};
+            if (ot >= 0) {
+                const double w = m.w[f], w1 = 1.0 - w;
+                const bool own = en > 0;
+                const double* un = Ucm + (size_t)ot * 3 * NP + j;
+#pragma unroll
+                for (int d = 0; d < 3; d++) {
+                    const double x = un[d * NP];
+                    const double uf = own ? (w * uc[d] + w1 * x) : (w * x + w1 * uc[d]);
+#pragma unroll
+                    for (int i = 0; i < 3; i++) {
+                        const double v = s[i] * uf;
+                        acc[i][d] += own ? v : -v;
+                    }
+                }
+            } else {
+                const long long b = -(long long)ot - 1;
+                if (!m.bmask[b]) continue;
+                const double* ub = Ubcm + (size_t)b * 3 * NP + j;
+#pragma unroll
+                for (int d = 0; d < 3; d++) {
+                    const double x = ub[d * NP];
+#pragma unroll
+                    for (int i = 0; i < 3; i++) acc[i][d] += s[i] * x;
+                }
+            }
+        }
+        double* t = Tcm + (size_t)c * 9 * NP + j;
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+#pragma unroll
+            for (int d = 0; d < 3; d++) t[(3 * i + d) * NP] = acc[i][d] / V;
+    }
+}
+
+// Lcm[c][d][NP] = fvc::laplacian(1, U_j)[c][d] for every field j (lane); Tcm = nullptr: uncorrected
+__global__ void __launch_bounds__(64 * CM_CELLS)
+laplacian_cm_kernel(MeshDev m, const double* __restrict__ Ucm, const double* __restrict__ Ubcm, int NP,
+                    const double* __restrict__ Tcm, double* __restrict__ Lcm)
+{
+    const long long c = (long long)blockIdx.x * CM_CELLS + threadIdx.y;
+    if (c >= m.nCells) return;
+    const int e0 = m.off[c], e1 = m.off[c + 1];
+    const double V = m.V[c];
+    for (int j = threadIdx.x; j < NP; j += 64) {
+        const double* uo = Ucm + (size_t)c * 3 * NP + j;
+        const double uc[3] = {uo[0], uo[NP], uo[2 * NP]};
+        double tc[9];
+        if (Tcm) {
+            const double* t = Tcm + (size_t)c * 9 * NP + j;
+#pragma unroll
+            for (int k = 0; k < 9; k++) tc[k] = t[k * NP];
+        }
+        double acc[3] = {0.0, 0.0, 0.0};
+        for (int e = e0; e < e1; e++) {
+            const int en = m.ent[e], ot = m.other[e];
+            const long long f = abs(en) - 1;
+            const double ms = m.magSf[f];
+            if (ot >= 0) {
+                const bool own = en > 0;
+                const double dc = m.dc[f];
+                double cr[3] = {0.0, 0.0, 0.0};
+                if (Tcm) {
+                    const double w = m.w[f], w1 = 1.0 - w;
+                    const double* tn = Tcm + (size_t)ot * 9 * NP + j;
+#pragma unroll
+                    for (int i = 0; i < 3; i++) {
+                        const double k = m.corr[3 * f + i];
+#pragma unroll
+                        for (int d = 0; d < 3; d++) {
+                            const double x = tn[(3 * i + d) * NP];
+                            cr[d] += k * (own ? (w * tc[3 * i + d] + w1 * x) : (w * x + w1 * tc[3 * i + d]));
+                        }
+                    }
+                }
+                const double* un = Ucm + (size_t)ot * 3 * NP + j;
+#pragma unroll
+                for (int d = 0; d < 3; d++) {
+                    const double x = un[d * NP];
+                    double sn = own ? dc * (x - uc[d]) : dc * (uc[d] - x);
+                    if (Tcm) sn += cr[d];
+                    const double v = ms * sn;
+                    acc[d] += own ? v : -v;
+                }
+            } else {
+                const long long b = -(long long)ot - 1;
+                if (!m.bmask[b]) continue;
+                const double* ub = Ubcm + (size_t)b * 3 * NP + j;
+                const double dcb = m.dcB[b];
+#pragma unroll
+                for (int d = 0; d < 3; d++) acc[d] += ms * (dcb * (ub[d * NP] - uc[d]));
+            }
+        }
+        double* o = Lcm + (size_t)c * 3 * NP + j;
+#pragma unroll
+        for (int d = 0; d < 3; d++) o[d * NP] = acc[d] / V;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -638,8 +814,47 @@ static int need_flux(ithaca_b200* h, ProjState* s)
 static int run_laplacians(ithaca_b200* h, ProjState* s, double* out)
 {
     const MeshDev m = mesh_dev(s);
-    const int batch = 8;
-    const long long ldT = pad16(9 * s->nCells);
+    // ITHACA_B200_LAP=cm selects the cell-major pass (all fields per cell, bitwise the same results). Measured at C4
+    // (2M cells, N = 50): 23.8 ms against 16.2 ms for the field-major kernels below -- both are bound by the latency of
+    // the per-face dependent loads, and the field-major blocks (64 consecutive cells of one field) reuse neighbour
+    // rows in L1 -- so field-major stays the default.
+    {
+        const int N = s->nU, NP = (N + 3) / 8 * 8 + 4;
+        const size_t per = (size_t)NP * 8;
+        const size_t need = per * ((size_t)s->nCells * (3 + 3 + (s->corrected ? 9 : 0)) + (size_t)std::max<long long>(s->nBnd, 1) * 3);
+        size_t have = s->conv.Ucm.cap + s->conv.Ubcm.cap + s->Tcm.cap + s->Lcm.cap, fr = 0, tot = 0;
+        cudaMemGetInfo(&fr, &tot);
+        const char* ev = getenv("ITHACA_B200_LAP");
+        if (ev && strcmp(ev, "cm") == 0 && need <= have + fr / 2) {
+            int rc;
+            if ((rc = ensure(h, s->conv.Ucm, (size_t)s->nCells * 3 * per)) ||
+                (rc = ensure(h, s->conv.Ubcm, (size_t)std::max<long long>(s->nBnd, 1) * 3 * per)) ||
+                (s->corrected && (rc = ensure(h, s->Tcm, (size_t)s->nCells * 9 * per))) ||
+                (rc = ensure(h, s->Lcm, (size_t)s->nCells * 3 * per)))
+                return rc;
+            StageTimer t(h->stream, &s->ms[2]);
+            const long long rows = 3 * s->nCells, rowsB = 3 * s->nBnd;
+            tr_fm2cm_kernel<<<(unsigned)((rows + 31) / 32), dim3(32, 8), 0, h->stream>>>(s->U.as<double>(), s->ldU, rows, N, NP,
+                                                                                        s->conv.Ucm.as<double>());
+            if (rowsB)
+                tr_fm2cm_kernel<<<(unsigned)((rowsB + 31) / 32), dim3(32, 8), 0, h->stream>>>(s->Ub.as<double>(), s->ldUb, rowsB, N, NP,
+                                                                                             s->conv.Ubcm.as<double>());
+            const unsigned gc = (unsigned)((s->nCells + CM_CELLS - 1) / CM_CELLS);
+            if (s->corrected)
+                grad_cm_kernel<<<gc, dim3(64, CM_CELLS), 0, h->stream>>>(m, s->conv.Ucm.as<double>(), s->conv.Ubcm.as<double>(), NP,
+                                                                         s->Tcm.as<double>());
+            laplacian_cm_kernel<<<gc, dim3(64, CM_CELLS), 0, h->stream>>>(m, s->conv.Ucm.as<double>(), s->conv.Ubcm.as<double>(), NP,
+                                                                          s->corrected ? s->Tcm.as<double>() : nullptr, s->Lcm.as<double>());
+            tr_cm2fm_kernel<<<(unsigned)((rows + 31) / 32), dim3(32, 8), 0, h->stream>>>(s->Lcm.as<double>(), rows, NP, N, out, s->ldU);
+            t.stop();
+            h->launches += 3 + (rowsB ? 1 : 0) + (s->corrected ? 1 : 0);
+            IB_CUDA(h, cudaGetLastError());
+            return IB200_OK;
+        }
+    }
+    int batch = 8;   // fields per launch (T holds batch gradient tensors); ITHACA_B200_LAP_BATCH overrides (tuning)
+    if (const char* e = getenv("ITHACA_B200_LAP_BATCH")) batch = std::max(1, std::min(atoi(e), 64));
+    const long long ldT = 9 * pad16(s->nCells);
     if (s->corrected) {
         int rc = ensure(h, s->T, (size_t)batch * ldT * sizeof(double));
         if (rc) return rc;
@@ -648,12 +863,12 @@ static int run_laplacians(ithaca_b200* h, ProjState* s, double* out)
     for (int j0 = 0; j0 < s->nU; j0 += batch) {
         const int nb = std::min(batch, s->nU - j0);
         if (s->corrected) {
-            grad_vec_kernel<<<dim3(gx(s->nCells), nb), PROJ_T, 0, h->stream>>>(m, s->U.as<double>(), s->ldU, s->Ub.as<double>(),
-                                                                                s->ldUb, j0, s->T.as<double>(), ldT);
+            grad_vec_kernel<<<gx(s->nCells) * nb, PROJ_T, 0, h->stream>>>(m, s->U.as<double>(), s->ldU, s->Ub.as<double>(),
+                                                                           s->ldUb, j0, nb, s->T.as<double>(), ldT);
             h->launches += 1;
         }
-        laplacian_kernel<<<dim3(gx(s->nCells), nb), PROJ_T, 0, h->stream>>>(m, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb,
-                                                                             j0, s->corrected ? s->T.as<double>() : nullptr, ldT, out, s->ldU);
+        laplacian_kernel<<<gx(s->nCells) * nb, PROJ_T, 0, h->stream>>>(m, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb,
+                                                                        j0, nb, s->corrected ? s->T.as<double>() : nullptr, ldT, out, s->ldU);
         h->launches += 1;
     }
     t.stop();

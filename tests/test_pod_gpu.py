@@ -172,3 +172,20 @@ def test_error_paths(pkg):
     with pytest.raises(pkg.IthacaB200Error):
         p.lift(2, "H1")
     p.close()
+
+
+@pytest.mark.parametrize("dim,solver", [(3, "spectra"), (3, "eigen"), (1, "spectra"), (1, "eigen")])
+def test_c1_tutorial_scale_matches_oracle(pkg, pod, dim, solver):
+    """BASELINE config C1: the 01POD cavity, 10 000 cells of 1e-8 m^3 each
+    (tutorials/CFD/01POD/system/blockMeshDict: uniform 100x100x1 block of a 0.1 x 0.1 x 0.01 m box), 100 U / p
+    snapshots, 10 modes, both EigenSolver settings, L2 norm."""
+    Nc, m, r = 10_000, 100, 10
+    S = synth.snapshots(Nc, dim, m, 2 * r, 20251104 + 1)
+    V = np.full(Nc, 1e-8)
+    out = pkg.getModes(pod, S, V, dim, r, solver, "L2")
+    ref = po.getmodes(S, V, dim, r, solver, "L2")
+    assert rel_max(out["G"], ref["G"]) <= 1e-13
+    assert len(out["evals_norm"]) == len(ref["evals_norm"]) == (r if solver == "spectra" else m)
+    assert np.all(np.abs(out["evals_norm"][:r] - ref["evals_norm"][:r]) <= 1e-10 * ref["evals_norm"][:r])
+    assert np.abs(out["cum"] - ref["cum"]).max() <= 1e-12
+    assert modes_rel(out["modes"], ref["modes"]) <= 1e-8
