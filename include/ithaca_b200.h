@@ -180,10 +180,24 @@ int ithaca_b200_fvc_eval(ithaca_b200_t* h, int op, int j, int k, double* out);
  *                                    faces between the outermost halo layer and cells outside the shard]; ascending
  *                                    global index inside each group. Cut faces are boundary faces of the shard mesh
  *                                    with mask 0 (they only touch outer-halo cells, whose results are never used).
+ * Ownership, `method`:
+ *   IB200_PART_LABEL_RANGE     owned = the contiguous LABEL range of ithaca_b200_cell_range (SURVEY 8(e)'s rule; what a
+ *                              decomposePar "simple"-like split of an already ordered mesh gives);
+ *   IB200_PART_LOCALITY_RANGE  owned = a contiguous range of the library's locality ordering (the Cuthill-McKee
+ *                              renumbering every mesh_upload applies internally, ithaca_b200_mesh_renumbering): same
+ *                              range rule, applied to ranks in that ordering, so that shards are spatially compact
+ *                              whatever labels the mesher produced (the C4 benchmark mesh is randomly relabelled, and a
+ *                              label range of it touches every other cell: its halo is the whole mesh).
  * Host code only (no GPU needed). sizes[5] = {nLocalCells, nOwned, nLocalInt, nLocalBnd (true boundary), nCut}. */
+enum { IB200_PART_LABEL_RANGE = 0, IB200_PART_LOCALITY_RANGE = 1 };
 typedef struct ithaca_b200_partition ithaca_b200_partition_t;
 int ithaca_b200_partition_create(ithaca_b200_partition_t** p, int64_t nCells, int64_t nIntFaces, int64_t nBndFaces,
-                                 const int32_t* owner, const int32_t* neighbour, int rank, int nranks, int halo_layers);
+                                 const int32_t* owner, const int32_t* neighbour, int rank, int nranks, int halo_layers,
+                                 int method);
+/* The locality ordering itself: old2new[c] = position of cell c (breadth-first Cuthill-McKee from a pseudo-peripheral
+ * cell, neighbours by increasing degree then label; one search per connected component in label order). */
+int ithaca_b200_mesh_renumbering(int64_t nCells, int64_t nIntFaces, const int32_t* owner, const int32_t* neighbour,
+                                 int32_t* old2new);
 int ithaca_b200_partition_destroy(ithaca_b200_partition_t* p);
 int ithaca_b200_partition_sizes(const ithaca_b200_partition_t* p, int64_t* sizes5);
 int ithaca_b200_partition_addressing(const ithaca_b200_partition_t* p, int32_t* cellProcAddressing,

@@ -27,7 +27,7 @@ SYMBOLS = [
     "ithaca_b200_fvc_eval", "ithaca_b200_proj_timings",
     "ithaca_b200_partition_create", "ithaca_b200_partition_destroy", "ithaca_b200_partition_sizes",
     "ithaca_b200_partition_addressing", "ithaca_b200_partition_gather", "ithaca_b200_mesh_upload_shard",
-    "ithaca_b200_mesh_set_owned",
+    "ithaca_b200_mesh_set_owned", "ithaca_b200_mesh_renumbering",
 ]
 
 _lib = None
@@ -74,7 +74,8 @@ def lib():
         L.ithaca_b200_project.argtypes = [P, I, P]
         L.ithaca_b200_fvc_eval.argtypes = [P, I, I, I, P]
         L.ithaca_b200_proj_timings.argtypes = [P, P, I]
-        L.ithaca_b200_partition_create.argtypes = [ctypes.POINTER(P), L64, L64, L64, P, P, I, I, I]
+        L.ithaca_b200_partition_create.argtypes = [ctypes.POINTER(P), L64, L64, L64, P, P, I, I, I, I]
+        L.ithaca_b200_mesh_renumbering.argtypes = [L64, L64, P, P, P]
         L.ithaca_b200_partition_destroy.argtypes = [P]
         L.ithaca_b200_partition_sizes.argtypes = [P, P]
         L.ithaca_b200_partition_addressing.argtypes = [P, P, P]
@@ -233,18 +234,31 @@ class Pod:
         return out
 
 
+def mesh_renumbering(mesh):
+    """old2new of the library's locality (Cuthill-McKee) ordering; host code."""
+    own = np.ascontiguousarray(mesh.owner, dtype=np.int32)
+    nei = np.ascontiguousarray(mesh.neighbour, dtype=np.int32)
+    out = np.zeros(int(mesh.nCells), dtype=np.int32)
+    if lib().ithaca_b200_mesh_renumbering(int(mesh.nCells), int(mesh.nInt), _ptr(own), _ptr(nei), _ptr(out)):
+        raise IthacaB200Error("mesh_renumbering: bad argument")
+    return out
+
+
 class Partition:
     """One rank's shard of a mesh: contiguous owned cell range + halo layers (host code of the library, no GPU needed).
     Addressing in the form of decomposePar's cellProcAddressing / faceProcAddressing
     (src/ITHACA_CORE/ITHACAparallel/ITHACAparallel.C:43-74)."""
 
-    def __init__(self, mesh, rank, nranks, halo_layers=2):
+    METHODS = {"label": 0, "locality": 1}
+
+    def __init__(self, mesh, rank, nranks, halo_layers=2, method="label"):
         self.L = lib()
         self.p = ctypes.c_void_p()
         self._own = np.ascontiguousarray(mesh.owner, dtype=np.int32)
         self._nei = np.ascontiguousarray(mesh.neighbour, dtype=np.int32)
         rc = self.L.ithaca_b200_partition_create(ctypes.byref(self.p), int(mesh.nCells), int(mesh.nInt), int(mesh.nBnd),
-                                                 _ptr(self._own), _ptr(self._nei), rank, nranks, halo_layers)
+                                                 _ptr(self._own), _ptr(self._nei), rank, nranks, halo_layers,
+                                                 self.METHODS[method])
         if rc:
             raise IthacaB200Error("partition_create: bad argument (status %d)" % rc)
         sz = np.zeros(5, dtype=np.int64)

@@ -11,6 +11,11 @@
 #include <algorithm>
 #include <vector>
 
+namespace ib200 {
+void mesh_renumber(long long nCells, long long nInt, const int* owner, const int* neigh, std::vector<int>& old2new,
+                   std::vector<int>& fnew2old);   // renumber.cu
+}
+
 struct ithaca_b200_partition {
     int64_t nCells = 0, nInt = 0, nBnd = 0;          // global mesh
     int64_t nOwned = 0, nLocInt = 0, nLocBnd = 0, nCut = 0;
@@ -22,12 +27,12 @@ struct ithaca_b200_partition {
 extern "C" {
 
 int ithaca_b200_partition_create(ithaca_b200_partition_t** out, int64_t nCells, int64_t nInt, int64_t nBnd, const int32_t* owner,
-                                 const int32_t* neighbour, int rank, int nranks, int halo)
+                                 const int32_t* neighbour, int rank, int nranks, int halo, int method)
 {
     if (!out) return IB200_ERR_ARG;
     *out = nullptr;
     if (nCells <= 0 || nInt < 0 || nBnd < 0 || !owner || (!neighbour && nInt > 0) || rank < 0 || nranks < 1 || rank >= nranks ||
-        halo < 0 || nCells >= 0x7fffffffLL || nInt + nBnd >= 0x7fffffffLL)
+        halo < 0 || (method != IB200_PART_LABEL_RANGE && method != IB200_PART_LOCALITY_RANGE) || nCells >= 0x7fffffffLL || nInt + nBnd >= 0x7fffffffLL)
         return IB200_ERR_ARG;
     for (int64_t f = 0; f < nInt + nBnd; f++)
         if (owner[f] < 0 || owner[f] >= nCells || (f < nInt && (neighbour[f] < 0 || neighbour[f] >= nCells))) return IB200_ERR_ARG;
@@ -38,7 +43,14 @@ int ithaca_b200_partition_create(ithaca_b200_partition_t** out, int64_t nCells, 
     p->nOwned = c1 - c0;
     // level[c]: 0 owned, L = halo layer L, -1 outside
     std::vector<signed char> level((size_t)nCells, -1);
-    for (int64_t c = c0; c < c1; c++) level[c] = 0;
+    if (method == IB200_PART_LOCALITY_RANGE) {
+        std::vector<int> old2new, fnew2old;
+        ib200::mesh_renumber(nCells, nInt, owner, neighbour, old2new, fnew2old);
+        for (int64_t c = 0; c < nCells; c++)
+            if (old2new[c] >= c0 && old2new[c] < c1) level[c] = 0;
+    } else {
+        for (int64_t c = c0; c < c1; c++) level[c] = 0;
+    }
     const int nl = std::min(halo, 120);
     for (int L = 1; L <= nl; L++) {
         bool any = false;
@@ -51,7 +63,8 @@ int ithaca_b200_partition_create(ithaca_b200_partition_t** out, int64_t nCells, 
     }
     p->g2l.assign((size_t)nCells, -1);
     p->cpa.reserve((size_t)(c1 - c0));
-    for (int64_t c = c0; c < c1; c++) { p->g2l[c] = (int32_t)p->cpa.size(); p->cpa.push_back((int32_t)c); }
+    for (int64_t c = 0; c < nCells; c++)
+        if (level[c] == 0) { p->g2l[c] = (int32_t)p->cpa.size(); p->cpa.push_back((int32_t)c); }
     for (int64_t c = 0; c < nCells; c++)
         if (level[c] > 0) { p->g2l[c] = (int32_t)p->cpa.size(); p->cpa.push_back((int32_t)c); }
     std::vector<int32_t> cut;
@@ -68,6 +81,17 @@ int ithaca_b200_partition_create(ithaca_b200_partition_t** out, int64_t nCells, 
     p->nCut = (int64_t)cut.size();
     p->fpa.insert(p->fpa.end(), cut.begin(), cut.end());
     *out = p;
+    return IB200_OK;
+}
+
+int ithaca_b200_mesh_renumbering(int64_t nCells, int64_t nInt, const int32_t* owner, const int32_t* neighbour, int32_t* old2new)
+{
+    if (nCells <= 0 || nInt < 0 || !old2new || (nInt > 0 && (!owner || !neighbour)) || nCells >= 0x7fffffffLL) return IB200_ERR_ARG;
+    for (int64_t f = 0; f < nInt; f++)
+        if (owner[f] < 0 || owner[f] >= nCells || neighbour[f] < 0 || neighbour[f] >= nCells) return IB200_ERR_ARG;
+    std::vector<int> o2n, f2o;
+    ib200::mesh_renumber(nCells, nInt, owner, neighbour, o2n, f2o);
+    std::copy(o2n.begin(), o2n.end(), old2new);
     return IB200_OK;
 }
 

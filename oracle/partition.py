@@ -18,14 +18,61 @@ def cell_range(nCells, rank, nranks):
     return (rank * nCells) // nranks, ((rank + 1) * nCells) // nranks
 
 
-def partition(nCells, owner, neighbour, nInt, rank, nranks, halo_layers=2):
-    """Returns dict(cpa, fpa, nOwned, nLocalInt, nLocalBnd, nCut). owner: nInt+nBnd labels, neighbour: nInt labels."""
+def cuthill_mckee(nCells, owner, neighbour, nInt):
+    """Restatement of the product's locality ordering (ithaca-fv_b200/csrc/renumber.cu: mesh_renumber), pure Python
+    (small meshes only). Returns old2new. Rule: for every connected component, in order of its lowest unvisited label,
+    a breadth-first search from that label finds a pseudo-peripheral cell (the LAST cell it reaches); the numbering is
+    the breadth-first order from there, the newly reached neighbours of a cell appended by (degree, label)."""
+    own = np.asarray(owner, dtype=np.int64)[:nInt]
+    nei = np.asarray(neighbour, dtype=np.int64)[:nInt]
+    adj = [[] for _ in range(nCells)]
+    for o, n in zip(own.tolist(), nei.tolist()):   # adjacency in face order (only its content matters: lists are sorted)
+        adj[o].append(n)
+        adj[n].append(o)
+    deg = [len(a) for a in adj]
+
+    def bfs(start, mark, out):
+        out.append(start)
+        mark[start] = True
+        head = len(out) - 1
+        while head < len(out):
+            c = out[head]
+            head += 1
+            nb = []
+            for x in adj[c]:
+                if not mark[x]:
+                    mark[x] = True
+                    nb.append(x)
+            nb.sort(key=lambda x: (deg[x], x))
+            out.extend(nb)
+
+    seen = [False] * nCells
+    order = []
+    for c0 in range(nCells):
+        if seen[c0]:
+            continue
+        probe_mark, probe = list(seen), []
+        bfs(c0, probe_mark, probe)
+        bfs(probe[-1], seen, order)
+    old2new = np.zeros(nCells, dtype=np.int32)
+    old2new[np.asarray(order, dtype=np.int64)] = np.arange(nCells, dtype=np.int32)
+    return old2new
+
+
+def partition(nCells, owner, neighbour, nInt, rank, nranks, halo_layers=2, old2new=None):
+    """Returns dict(cpa, fpa, nOwned, nLocalInt, nLocalBnd, nCut). owner: nInt+nBnd labels, neighbour: nInt labels.
+    old2new = None: owned cells are the label range (IB200_PART_LABEL_RANGE); else the cells whose position in that
+    ordering falls in the range (IB200_PART_LOCALITY_RANGE)."""
     owner = np.asarray(owner, dtype=np.int64)
     nei = np.asarray(neighbour, dtype=np.int64)[:nInt]
     own_i = owner[:nInt]
     c0, c1 = cell_range(nCells, rank, nranks)
     level = np.full(nCells, -1, dtype=np.int64)
-    level[c0:c1] = 0
+    if old2new is None:
+        level[c0:c1] = 0
+    else:
+        o2n = np.asarray(old2new, dtype=np.int64)
+        level[(o2n >= c0) & (o2n < c1)] = 0
     for L in range(1, halo_layers + 1):
         # face neighbours of layer L-1 that are still outside (simultaneous update = breadth-first layer)
         grow_n = (level[own_i] == L - 1) & (level[nei] < 0)
@@ -35,7 +82,7 @@ def partition(nCells, owner, neighbour, nInt, rank, nranks, halo_layers=2):
             break
         level[new] = L
     halo = np.flatnonzero(level > 0)
-    cpa = np.concatenate([np.arange(c0, c1), halo]).astype(np.int32)
+    cpa = np.concatenate([np.flatnonzero(level == 0), halo]).astype(np.int32)
     inside = level >= 0
     lo, ln = inside[own_i], inside[nei]
     f_int = np.flatnonzero(lo & ln)

@@ -45,6 +45,36 @@ def test_addressing_matches_oracle_bit_exact(mesh, nranks, halo):
     assert np.all(owned == 1)  # every cell owned by exactly one rank
 
 
+def test_locality_ordering_matches_restatement(mesh):
+    """The library's Cuthill-McKee ordering equals the oracle's restatement label for label."""
+    o2n = pkg.mesh_renumbering(mesh)
+    ref = op.cuthill_mckee(mesh.nCells, mesh.owner, mesh.neighbour, mesh.nInt)
+    assert o2n.dtype == np.int32 and np.array_equal(o2n, ref)
+    assert np.array_equal(np.sort(o2n), np.arange(mesh.nCells))
+
+
+@pytest.mark.parametrize("nranks", [2, 3, 8])
+def test_locality_partition_matches_oracle_bit_exact(mesh, nranks):
+    o2n = op.cuthill_mckee(mesh.nCells, mesh.owner, mesh.neighbour, mesh.nInt)
+    owned = np.zeros(mesh.nCells, dtype=np.int64)
+    shard_cells = 0
+    for rank in range(nranks):
+        ref = op.partition(mesh.nCells, mesh.owner, mesh.neighbour, mesh.nInt, rank, nranks, 2, old2new=o2n)
+        p = pkg.Partition(mesh, rank, nranks, 2, method="locality")
+        cpa, fpa = p.addressing()
+        assert np.array_equal(cpa, ref["cpa"]) and np.array_equal(fpa, ref["fpa"])
+        assert (p.nOwned, p.nLocalInt, p.nLocalBnd, p.nCut) == (ref["nOwned"], ref["nLocalInt"], ref["nLocalBnd"], ref["nCut"])
+        b, e = pkg.cell_range(mesh.nCells, rank, nranks)
+        assert np.array_equal(np.sort(o2n[cpa[:p.nOwned]]), np.arange(b, e))
+        owned[cpa[:p.nOwned]] += 1
+        shard_cells += p.nLocalCells
+        p.close()
+    assert np.all(owned == 1)
+    # compact shards: the halo stays a fraction of the mesh (a label range of a randomly relabelled mesh drags in all of it)
+    if nranks == 2:
+        assert shard_cells < 1.7 * mesh.nCells
+
+
 def test_owned_cells_see_all_their_faces(mesh):
     nranks, halo = 3, 2
     for rank in range(nranks):
@@ -54,7 +84,7 @@ def test_owned_cells_see_all_their_faces(mesh):
         # cut faces only touch cells of the outermost halo layer: no owned cell on either side
         cut = g[p.nLocalInt + p.nLocalBnd:]
         b, e = pkg.cell_range(mesh.nCells, rank, nranks)
-        for arr in (mesh.owner[cut], mesh.neighbour[cut]):
+        for arr in (mesh.owner[cut], mesh.neighbour[cut[cut < mesh.nInt]]):
             assert not np.any((arr >= b) & (arr < e))
         # flipped sign exactly when the shard-side cell is the global neighbour
         inside = np.zeros(mesh.nCells, dtype=bool)

@@ -141,8 +141,8 @@ def test_projection_error_paths(pkg):
     p.close()
 
 
-@pytest.mark.parametrize("nranks,name", [(2, "tutorial04"), (3, "cyl")])
-def test_sharded_projection_sums_to_the_global_operators(pkg, pod, nranks, name):
+@pytest.mark.parametrize("nranks,name,method", [(2, "tutorial04", "label"), (3, "cyl", "locality"), (4, "tutorial04", "locality")])
+def test_sharded_projection_sums_to_the_global_operators(pkg, pod, nranks, name, method):
     """every rank projects on its shard mesh (owned cells + 2 halo layers, halo cells weigh 0); the sum
     over ranks -- what the per-operator all-reduce forms -- equals the single-mesh operators to 1e-10."""
     mesh = meshes()[name]()
@@ -155,7 +155,7 @@ def test_sharded_projection_sums_to_the_global_operators(pkg, pod, nranks, name)
     acc = {k: np.zeros_like(v) for k, v in ref.items()}
     pr = pkg.Projector(pod)
     for rank in range(nranks):
-        part = pkg.Partition(mesh, rank, nranks, 2)
+        part = pkg.Partition(mesh, rank, nranks, 2, method=method)
         pr.set_mesh_shard(mesh, part, corrected=True)
         pr.set_basis("U", [part.gather(u, "cell", 3) for u in U], [part.gather(u, "bnd", 3) for u in Ub])
         pr.set_basis("P", [part.gather(p, "cell", 1) for p in P], [part.gather(p, "bnd", 1) for p in Pb])
