@@ -165,6 +165,7 @@ def run(pod, torch, dev, which="c4", N=50, Np=10, reps=2, hbm_peak=6540.0, dmma_
         out["sharding"] = shard
     if check:  # size-independent properties (the oracle parity proper is tests/test_proj_gpu.py)
         M = ops["M"]
-        out["checks"] = {"M_symmetric": bool(np.array_equal(M, M.T)),
+        out["checks"] = {"M_symmetric": bool(np.array_equal(M, M.T)),   # bitwise for one rank; the all-reduce order breaks it at N > 1
+                         "M_asymmetry_rel": float(np.abs(M - M.T).max() / np.abs(M).max()),
                          "C_fused_vs_materialised_rel": float(np.abs(ops["C"] - ops["Cmat"]).max() / np.abs(ops["Cmat"]).max())}
     return out, mesh, (U, Ub, P, Pb), ops

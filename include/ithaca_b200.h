@@ -111,6 +111,32 @@ int ithaca_b200_pod_lift(ithaca_b200_t* h, int r, int norm_kind, double* const* 
  * Foam2Eigen.C:272-411); out: rows*r col-major. Host pointers. Must follow pod_lift. */
 int ithaca_b200_pod_lift_patch(ithaca_b200_t* h, const double* Sbc, int64_t rows, double* out);
 
+/* ---- the callers either side of getModes: snapshot projection and reconstruction ----------
+ * All of them work on the snapshot matrix of pod_upload and on the RESIDENT MODES: the result of pod_lift, or a mode
+ * list uploaded with pod_set_modes. nmodes = 0 means all resident modes (the reference's "Nmodes == 0" convention). */
+
+/* Install r modes (nCells*dim doubles each, host or device) as the resident modes; requires pod_upload (sizes). */
+int ithaca_b200_pod_set_modes(ithaca_b200_t* h, const double* const* mode_ptrs, int r);
+
+/* Modes::project over a field list (src/ITHACA_CORE/Containers/Modes.C:228-290):
+ *   proj_type 0 = "G": Phi_n^T diag(V) S;  1 = "F": Phi_n^T S (the list overload replaces vol by ones, :246-249, :271-275).
+ * out: nmodes x m col-major (host). All-reduced over ranks. */
+int ithaca_b200_pod_project(ithaca_b200_t* h, int nmodes, int proj_type, double* out);
+
+/* ITHACAutilities::getMassMatrix over the mode list (ITHACAcoeffsMass.C:67-118): Phi_n^T diag(V) Phi_n, nmodes x nmodes. */
+int ithaca_b200_pod_modes_mass(ithaca_b200_t* h, int nmodes, double* out);
+
+/* ITHACAutilities::getCoeffs over the snapshot list (ITHACAcoeffsMass.C:348-388 per snapshot, :424-443):
+ * coeff(:, i) = M.fullPivLu().solve(Phi_n^T diag(V) s_i), M = the mass matrix above. out: nmodes x m col-major. */
+int ithaca_b200_pod_get_coeffs(ithaca_b200_t* h, int nmodes, double* out);
+
+/* Modes::reconstruct, internal field (Modes.C:294-305): out_j = Phi[:, 0:nmodes] * coeff(:, j) for j < k.
+ * coeff: nmodes x k col-major (host). clip_negative != 0 applies the reference's "nut" rule (negative entries -> 0).
+ * out_ptrs[j]: nCells*dim doubles (host or device). Boundary patches: ithaca_b200_pod_lift_patch-style rows are the
+ * caller's (EigenModes[i+1] are small host matrices in the reference too). */
+int ithaca_b200_pod_reconstruct(ithaca_b200_t* h, int nmodes, const double* coeff, int k, int clip_negative,
+                                double* const* out_ptrs);
+
 /* ---- Galerkin projection: steadyNS::projectSUP term builders ---------------------------------------
  * (src/ITHACA_FOMPROBLEMS/steadyNS/steadyNS.C:556-707 calls :883-1137; inherited by unsteadyNS,
  *  src/ITHACA_FOMPROBLEMS/unsteadyNS/unsteadyNS.H:61). Scheme set: Gauss linear (grad, div, interpolate),

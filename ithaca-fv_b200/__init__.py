@@ -23,6 +23,8 @@ SYMBOLS = [
     "ithaca_b200_pod_upload", "ithaca_b200_pod_gram", "ithaca_b200_pod_eig", "ithaca_b200_pod_set_gram",
     "ithaca_b200_pod_postprocess_eigenvalues", "ithaca_b200_pod_lift", "ithaca_b200_pod_lift_patch",
     "ithaca_b200_dmma_peak",
+    "ithaca_b200_pod_set_modes", "ithaca_b200_pod_project", "ithaca_b200_pod_modes_mass", "ithaca_b200_pod_get_coeffs",
+    "ithaca_b200_pod_reconstruct",
     "ithaca_b200_mesh_upload", "ithaca_b200_mesh_addressing", "ithaca_b200_basis_upload", "ithaca_b200_project",
     "ithaca_b200_fvc_eval", "ithaca_b200_proj_timings",
     "ithaca_b200_partition_create", "ithaca_b200_partition_destroy", "ithaca_b200_partition_sizes",
@@ -68,6 +70,11 @@ def lib():
         L.ithaca_b200_pod_lift.argtypes = [P, I, I, P, P]
         L.ithaca_b200_pod_lift_patch.argtypes = [P, P, L64, P]
         L.ithaca_b200_dmma_peak.argtypes = [I, ctypes.POINTER(D)]
+        L.ithaca_b200_pod_set_modes.argtypes = [P, P, I]
+        L.ithaca_b200_pod_project.argtypes = [P, I, I, P]
+        L.ithaca_b200_pod_modes_mass.argtypes = [P, I, P]
+        L.ithaca_b200_pod_get_coeffs.argtypes = [P, I, P]
+        L.ithaca_b200_pod_reconstruct.argtypes = [P, I, P, I, I, P]
         L.ithaca_b200_mesh_upload.argtypes = [P, L64, L64, L64] + [P] * 10
         L.ithaca_b200_mesh_addressing.argtypes = [P, P, P, P, ctypes.POINTER(ctypes.c_uint64)]
         L.ithaca_b200_basis_upload.argtypes = [P, I, P, P, I]
@@ -225,7 +232,59 @@ class Pod:
             Phi = np.zeros((self.nCells * self.dim, r), order="F")
             arr = (ctypes.c_void_p * r)(*[Phi.ctypes.data + i * Phi.strides[1] for i in range(r)])
         self._chk(self.L.ithaca_b200_pod_lift(self.h, r, 0 if norm == "L2" else 1, arr, nf.ctypes.data))
+        self.r = r
         return Phi, nf
+
+    # ---- callers either side of getModes: Modes::project / getCoeffs / Modes::reconstruct on the resident modes ----
+    def set_modes(self, modes):
+        """modes: list of r arrays/tensors (nCells*dim doubles each) or a Fortran-ordered (Nd, r) array."""
+        if isinstance(modes, np.ndarray) and modes.ndim == 2:
+            assert modes.flags.f_contiguous and modes.dtype == np.float64
+            ptrs = [modes.ctypes.data + j * modes.strides[1] for j in range(modes.shape[1])]
+        else:
+            ptrs = [_ptr(x) for x in modes]
+        self._keep_modes = modes
+        arr = (ctypes.c_void_p * len(ptrs))(*ptrs)
+        self._chk(self.L.ithaca_b200_pod_set_modes(self.h, arr, len(ptrs)))
+        self.r = len(ptrs)
+
+    def project(self, nmodes, proj_type="G", r=None):
+        """Modes::project over the uploaded snapshots (Modes.C:228-290): (nmodes or all) x m."""
+        if proj_type not in ("G", "F"):
+            raise IthacaB200Error("Projection type can be G for Galerking or F for Frobenius")
+        n = nmodes if nmodes else (r if r is not None else getattr(self, "r", 0))
+        out = np.zeros((n, self.m), order="F")
+        self._chk(self.L.ithaca_b200_pod_project(self.h, nmodes, 0 if proj_type == "G" else 1, out.ctypes.data))
+        return out
+
+    def modes_mass(self, nmodes, r=None):
+        n = nmodes if nmodes else (r if r is not None else getattr(self, "r", 0))
+        out = np.zeros((n, n), order="F")
+        self._chk(self.L.ithaca_b200_pod_modes_mass(self.h, nmodes, out.ctypes.data))
+        return out
+
+    def get_coeffs(self, nmodes, r=None):
+        """ITHACAutilities::getCoeffs over the uploaded snapshots (ITHACAcoeffsMass.C:348-443)."""
+        n = nmodes if nmodes else (r if r is not None else getattr(self, "r", 0))
+        out = np.zeros((n, self.m), order="F")
+        self._chk(self.L.ithaca_b200_pod_get_coeffs(self.h, nmodes, out.ctypes.data))
+        return out
+
+    def reconstruct(self, coeff, clip_negative=False, out=None):
+        """Modes::reconstruct (Modes.C:294-305): Phi[:, :Nmodes] @ coeff, coeff (Nmodes, k)."""
+        coeff = np.asfortranarray(coeff, dtype=np.float64)
+        if coeff.ndim == 1:
+            coeff = np.asfortranarray(coeff[:, None])
+        n, k = coeff.shape
+        R = None
+        if out is None:
+            R = np.zeros((self.nCells * self.dim, k), order="F")
+            ptrs = [R.ctypes.data + j * R.strides[1] for j in range(k)]
+        else:
+            ptrs = [_ptr(o) for o in out]
+        arr = (ctypes.c_void_p * k)(*ptrs)
+        self._chk(self.L.ithaca_b200_pod_reconstruct(self.h, n, coeff.ctypes.data, k, 1 if clip_negative else 0, arr))
+        return R
 
     def lift_patch(self, Sbc, r):
         Sbc = np.asfortranarray(Sbc, dtype=np.float64)

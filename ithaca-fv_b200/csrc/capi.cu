@@ -319,7 +319,7 @@ int ithaca_b200_pod_upload(ithaca_b200_t* h, const double* const* snap_ptrs, int
     tstop(h, T_UPLOAD);
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
     h->m = m; h->dim = dim; h->Nd = Nd; h->ld = ld;
-    h->have_gram = h->have_eig = h->have_lift = false;
+    h->have_gram = h->have_eig = h->have_lift = h->have_modes = false;
     return IB200_OK;
 }
 
@@ -426,6 +426,7 @@ int ithaca_b200_pod_lift(ithaca_b200_t* h, int r, int norm_kind, double* const* 
     tstop(h, T_DOWNLOAD);
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
     h->have_lift = true;
+    h->have_modes = true;
     return IB200_OK;
 }
 
@@ -453,6 +454,171 @@ int ithaca_b200_pod_lift_patch(ithaca_b200_t* h, const double* Sbc, int64_t rows
     cudaFree(dIn);
     cudaFree(dOut);
     return rc;
+}
+
+// ---- snapshot projection / coefficients / reconstruction on the resident modes ----------------
+
+int ithaca_b200_pod_set_modes(ithaca_b200_t* h, const double* const* mode_ptrs, int r)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!mode_ptrs || r <= 0) { set_error(h, "pod_set_modes: bad argument"); return IB200_ERR_ARG; }
+    if (h->Nd <= 0) { set_error(h, "pod_set_modes: call pod_upload first (it fixes the field size)"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    const size_t need = (size_t)h->ld * r * sizeof(double);
+    if (need > h->dPhi_cap) {
+        if (h->dPhi) cudaFree(h->dPhi);
+        h->dPhi = nullptr; h->dPhi_cap = 0;
+        IB_CUDA(h, cudaMalloc(&h->dPhi, need));
+        h->dPhi_cap = need;
+    }
+    for (int i = 0; i < r; i++) {
+        if (!mode_ptrs[i]) { set_error(h, "pod_set_modes: null mode pointer"); return IB200_ERR_ARG; }
+        IB_CUDA(h, cudaMemcpyAsync(h->dPhi + (size_t)i * h->ld, mode_ptrs[i], (size_t)h->Nd * sizeof(double), cudaMemcpyDefault, h->stream));
+    }
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->r = r;
+    h->have_modes = true;
+    h->have_lift = false;   // lift_patch needs the eigenvectors and norm factors of a pod_lift
+    return IB200_OK;
+}
+
+// Phi_n^T diag(w) X on the device into a fresh buffer (n x cols, col-major), all-reduced. X = dS (cols = m) or dPhi (cols = n).
+static int modes_contract(ithaca_b200* h, int n, bool weighted, bool with_modes, double** dOut)
+{
+    const int cols = with_modes ? n : h->m;
+    IB_CUDA(h, cudaMalloc(dOut, (size_t)n * cols * sizeof(double)));
+    int rc = atvb_launch(h, h->dPhi, h->ld, n, with_modes ? h->dPhi : h->dS, h->ld, cols, h->Nd, weighted ? h->dV : nullptr, h->dim,
+                         with_modes ? 1 : 0, *dOut, 1, 0x7fffffff, 0, n);
+    if (!rc) rc = allreduce_sum(h, *dOut, (size_t)n * cols);
+    if (rc) { cudaFree(*dOut); *dOut = nullptr; }
+    return rc;
+}
+
+static int modes_args(ithaca_b200* h, const char* who, int& nmodes, const void* out)
+{
+    if (!h->have_modes || h->Nd <= 0) { set_error(h, std::string(who) + ": no resident modes (call pod_lift or pod_set_modes)"); return IB200_ERR_ARG; }
+    if (!out) { set_error(h, std::string(who) + ": null output"); return IB200_ERR_ARG; }
+    if (nmodes == 0) nmodes = h->r;
+    if (nmodes < 0 || nmodes > h->r) {
+        set_error(h, std::string(who) + ": The Number of requested modes is larger then the available quantity.");
+        return IB200_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_project(ithaca_b200_t* h, int nmodes, int proj_type, double* out)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (proj_type != 0 && proj_type != 1) { set_error(h, "pod_project: Projection type can be G for Galerking or F for Frobenius"); return IB200_ERR_ARG; }
+    int rc = modes_args(h, "pod_project", nmodes, out);
+    if (rc) return rc;
+    double* d = nullptr;
+    if ((rc = modes_contract(h, nmodes, proj_type == 0, false, &d))) return rc;
+    cudaError_t e = cudaMemcpyAsync(out, d, (size_t)nmodes * h->m * sizeof(double), cudaMemcpyDefault, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(d);
+    IB_CUDA(h, e);
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_modes_mass(ithaca_b200_t* h, int nmodes, double* out)
+{
+    if (!h) return IB200_ERR_ARG;
+    int rc = modes_args(h, "pod_modes_mass", nmodes, out);
+    if (rc) return rc;
+    double* d = nullptr;
+    if ((rc = modes_contract(h, nmodes, true, true, &d))) return rc;
+    cudaError_t e = cudaMemcpyAsync(out, d, (size_t)nmodes * nmodes * sizeof(double), cudaMemcpyDefault, h->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(d);
+    IB_CUDA(h, e);
+    return IB200_OK;
+}
+
+// x = A^-1 B by LU with complete pivoting (what Eigen's fullPivLu().solve does), A: n x n, B: n x k, col-major, in place in B.
+// Returns false when a pivot is exactly zero.
+static bool full_piv_lu_solve(std::vector<double>& A, int n, double* B, int k)
+{
+    std::vector<int> colperm(n);
+    for (int i = 0; i < n; i++) colperm[i] = i;
+    for (int s = 0; s < n; s++) {
+        int pr = s, pc = s;
+        double best = -1.0;
+        for (int c = s; c < n; c++)
+            for (int r = s; r < n; r++)
+                if (std::fabs(A[r + (size_t)c * n]) > best) { best = std::fabs(A[r + (size_t)c * n]); pr = r; pc = c; }
+        if (!(best > 0.0)) return false;
+        if (pr != s) {
+            for (int c = 0; c < n; c++) std::swap(A[s + (size_t)c * n], A[pr + (size_t)c * n]);
+            for (int j = 0; j < k; j++) std::swap(B[s + (size_t)j * n], B[pr + (size_t)j * n]);
+        }
+        if (pc != s) {
+            for (int r = 0; r < n; r++) std::swap(A[r + (size_t)s * n], A[r + (size_t)pc * n]);
+            std::swap(colperm[s], colperm[pc]);
+        }
+        const double piv = A[s + (size_t)s * n];
+        for (int r = s + 1; r < n; r++) {
+            const double l = A[r + (size_t)s * n] / piv;
+            if (l == 0.0) continue;
+            for (int c = s + 1; c < n; c++) A[r + (size_t)c * n] -= l * A[s + (size_t)c * n];
+            for (int j = 0; j < k; j++) B[r + (size_t)j * n] -= l * B[s + (size_t)j * n];
+        }
+    }
+    std::vector<double> y(n);
+    for (int j = 0; j < k; j++) {
+        double* b = B + (size_t)j * n;
+        for (int r = n - 1; r >= 0; r--) {
+            double v = b[r];
+            for (int c = r + 1; c < n; c++) v -= A[r + (size_t)c * n] * y[c];
+            y[r] = v / A[r + (size_t)r * n];
+        }
+        for (int c = 0; c < n; c++) b[colperm[c]] = y[c];
+    }
+    return true;
+}
+
+int ithaca_b200_pod_get_coeffs(ithaca_b200_t* h, int nmodes, double* out)
+{
+    if (!h) return IB200_ERR_ARG;
+    int rc = modes_args(h, "pod_get_coeffs", nmodes, out);
+    if (rc) return rc;
+    std::vector<double> M((size_t)nmodes * nmodes);
+    if ((rc = ithaca_b200_pod_modes_mass(h, nmodes, M.data()))) return rc;
+    if ((rc = ithaca_b200_pod_project(h, nmodes, 0, out))) return rc;
+    if (!full_piv_lu_solve(M, nmodes, out, h->m)) { set_error(h, "pod_get_coeffs: the mass matrix of the modes is singular"); return IB200_ERR_ARG; }
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_reconstruct(ithaca_b200_t* h, int nmodes, const double* coeff, int k, int clip_negative, double* const* out_ptrs)
+{
+    if (!h) return IB200_ERR_ARG;
+    int rc = modes_args(h, "pod_reconstruct", nmodes, out_ptrs);
+    if (rc) return rc;
+    if (!coeff || k <= 0) { set_error(h, "pod_reconstruct: bad argument"); return IB200_ERR_ARG; }
+    const int KB = 8;   // columns per pass (RC_K in lift.cu)
+    double *dC = nullptr, *dOut = nullptr;
+    IB_CUDA(h, cudaMalloc(&dC, (size_t)nmodes * k * sizeof(double)));
+    if (cudaMalloc(&dOut, (size_t)h->ld * KB * sizeof(double)) != cudaSuccess) {
+        cudaFree(dC);
+        set_error(h, "pod_reconstruct: out of device memory");
+        return IB200_ERR_CUDA;
+    }
+    cudaError_t e = cudaMemcpyAsync(dC, coeff, (size_t)nmodes * k * sizeof(double), cudaMemcpyDefault, h->stream);
+    for (int j0 = 0; j0 < k && e == cudaSuccess && rc == IB200_OK; j0 += KB) {
+        const int kc = std::min(KB, k - j0);
+        rc = reconstruct_launch(h, nmodes, dC + (size_t)j0 * nmodes, kc, clip_negative, dOut);
+        for (int j = 0; j < kc && e == cudaSuccess && rc == IB200_OK; j++) {
+            if (!out_ptrs[j0 + j]) { set_error(h, "pod_reconstruct: null output pointer"); rc = IB200_ERR_ARG; break; }
+            e = cudaMemcpyAsync(out_ptrs[j0 + j], dOut + (size_t)j * h->ld, (size_t)h->Nd * sizeof(double), cudaMemcpyDefault, h->stream);
+        }
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(dC);
+    cudaFree(dOut);
+    if (rc) return rc;
+    IB_CUDA(h, e);
+    return IB200_OK;
 }
 
 }  // extern "C"

@@ -144,6 +144,8 @@ int eig_launch(ithaca_b200* h, int* sweeps);
 // lift.cu
 int lift_launch(ithaca_b200* h, int r, int norm_kind);
 int lift_patch_launch(ithaca_b200* h, const double* dSbc, int64_t rows, double* dOut);
+// out[:, j] = Phi[:, 0:nmodes] * C[:, j] for j < kc <= 8 (C: nmodes x kc col-major on the device); out columns of ld doubles
+int reconstruct_launch(ithaca_b200* h, int nmodes, const double* dC, int kc, int clip, double* dOut);
 // gram.cu: general weighted contraction  out(i,j) = sum_k A(k,i) * V[k/dim] * B(k,j)  (V == nullptr: unweighted).
 // A: Ma columns of lda doubles, B: Nb columns of ldb doubles, both with K valid rows (K-contiguous columns).
 // symmetric != 0: B == A, only the lower triangle is computed and mirrored. out(i,j) is written to
@@ -198,6 +200,7 @@ struct ithaca_b200 {
     double* dNorm = nullptr;  // rpad doubles: squared norms then norm factors
     int norm_cap = 0;
     bool have_lift = false;
+    bool have_modes = false;   // dPhi holds h->r modes (from pod_lift or pod_set_modes)
     void* dJobs = nullptr;
     size_t dJobs_cap = 0;
     // dim-times repeated weight vectors of the contraction kernel (gram.cu), keyed on (V, dim, K, vol_gen)

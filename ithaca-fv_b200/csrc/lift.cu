@@ -305,6 +305,44 @@ int lift_launch(ithaca_b200* h, int r, int norm_kind)
     return IB200_OK;
 }
 
+// ---- Modes::reconstruct (Containers/Modes.C:294-305): out_j = Phi[:, 0:n] c_j, up to RC_K columns per launch -------------
+// HBM-bound streaming pass: one thread per row, the n x kc coefficient block in shared memory, kc accumulators in
+// registers; Phi is read once per launch (coalesced), each output column written once.
+constexpr int RC_K = 8;
+__global__ void __launch_bounds__(256)
+reconstruct_kernel(const double* __restrict__ Phi, long long Nd, long long ld, int n, const double* __restrict__ C, int kc,
+                   int clip, double* __restrict__ out)
+{
+    extern __shared__ double sc[];   // [n][RC_K]
+    for (int idx = threadIdx.x; idx < n * RC_K; idx += blockDim.x) {
+        const int i = idx / RC_K, j = idx % RC_K;
+        sc[idx] = (j < kc) ? C[(size_t)i + (size_t)j * n] : 0.0;
+    }
+    __syncthreads();
+    for (long long row = blockIdx.x * (long long)blockDim.x + threadIdx.x; row < Nd; row += (long long)gridDim.x * blockDim.x) {
+        double acc[RC_K];
+#pragma unroll
+        for (int j = 0; j < RC_K; j++) acc[j] = 0.0;
+        for (int i = 0; i < n; i++) {
+            const double p = Phi[(size_t)i * ld + row];
+#pragma unroll
+            for (int j = 0; j < RC_K; j++) acc[j] += p * sc[i * RC_K + j];
+        }
+#pragma unroll
+        for (int j = 0; j < RC_K; j++)
+            if (j < kc) out[(size_t)j * ld + row] = (clip && acc[j] < 0.0) ? 0.0 : acc[j];
+    }
+}
+
+int reconstruct_launch(ithaca_b200* h, int nmodes, const double* dC, int kc, int clip, double* dOut)
+{
+    const int grid = (int)std::min<long long>((h->Nd + 255) / 256, 16LL * h->num_sms);
+    reconstruct_kernel<<<grid, 256, (size_t)nmodes * RC_K * sizeof(double), h->stream>>>(h->dPhi, h->Nd, h->ld, nmodes, dC, kc, clip, dOut);
+    IB_CUDA(h, cudaGetLastError());
+    h->launches += 1;
+    return IB200_OK;
+}
+
 int lift_patch_launch(ithaca_b200* h, const double* dSbc, int64_t rows, double* dOut)
 {
     const long long total = rows * h->r;

@@ -15,6 +15,8 @@
 //   norm factors: ITHACAPOD/ITHACAPOD.C:196-243
 //   BC lift     : ITHACAPOD/ITHACAPOD.C:245-264
 //   eigenvalue normalisation / cumulative sum: ITHACAPOD/ITHACAPOD.C:281-287
+//   getCoeffs   : ITHACAutilities/ITHACAcoeffsMass.C:348-388, :424-443
+//   Modes::project / reconstruct: Containers/Modes.C:228-290, :294-305
 //
 // Used by: tests/ (checker), tests/golden/make_golden.py (fixture generator),
 // bench.py cpu_baseline / --impl reference (timed CPU baseline). Nothing else.
@@ -204,6 +206,63 @@ int podref_lift(const double* S, i64 Nc, int dim, int m, const double* Vc, const
         if (normfact_out) normfact_out[i] = nf;
     }
     if (modes_out) std::memcpy(modes_out, modesEig.data(), sizeof(double) * Nd * nmodes);
+    return 0;
+}
+
+// getCoeffs over a snapshot list (ITHACAcoeffsMass.C:348-388 per snapshot, :424-443 over the list):
+// b = F^T.topRows(Msize) V snap; a = getMassMatrix(modes, Nmodes).fullPivLu().solve(b). The mass matrix is the
+// 1-list getMassMatrix (ITHACAcoeffsMass.C:67-118, GEMM branch). coeff_out: Msize x nsnap col-major.
+int podref_getcoeffs(const double* S, i64 Nc, int dim, int nsnap, const double* Vc, const double* modes, int nmodes_avail,
+                     int Nmodes, double* coeff_out)
+{
+    const i64 Nd = Nc * dim;
+    const int Msize = (Nmodes == 0) ? nmodes_avail : Nmodes;
+    if (nmodes_avail < Msize) return 1;  // "The Number of requested modes is larger then the available quantity."
+    CMap F(modes, Nd, nmodes_avail);
+    Eigen::VectorXd V = mass_fv(Vc, Nc, dim);
+    Eigen::MatrixXd M_matrix = F.transpose().topRows(Msize) * V.asDiagonal() * F.leftCols(Msize);
+    Eigen::Map<Eigen::MatrixXd> coeff(coeff_out, Msize, nsnap);
+    for (int i = 0; i < nsnap; i++)
+    {
+        CMap snapEigen(S + (size_t)i * Nd, Nd, 1);
+        Eigen::VectorXd b = F.transpose().topRows(Msize) * V.asDiagonal() * snapEigen;
+        Eigen::VectorXd a = M_matrix.fullPivLu().solve(b);
+        coeff.col(i) = a;
+    }
+    return 0;
+}
+
+// Modes::project over a field list (Containers/Modes.C:228-290): projType "G" (0) and "F" (1; this overload
+// REPLACES vol by ones, :246-249 and :271-275, and does not solve with a mass matrix). proj_out: nmodes x nsnap.
+int podref_project(const double* S, i64 Nc, int dim, int nsnap, const double* Vc, const double* modes, int nmodes_avail,
+                   int numberOfModes, int projType, double* proj_out)
+{
+    const i64 Nd = Nc * dim;
+    const int nm = (numberOfModes == 0) ? nmodes_avail : numberOfModes;
+    if (nm > nmodes_avail) return 1;
+    CMap fieldEig(S, Nd, nsnap);
+    CMap EigenModes0(modes, Nd, nmodes_avail);
+    Eigen::VectorXd vol = mass_fv(Vc, Nc, dim);
+    if (projType == 1) vol = Eigen::VectorXd::Ones(vol.size());
+    Eigen::MatrixXd projField = (EigenModes0.leftCols(nm)).transpose() * vol.asDiagonal() * fieldEig;
+    std::memcpy(proj_out, projField.data(), sizeof(double) * nm * nsnap);
+    return 0;
+}
+
+// Modes::reconstruct, internal field (Containers/Modes.C:294-305): InField = EigenModes[0].leftCols(Nmodes) * Coeff,
+// negative entries clipped when the field is called "nut" (clip != 0). Coeff: Nmodes x k col-major.
+int podref_reconstruct(const double* modes, i64 Nd, int nmodes_avail, const double* Coeff, int Nmodes, int k, int clip,
+                       double* out)
+{
+    if (Nmodes > nmodes_avail) return 1;
+    CMap EigenModes0(modes, Nd, nmodes_avail);
+    CMap C(Coeff, Nmodes, k);
+    for (int j = 0; j < k; j++)
+    {
+        Eigen::VectorXd InField = EigenModes0.leftCols(Nmodes) * C.col(j);
+        if (clip) InField = (InField.array() < 0).select(0, InField);
+        std::memcpy(out + (size_t)j * Nd, InField.data(), sizeof(double) * Nd);
+    }
     return 0;
 }
 

@@ -80,3 +80,25 @@ def test_negative_shift_rule():
     assert np.allclose(ev, [4.0, 2.0, 0.5])
     ev, _ = po.eig(G, 2, "spectra")  # only the kept values are inspected: no shift
     assert np.allclose(ev, [3.0, 1.0])
+
+
+@pytest.mark.skipif(not po.ref_available(), reason="oracle/_ref not built")
+def test_project_getcoeffs_reconstruct_restatement_matches_reference_build():
+    """The numpy restatement of getCoeffs / Modes::project / Modes::reconstruct equals the reference's own Eigen
+    expressions (oracle/pod_ref.cpp: ITHACAcoeffsMass.C:348-443, Modes.C:228-305) compiled on the vendored Eigen."""
+    Nc, dim, m, r = 501, 3, 12, 5
+    S = synth.snapshots(Nc, dim, m, 2 * r, 3)
+    V = synth.volumes(Nc, 3)
+    Phi = po.getmodes(S, V, dim, r, "eigen", "L2")["modes"]
+    rng = np.random.default_rng(2)
+    W = Phi @ (np.eye(r) + 0.3 * rng.standard_normal((r, r)))   # non-orthonormal modes: the fullPivLu solve matters
+    for nm in (0, 3):
+        a, b = po.get_coeffs(S, V, dim, W, nm), po.ref_get_coeffs(S, V, dim, W, nm)
+        assert np.abs(a - b).max() <= 1e-12 * np.abs(b).max()
+        for t in ("G", "F"):
+            a, b = po.project(S, V, dim, W, nm, t), po.ref_project(S, V, dim, W, nm, t)
+            assert np.abs(a - b).max() <= 1e-13 * np.abs(b).max()
+    c = rng.standard_normal((4, 3))
+    for clip in (False, True):
+        a, b = po.reconstruct(W, c, clip), po.ref_reconstruct(W, c, clip)
+        assert np.abs(a - b).max() <= 1e-14 * np.abs(b).max()

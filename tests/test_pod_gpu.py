@@ -189,3 +189,37 @@ def test_c1_tutorial_scale_matches_oracle(pkg, pod, dim, solver):
     assert np.all(np.abs(out["evals_norm"][:r] - ref["evals_norm"][:r]) <= 1e-10 * ref["evals_norm"][:r])
     assert np.abs(out["cum"] - ref["cum"]).max() <= 1e-12
     assert modes_rel(out["modes"], ref["modes"]) <= 1e-8
+
+
+@pytest.mark.parametrize("Nc,dim,m,r", [(4099, 3, 37, 6), (10_000, 1, 100, 10), (777, 3, 9, 9)])
+def test_project_getcoeffs_reconstruct_match_oracle(pkg, pod, Nc, dim, m, r):
+    """SURVEY 8(f) rank 2: Modes::project (G / F), getMassMatrix over modes, getCoeffs, Modes::reconstruct on the
+    device-resident snapshots and modes, against the numpy restatement (pinned to the compiled reference expressions by
+    tests/test_oracle_pod.py)."""
+    S = synth.snapshots(Nc, dim, m, 2 * r, 77)
+    V = synth.volumes(Nc, 77)
+    ref = po.getmodes(S, V, dim, r, "eigen", "L2")
+    out = pkg.getModes(pod, S, V, dim, r, "eigen", "L2")          # leaves snapshots + lifted modes resident
+    Phi = out["modes"]
+    for nm in (0, max(1, r // 2)):
+        for t in ("G", "F"):
+            assert rel_max(pod.project(nm, t), po.project(S, V, dim, Phi, nm, t)) <= 1e-12
+        assert rel_max(pod.modes_mass(nm), po.modes_mass(Phi, V, dim, nm)) <= 1e-12
+        assert rel_max(pod.get_coeffs(nm), po.get_coeffs(S, V, dim, Phi, nm)) <= 1e-10
+    # externally supplied modes (not orthonormal: the mass matrix solve matters)
+    rng = np.random.default_rng(5)
+    W = np.asfortranarray(Phi @ (np.eye(r) + 0.3 * rng.standard_normal((r, r))))
+    pod.set_modes(W)
+    assert rel_max(pod.get_coeffs(0), po.get_coeffs(S, V, dim, W, 0)) <= 1e-10
+    coeff = rng.standard_normal((r, 11))
+    assert rel_max(pod.reconstruct(coeff), po.reconstruct(W, coeff)) <= 1e-13
+    clipped = pod.reconstruct(coeff[:2, :3], clip_negative=True)
+    assert np.array_equal(clipped, po.reconstruct(W, coeff[:2, :3], clip=True)) or rel_max(clipped, po.reconstruct(W, coeff[:2, :3], clip=True)) <= 1e-13
+    assert clipped.min() >= 0.0
+    # projecting the snapshots and reconstructing from all m = rank modes returns them (round trip)
+    if r == m:
+        pod.set_modes(np.asfortranarray(Phi))
+        back = pod.reconstruct(pod.get_coeffs(0))
+        assert rel_max(back, S) <= 1e-8
+    with pytest.raises(pkg.IthacaB200Error):
+        pod.get_coeffs(r + 1)
