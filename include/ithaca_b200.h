@@ -169,7 +169,8 @@ int ithaca_b200_mesh_addressing(ithaca_b200_t* h, int32_t* off, int32_t* ent, in
 int ithaca_b200_basis_upload(ithaca_b200_t* h, int which, const double* const* int_ptrs,
                              const double* const* bnd_ptrs, int n);
 
-enum { IB200_OP_M = 0, IB200_OP_B = 1, IB200_OP_K = 2, IB200_OP_P = 3, IB200_OP_C = 4, IB200_OP_C_MATERIALISED = 5 };
+enum { IB200_OP_M = 0, IB200_OP_B = 1, IB200_OP_K = 2, IB200_OP_P = 3, IB200_OP_C = 4, IB200_OP_C_MATERIALISED = 5,
+       IB200_OP_D = 6, IB200_OP_G = 7, IB200_OP_BC3 = 8, IB200_OP_BC4 = 9 };
 /* One projected operator, laid out as the reference's Eigen object (column-major):
  *   IB200_OP_M  mass_term              steadyNS.C:1085-1108   N x N        M(i,j) = int U_i . U_j
  *   IB200_OP_B  diffusive_term         steadyNS.C:883-907     N x N        B(i,j) = int U_i . laplacian(1, U_j)
@@ -179,7 +180,16 @@ enum { IB200_OP_M = 0, IB200_OP_B = 1, IB200_OP_K = 2, IB200_OP_P = 3, IB200_OP_
  *               (values identical to convective_term_tens_cache :1038-1083), stored with i fastest. Computed as one
  *               face-based contraction sum_f flux_j(f) * (Uf_k(f) . (U_i[own] - U_i[nei])) without materialising div fields.
  *   IB200_OP_C_MATERIALISED  the same tensor through N^2 materialised fvc::div(flux_j, U_k) fields (the reference's
- *               convective_term_tens_cache structure); kept as a cross-check and for the HBM-roofline measurement. */
+ *               convective_term_tens_cache structure); kept as a cross-check and for the HBM-roofline measurement.
+ * The operators steadyNS::projectPPE adds (steadyNS.C:354-553):
+ *   IB200_OP_D    laplacian_pressure   steadyNS.C:1295-1317   Np x Np      D(i,j) = int grad(P_i) . grad(P_j)
+ *   IB200_OP_G    divMomentum          steadyNS.C:1176-1254   Np x N x N   G(i,j,k) = int grad(P_i) . div(interpolate(U_j) & Sf, U_k),
+ *                 i fastest (Eigen::Tensor), through materialised div fields (the reference's divMomentum_cache structure)
+ *   IB200_OP_BC3  pressure_BC3         steadyNS.C:1439-1475   Np x N       sum over boundary faces of
+ *                 (interpolate(curl U_j) & (n ^ interpolate(grad P_i))) |Sf|
+ *   IB200_OP_BC4  pressure_BC4         steadyNS.C:1477-1513   Np x N       sum over boundary faces of P_i (n & U_j) |Sf|
+ * BC3 and BC4 are returned for ALL N velocity fields; the reference keeps the leading lift + NUmodes columns
+ * (P_BC2size = NUmodes + liftfield.size()): take leftCols. Faces of masked (`empty`) patches do not contribute. */
 int ithaca_b200_project(ithaca_b200_t* h, int op, double* out);
 
 enum { IB200_FVC_FLUX = 0, IB200_FVC_DIV_PHI = 1, IB200_FVC_LAPLACIAN = 2, IB200_FVC_GRAD_P = 3, IB200_FVC_DIV_U = 4 };

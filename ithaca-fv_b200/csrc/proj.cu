@@ -53,6 +53,8 @@ struct ProjState {
     bool have_flux = false;
     DevBuf work;   // operator fields, columns of ldU (vector) or ldP (scalar) doubles
     DevBuf T;      // gradient tensors of a batch of fields, 9*nCells doubles each
+    DevBuf gradP;      // grad(P_i), Np columns of ldU doubles (D and G operators)
+    DevBuf bndA, bndB; // boundary-face fields of the BC3 / BC4 operators
     DevBuf Tcm, Lcm;   // cell-major gradient tensors [c][9][NP] and laplacians [c][3][NP] of all fields
     DevBuf out;    // device copy of the projected operator
     ConvBufs conv; // fused convective tensor (conv.cu)
@@ -86,7 +88,7 @@ void proj_destroy(ithaca_b200* h)
     if (!s) return;
     for (DevBuf* b : {&s->owner, &s->neigh, &s->Sf, &s->magSf, &s->w, &s->dc, &s->dcB, &s->corr, &s->V, &s->bmask,
                       &s->off, &s->ent, &s->other, &s->cnt, &s->blocksum, &s->U, &s->Ub, &s->P, &s->Pb, &s->flux,
-                      &s->owner0, &s->neigh0, &s->off0, &s->ent0, &s->other0, &s->perm, &s->fperm, &s->stage, &s->Vw, &s->cmask, &s->Tcm, &s->Lcm,
+                      &s->owner0, &s->neigh0, &s->off0, &s->ent0, &s->other0, &s->perm, &s->fperm, &s->stage, &s->Vw, &s->cmask, &s->Tcm, &s->Lcm, &s->gradP, &s->bndA, &s->bndB,
                       &s->work, &s->T, &s->out, &s->conv.Ucm, &s->conv.Ubcm, &s->conv.Aj, &s->conv.Bk, &s->conv.Dd,
                       &s->conv.ws, &s->conv.chunks})
         if (b->p) cudaFree(b->p);
@@ -562,6 +564,156 @@ laplacian_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const d
     const double V = m.V[c];
 #pragma unroll
     for (int d = 0; d < 3; d++) out[(size_t)j * ldo + 3 * c + d] = acc[d] / V;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K10: boundary-face kernels of the PPE operators (steadyNS::pressure_BC3 / pressure_BC4, steadyNS.C:1439-1513).
+// One thread per (boundary face, field). The boundary value of an fvc::grad result on face b with owner cell P is
+// grad_P + n (snGrad_b - n . grad_P), snGrad_b = deltaCoeffs_b (value_b - value_P) (gaussGrad::correctBoundaryConditions);
+// grad_P is recomputed here from the cell's CSR segment (same order as grad_vec_kernel / grad_scalar_kernel), so no
+// N x 9 x nCells gradient array is materialised for the few cells that touch the boundary.
+// Faces of masked patches and (in a shard) faces whose owner is a halo cell produce zeros.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ bool bnd_face_active(const MeshDev& m, const unsigned char* cmask, long long b, int c)
+{
+    return m.bmask[b] != 0 && (!cmask || cmask[c] != 0);
+}
+
+// Fb[j][b] = (n . Ub_j) |Sf|   (BC4 = Pb^T Fb)
+__global__ void __launch_bounds__(PROJ_T)
+bnd_normal_flux_kernel(MeshDev m, const unsigned char* __restrict__ cmask, const double* __restrict__ Ub, long long ldUb, int N,
+                       double* __restrict__ out, long long ldo)
+{
+    const long long b = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    if (b >= m.nBnd) return;
+    const int j = blockIdx.y;
+    const long long f = m.nInt + b;
+    double v = 0.0;
+    if (bnd_face_active(m, cmask, b, m.owner[f])) {
+        const double ms = m.magSf[f];
+        const double* u = Ub + (size_t)j * ldUb + 3 * b;
+        v = ((m.Sf[3 * f] / ms) * u[0] + (m.Sf[3 * f + 1] / ms) * u[1] + (m.Sf[3 * f + 2] / ms) * u[2]) * ms;
+    }
+    out[(size_t)j * ldo + b] = v;
+}
+
+// Cb[j][3b+d] = curl(U_j) on boundary face b = 2 *skew(grad_b): (g_yz - g_zy, g_zx - g_xz, g_xy - g_yx), g_id = d_i U_d
+__global__ void __launch_bounds__(PROJ_T)
+bnd_curl_kernel(MeshDev m, const unsigned char* __restrict__ cmask, const double* __restrict__ U, long long ldU,
+                const double* __restrict__ Ub, long long ldUb, int N, double* __restrict__ out, long long ldo)
+{
+    const long long b0 = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    if (b0 >= m.nBnd) return;
+    const int j = blockIdx.y;
+    const long long f0 = m.nInt + b0;
+    const int c = m.owner[f0];
+    double* o = out + (size_t)j * ldo + 3 * b0;
+    if (!bnd_face_active(m, cmask, b0, c)) { o[0] = o[1] = o[2] = 0.0; return; }
+    const double* u = U + (size_t)j * ldU;
+    const double uc[3] = {u[3 * (size_t)c], u[3 * (size_t)c + 1], u[3 * (size_t)c + 2]};
+    double g[3][3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) g[i][0] = g[i][1] = g[i][2] = 0.0;
+    const int e0 = m.off[c], e1 = m.off[c + 1];
+    for (int e = e0; e < e1; e++) {
+        const int en = m.ent[e], ot = m.other[e];
+        const long long f = abs(en) - 1;
+        const double s[3] = {m.Sf[3 * f], m.Sf[3 * f + 1], m.Sf[3 * f + 2]};
+        if (ot >= 0) {
+            const double w = m.w[f], w1 = 1.0 - w;
+            const bool own = en > 0;
+#pragma unroll
+            for (int d = 0; d < 3; d++) {
+                const double x = u[3 * (size_t)ot + d];
+                const double uf = own ? (w * uc[d] + w1 * x) : (w * x + w1 * uc[d]);
+#pragma unroll
+                for (int i = 0; i < 3; i++) {
+                    const double v = s[i] * uf;
+                    g[i][d] += own ? v : -v;
+                }
+            }
+        } else {
+            const long long b = -(long long)ot - 1;
+            if (!m.bmask[b]) continue;
+            const double* ub = Ub + (size_t)j * ldUb + 3 * b;
+#pragma unroll
+            for (int d = 0; d < 3; d++)
+#pragma unroll
+                for (int i = 0; i < 3; i++) g[i][d] += s[i] * ub[d];
+        }
+    }
+    const double V = m.V[c];
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int d = 0; d < 3; d++) g[i][d] /= V;
+    const double ms = m.magSf[f0];
+    const double n[3] = {m.Sf[3 * f0] / ms, m.Sf[3 * f0 + 1] / ms, m.Sf[3 * f0 + 2] / ms};
+    const double* ub = Ub + (size_t)j * ldUb + 3 * b0;
+    const double dcb = m.dcB[b0];
+#pragma unroll
+    for (int d = 0; d < 3; d++) {
+        const double sn = dcb * (ub[d] - uc[d]);
+        const double ng = n[0] * g[0][d] + n[1] * g[1][d] + n[2] * g[2][d];
+        const double corr = sn - ng;
+#pragma unroll
+        for (int i = 0; i < 3; i++) g[i][d] = g[i][d] + n[i] * corr;
+    }
+    o[0] = g[1][2] - g[2][1];
+    o[1] = g[2][0] - g[0][2];
+    o[2] = g[0][1] - g[1][0];
+}
+
+// Gb[i][3b+d] = (n x grad(P_i)_b) |Sf| on boundary face b
+__global__ void __launch_bounds__(PROJ_T)
+bnd_ncross_gradp_kernel(MeshDev m, const unsigned char* __restrict__ cmask, const double* __restrict__ P, long long ldP,
+                        const double* __restrict__ Pb, long long ldPb, int Np, double* __restrict__ out, long long ldo)
+{
+    const long long b0 = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    if (b0 >= m.nBnd) return;
+    const int j = blockIdx.y;
+    const long long f0 = m.nInt + b0;
+    const int c = m.owner[f0];
+    double* o = out + (size_t)j * ldo + 3 * b0;
+    if (!bnd_face_active(m, cmask, b0, c)) { o[0] = o[1] = o[2] = 0.0; return; }
+    const double* p = P + (size_t)j * ldP;
+    const double pc = p[c];
+    double g[3] = {0.0, 0.0, 0.0};
+    const int e0 = m.off[c], e1 = m.off[c + 1];
+    for (int e = e0; e < e1; e++) {
+        const int en = m.ent[e], ot = m.other[e];
+        const long long f = abs(en) - 1;
+        const double s[3] = {m.Sf[3 * f], m.Sf[3 * f + 1], m.Sf[3 * f + 2]};
+        if (ot >= 0) {
+            const double w = m.w[f], w1 = 1.0 - w;
+            const bool own = en > 0;
+            const double x = p[ot];
+            const double pf = own ? (w * pc + w1 * x) : (w * x + w1 * pc);
+#pragma unroll
+            for (int d = 0; d < 3; d++) {
+                const double v = s[d] * pf;
+                g[d] += own ? v : -v;
+            }
+        } else {
+            const long long b = -(long long)ot - 1;
+            if (!m.bmask[b]) continue;
+            const double pb = Pb[(size_t)j * ldPb + b];
+#pragma unroll
+            for (int d = 0; d < 3; d++) g[d] += s[d] * pb;
+        }
+    }
+    const double V = m.V[c];
+#pragma unroll
+    for (int d = 0; d < 3; d++) g[d] /= V;
+    const double ms = m.magSf[f0];
+    const double n[3] = {m.Sf[3 * f0] / ms, m.Sf[3 * f0 + 1] / ms, m.Sf[3 * f0 + 2] / ms};
+    const double sn = m.dcB[b0] * (Pb[(size_t)j * ldPb + b0] - pc);
+    const double ng = n[0] * g[0] + n[1] * g[1] + n[2] * g[2];
+#pragma unroll
+    for (int d = 0; d < 3; d++) g[d] = g[d] + n[d] * (sn - ng);
+    o[0] = (n[1] * g[2] - n[2] * g[1]) * ms;
+    o[1] = (n[2] * g[0] - n[0] * g[2]) * ms;
+    o[2] = (n[0] * g[1] - n[1] * g[0]) * ms;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1157,7 +1309,8 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
     ProjState* s = h->proj;
     PROJ_REQUIRE(s && s->have_mesh && s->nU > 0, "project: call mesh_upload and basis_upload(U) first");
     PROJ_REQUIRE(out, "project: null output");
-    PROJ_REQUIRE((op != IB200_OP_K && op != IB200_OP_P) || s->nP > 0, "project: K and P need basis_upload(P)");
+    PROJ_REQUIRE((op != IB200_OP_K && op != IB200_OP_P && op != IB200_OP_D && op != IB200_OP_G && op != IB200_OP_BC3 &&
+                  op != IB200_OP_BC4) || s->nP > 0, "project: K, P, D, G, BC3 and BC4 need basis_upload(P)");
     cudaSetDevice(h->device);
     const MeshDev m = mesh_dev(s);
     const int N = s->nU, Np = s->nP, BIG = 0x7fffffff;
@@ -1259,6 +1412,108 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
             // column jj*N + k of the work matrix = div(phi_{j0+jj}, U_k)  ->  C(i, j0+jj, k)
             rc = atvb_launch(h, U, s->ldU, N, s->work.as<double>(), s->ldU, nj * N, K3, V, 3, 0,
                              s->out.as<double>() + (size_t)N * j0, 1, N, N, (long long)N * N);
+            t.stop();
+            if (rc) return rc;
+        }
+        break;
+    }
+    case IB200_OP_D: {  // laplacian_pressure, steadyNS.C:1295-1317: Np x Np
+        nout = (size_t)Np * Np;
+        if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
+        if ((rc = ensure(h, s->gradP, (size_t)Np * s->ldU * sizeof(double)))) return rc;
+        {
+            StageTimer t(h->stream, &s->ms[3]);
+            grad_scalar_kernel<<<dim3(gx(s->nCells), gy(Np)), PROJ_T, 0, h->stream>>>(m, s->P.as<double>(), s->ldP, s->Pb.as<double>(),
+                                                                                       s->ldPb, Np, s->gradP.as<double>(), s->ldU);
+            t.stop();
+            h->launches += 1;
+        }
+        StageTimer t(h->stream, &s->ms[5]);
+        rc = atvb_launch(h, s->gradP.as<double>(), s->ldU, Np, s->gradP.as<double>(), s->ldU, Np, K3, V, 3, 1, s->out.as<double>(), 1,
+                         BIG, 0, Np);
+        t.stop();
+        if (rc) return rc;
+        break;
+    }
+    case IB200_OP_G: {  // divMomentum (== divMomentum_cache), steadyNS.C:1176-1254: Np x N x N, i fastest
+        nout = (size_t)Np * N * N;
+        if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
+        if ((rc = ensure(h, s->gradP, (size_t)Np * s->ldU * sizeof(double)))) return rc;
+        if ((rc = need_flux(h, s))) return rc;
+        {
+            StageTimer t(h->stream, &s->ms[3]);
+            grad_scalar_kernel<<<dim3(gx(s->nCells), gy(Np)), PROJ_T, 0, h->stream>>>(m, s->P.as<double>(), s->ldP, s->Pb.as<double>(),
+                                                                                       s->ldPb, Np, s->gradP.as<double>(), s->ldU);
+            t.stop();
+            h->launches += 1;
+        }
+        const size_t percol = (size_t)s->ldU * sizeof(double);
+        int jb = (int)std::max<size_t>(1, std::min<size_t>({(size_t)N, 8, (size_t)12e9 / (percol * N)}));
+        if ((rc = ensure(h, s->work, (size_t)jb * N * percol))) return rc;
+        for (int j0 = 0; j0 < N; j0 += jb) {
+            const int nj = std::min(jb, N - j0);
+            {
+                StageTimer t(h->stream, &s->ms[1]);
+                for (int jj = 0; jj < nj; jj++) {
+                    div_phi_kernel<<<dim3(gx(s->nCells), gy(N)), PROJ_T, 0, h->stream>>>(
+                        m, s->flux.as<double>() + (size_t)(j0 + jj) * s->ldF, U, s->ldU, s->Ub.as<double>(), s->ldUb, N,
+                        s->work.as<double>() + (size_t)jj * N * s->ldU, s->ldU);
+                    h->launches += 1;
+                }
+                t.stop();
+            }
+            StageTimer t(h->stream, &s->ms[5]);
+            // column jj*N + k of the work matrix = div(phi_{j0+jj}, U_k)  ->  G(i, j0+jj, k) at i + Np*(j + N*k)
+            rc = atvb_launch(h, s->gradP.as<double>(), s->ldU, Np, s->work.as<double>(), s->ldU, nj * N, K3, V, 3, 0,
+                             s->out.as<double>() + (size_t)Np * j0, 1, N, Np, (long long)Np * N);
+            t.stop();
+            if (rc) return rc;
+        }
+        break;
+    }
+    case IB200_OP_BC4: {  // pressure_BC4, steadyNS.C:1477-1513: Np x N, boundary-face sum of P_i (n . U_j) |Sf|
+        nout = (size_t)Np * N;
+        if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
+        IB_CUDA(h, cudaMemsetAsync(s->out.p, 0, nout * sizeof(double), h->stream));
+        if (s->nBnd > 0) {
+            const long long ldB = pad16(s->nBnd);
+            if ((rc = ensure(h, s->bndA, (size_t)N * ldB * sizeof(double)))) return rc;
+            {
+                StageTimer t(h->stream, &s->ms[0]);
+                bnd_normal_flux_kernel<<<dim3(gx(s->nBnd), N), PROJ_T, 0, h->stream>>>(m, shard ? s->cmask.as<unsigned char>() : nullptr,
+                                                                                        s->Ub.as<double>(), s->ldUb, N, s->bndA.as<double>(), ldB);
+                t.stop();
+                h->launches += 1;
+            }
+            StageTimer t(h->stream, &s->ms[5]);
+            rc = atvb_launch(h, s->Pb.as<double>(), s->ldPb, Np, s->bndA.as<double>(), ldB, N, s->nBnd, nullptr, 1, 0, s->out.as<double>(), 1,
+                             BIG, 0, Np);
+            t.stop();
+            if (rc) return rc;
+        }
+        break;
+    }
+    case IB200_OP_BC3: {  // pressure_BC3, steadyNS.C:1439-1475: Np x N, boundary-face sum of curl(U_j) . (n x grad P_i) |Sf|
+        nout = (size_t)Np * N;
+        if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
+        IB_CUDA(h, cudaMemsetAsync(s->out.p, 0, nout * sizeof(double), h->stream));
+        if (s->nBnd > 0) {
+            const long long ld3 = pad16(3 * s->nBnd);
+            const unsigned char* cm = shard ? s->cmask.as<unsigned char>() : nullptr;
+            if ((rc = ensure(h, s->bndA, (size_t)N * ld3 * sizeof(double))) || (rc = ensure(h, s->bndB, (size_t)Np * ld3 * sizeof(double))))
+                return rc;
+            {
+                StageTimer t(h->stream, &s->ms[3]);
+                bnd_curl_kernel<<<dim3(gx(s->nBnd), N), PROJ_T, 0, h->stream>>>(m, cm, U, s->ldU, s->Ub.as<double>(), s->ldUb, N,
+                                                                                 s->bndA.as<double>(), ld3);
+                bnd_ncross_gradp_kernel<<<dim3(gx(s->nBnd), Np), PROJ_T, 0, h->stream>>>(m, cm, s->P.as<double>(), s->ldP, s->Pb.as<double>(),
+                                                                                          s->ldPb, Np, s->bndB.as<double>(), ld3);
+                t.stop();
+                h->launches += 2;
+            }
+            StageTimer t(h->stream, &s->ms[5]);
+            rc = atvb_launch(h, s->bndB.as<double>(), ld3, Np, s->bndA.as<double>(), ld3, N, 3 * s->nBnd, nullptr, 1, 0, s->out.as<double>(), 1,
+                             BIG, 0, Np);
             t.stop();
             if (rc) return rc;
         }

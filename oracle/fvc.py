@@ -132,6 +132,39 @@ class Oracle:
         fn(self._ref(), N, pu, pb, P(C.ctypes.data))
         return C
 
+    # ---- PPE operators (steadyNS::projectPPE) ----
+    def laplacian_pressure(self, Pm, Pb):
+        fp, pp = self._ptrs(Pm)
+        fb, pb = self._ptrs(Pb)
+        D = np.zeros((len(fp), len(fp)), order="F")
+        self.L.fvo_laplacian_pressure(self._ref(), len(fp), pp, pb, P(D.ctypes.data))
+        return D
+
+    def div_momentum(self, U, Ub, Pm, Pb):
+        fs, pu = self._ptrs(U)
+        fb, pub = self._ptrs(Ub)
+        fp, pp = self._ptrs(Pm)
+        fpb, ppb = self._ptrs(Pb)
+        G = np.zeros((len(fp), len(fs), len(fs)), order="F")
+        self.L.fvo_div_momentum(self._ref(), len(fs), len(fp), pu, pub, pp, ppb, P(G.ctypes.data))
+        return G
+
+    def pressure_bc4(self, Ub, Pb):
+        fb, pub = self._ptrs(Ub)
+        fpb, ppb = self._ptrs(Pb)
+        out = np.zeros((len(fpb), len(fb)), order="F")
+        self.L.fvo_pressure_bc4(self._ref(), len(fb), len(fpb), pub, ppb, P(out.ctypes.data))
+        return out
+
+    def pressure_bc3(self, U, Ub, Pm, Pb):
+        fs, pu = self._ptrs(U)
+        fb, pub = self._ptrs(Ub)
+        fp, pp = self._ptrs(Pm)
+        fpb, ppb = self._ptrs(Pb)
+        out = np.zeros((len(fp), len(fs)), order="F")
+        self.L.fvo_pressure_bc3(self._ref(), len(fs), len(fp), pu, pub, pp, ppb, P(out.ctypes.data))
+        return out
+
     def cell_faces(self):
         nnz = 2 * self.mesh.nInt + self.mesh.nBnd
         off = np.zeros(self.mesh.nCells + 1, dtype=np.int32)

@@ -282,6 +282,138 @@ void fvo_convective_term_tens_cache(const fvo_mesh* m, int N, const double* cons
     free(D);
 }
 
+/* ---- PPE operators (steadyNS::projectPPE, steadyNS.C:354-553) ------------------------------------------------
+ * Boundary values of fvc results, restated from OpenFOAM v2412 (recalled, unpinned like the operators above):
+ *   fvc::grad(vf) on a non-coupled patch face b with cell P and unit normal n (gaussGrad::correctBoundaryConditions):
+ *       grad_b = grad_P + n * (snGrad_b - (n & grad_P)),   snGrad_b = deltaCoeffs_b * (vf_b - vf_P)
+ *       (fvPatchField::snGrad; for a zeroGradient patch vf_b == vf_P and it vanishes)
+ *   fvc::curl(vf) = 2 * (*skew(fvc::grad(vf)))  (fvcCurl.C), boundary field = the same expression of grad_b;
+ *       with grad_id = d_i vf_d: curl = (g_yz - g_zy, g_zx - g_xz, g_xy - g_yx)
+ *   fvc::interpolate(vol field) on a boundary face = the field's boundary value. */
+
+/* steadyNS::laplacian_pressure, steadyNS.C:1295-1317: D(i,j) = domainIntegrate(grad(P_i) & grad(P_j)). D: Np x Np. */
+void fvo_laplacian_pressure(const fvo_mesh* m, int Np, const double* const* P, const double* const* Pb, double* D)
+{
+    double** G = (double**)malloc(sizeof(double*) * Np);
+    for (int i = 0; i < Np; i++) {
+        G[i] = (double*)malloc(sizeof(double) * 3 * m->nCells);
+        fvo_grad_scalar(m, P[i], Pb[i], G[i]);
+    }
+    for (int i = 0; i < Np; i++)
+        for (int j = 0; j < Np; j++) D[i + (size_t)j * Np] = fvo_domain_integrate_dot(m, G[i], G[j], 3);
+    for (int i = 0; i < Np; i++) free(G[i]);
+    free(G);
+}
+
+/* steadyNS::divMomentum_cache, steadyNS.C:1207-1254 (values identical to divMomentum :1176-1205):
+ * G(i,j,k) = domainIntegrate(grad(P_i) & div(interpolate(U_j) & Sf, U_k)) at G[i + Np*(j + N*k)]. */
+void fvo_div_momentum(const fvo_mesh* m, int N, int Np, const double* const* U, const double* const* Ub,
+                      const double* const* P, const double* const* Pb, double* G)
+{
+    double** gp = (double**)malloc(sizeof(double*) * Np);
+    for (int i = 0; i < Np; i++) {
+        gp[i] = (double*)malloc(sizeof(double) * 3 * m->nCells);
+        fvo_grad_scalar(m, P[i], Pb[i], gp[i]);
+    }
+    double* phi = (double*)malloc(sizeof(double) * (m->nInt + m->nBnd));
+    double* D = (double*)malloc(sizeof(double) * 3 * m->nCells);
+    for (int j = 0; j < N; j++) {
+        fvo_flux(m, U[j], Ub[j], phi);
+        for (int k = 0; k < N; k++) {
+            fvo_div_phi_vec(m, phi, U[k], Ub[k], D);
+            for (int i = 0; i < Np; i++) G[i + (size_t)Np * (j + (size_t)N * k)] = fvo_domain_integrate_dot(m, gp[i], D, 3);
+        }
+    }
+    for (int i = 0; i < Np; i++) free(gp[i]);
+    free(gp);
+    free(phi);
+    free(D);
+}
+
+/* steadyNS::pressure_BC4, steadyNS.C:1477-1513: BC4(i,j) = sum over boundary faces of
+ * interpolate(P_i) * (n & interpolate(U_j)) * magSf, n = Sf/magSf. BC4: Np x N. */
+void fvo_pressure_bc4(const fvo_mesh* m, int N, int Np, const double* const* Ub, const double* const* Pb, double* BC4)
+{
+    for (int i = 0; i < Np; i++)
+        for (int j = 0; j < N; j++) {
+            double s = 0.0;
+            for (long long b = 0; b < m->nBnd; b++) {
+                if (!m->bmask[b]) continue;
+                const long long f = m->nInt + b;
+                const double ms = m->magSf[f];
+                const double n[3] = {m->Sf[3 * f] / ms, m->Sf[3 * f + 1] / ms, m->Sf[3 * f + 2] / ms};
+                const double* u = Ub[j] + 3 * b;
+                const double bc4 = n[0] * u[0] + n[1] * u[1] + n[2] * u[2];
+                s += (Pb[i][b] * bc4) * ms;
+            }
+            BC4[i + (size_t)j * Np] = s;
+        }
+}
+
+/* boundary value of fvc::grad of a field with `dim` components at boundary face b (see the note above).
+ * gP: the cell gradient of the owner, g[i*dim + d] = d_i vf_d; vb, vP: boundary and owner-cell values. */
+static void bnd_grad(const fvo_mesh* m, long long b, int dim, const double* gP, const double* vb, const double* vP, double* g)
+{
+    const long long f = m->nInt + b;
+    const double ms = m->magSf[f];
+    const double n[3] = {m->Sf[3 * f] / ms, m->Sf[3 * f + 1] / ms, m->Sf[3 * f + 2] / ms};
+    for (int d = 0; d < dim; d++) {
+        const double sn = m->dcB[b] * (vb[d] - vP[d]);
+        const double ng = n[0] * gP[0 * dim + d] + n[1] * gP[1 * dim + d] + n[2] * gP[2 * dim + d];
+        for (int i = 0; i < 3; i++) g[i * dim + d] = gP[i * dim + d] + n[i] * (sn - ng);
+    }
+}
+
+/* steadyNS::pressure_BC3, steadyNS.C:1439-1475: BC3(i,j) = sum over boundary faces of
+ * (interpolate(curl(U_j)) & (n ^ interpolate(grad(P_i)))) * magSf. BC3: Np x N. */
+void fvo_pressure_bc3(const fvo_mesh* m, int N, int Np, const double* const* U, const double* const* Ub,
+                      const double* const* P, const double* const* Pb, double* BC3)
+{
+    const long long nB = m->nBnd;
+    double* T = (double*)malloc(sizeof(double) * 9 * m->nCells);
+    double* gp = (double*)malloc(sizeof(double) * 3 * m->nCells);
+    double* curl = (double*)malloc(sizeof(double) * 3 * nB * (size_t)N);
+    double* ngp = (double*)malloc(sizeof(double) * 3 * nB * (size_t)Np);
+    for (int j = 0; j < N; j++) {
+        fvo_grad_vec(m, U[j], Ub[j], T);
+        for (long long b = 0; b < nB; b++) {
+            const long long c = m->owner[m->nInt + b];
+            double g[9];
+            bnd_grad(m, b, 3, T + 9 * c, Ub[j] + 3 * b, U[j] + 3 * c, g);
+            double* cu = curl + 3 * (b + nB * (size_t)j);
+            cu[0] = g[1 * 3 + 2] - g[2 * 3 + 1];
+            cu[1] = g[2 * 3 + 0] - g[0 * 3 + 2];
+            cu[2] = g[0 * 3 + 1] - g[1 * 3 + 0];
+        }
+    }
+    for (int i = 0; i < Np; i++) {
+        fvo_grad_scalar(m, P[i], Pb[i], gp);
+        for (long long b = 0; b < nB; b++) {
+            const long long f = m->nInt + b, c = m->owner[f];
+            const double ms = m->magSf[f];
+            const double n[3] = {m->Sf[3 * f] / ms, m->Sf[3 * f + 1] / ms, m->Sf[3 * f + 2] / ms};
+            double g[3];
+            bnd_grad(m, b, 1, gp + 3 * c, Pb[i] + b, P[i] + c, g);
+            double* o = ngp + 3 * (b + nB * (size_t)i);
+            o[0] = n[1] * g[2] - n[2] * g[1];
+            o[1] = n[2] * g[0] - n[0] * g[2];
+            o[2] = n[0] * g[1] - n[1] * g[0];
+        }
+    }
+    for (int i = 0; i < Np; i++)
+        for (int j = 0; j < N; j++) {
+            double s = 0.0;
+            for (long long b = 0; b < nB; b++) {
+                if (!m->bmask[b]) continue;
+                const double* a = curl + 3 * (b + nB * (size_t)j);
+                const double* q = ngp + 3 * (b + nB * (size_t)i);
+                s += (a[0] * q[0] + a[1] * q[1] + a[2] * q[2]) * m->magSf[m->nInt + b];
+            }
+            BC3[i + (size_t)j * Np] = s;
+        }
+    free(T); free(gp); free(curl); free(ngp);
+}
+
 /* ---- addressing: cell -> face CSR in ascending face order (= primitiveMesh::cells() order) -------------
  * entry = +(f+1) when the cell owns face f (Sf points outwards), -(f+1) when it is the neighbour.
  * off: nCells+1, ent/other: 2*nInt+nBnd. other = the cell across the face, or -(b+1) for boundary face b. */

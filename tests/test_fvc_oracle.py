@@ -134,3 +134,47 @@ def test_cell_faces_csr(cyl):
                 assert m.owner[fe] == c and (oc == (m.neighbour[fe] if fe < m.nInt else -(fe - m.nInt + 1)))
             else:
                 assert m.neighbour[fe] == c and oc == m.owner[fe]
+
+
+def test_ppe_operators_known_answers(box, cyl):
+    """D, G, BC3, BC4 of steadyNS::projectPPE (steadyNS.C:1176-1513) against closed forms:
+    D is the V-weighted Gram of the pressure gradients; on the orthogonal box mesh linear fields have exact gradients, so
+    D(i,j) = a_i . a_j * |Omega|; BC4 with P = 1 is the boundary flux = integral of div(U) (Gauss);
+    BC3 = closed-surface integral of n . (grad p x curl U) = 0 for a rigid rotation (constant curl) and a linear p;
+    G(i,j,k) = integral of grad(P_i) . div(phi_j, U_k) from its definition."""
+    m = box
+    o = fvc.Oracle(m)
+    X, Xb = m.Cc, m.Cf[m.nInt:]
+    a = np.array([[1.0, -2.0, 0.5], [0.3, 0.7, -1.1]])
+    P = [np.ascontiguousarray(X @ a[i] + 0.2 * i) for i in range(2)]
+    Pb = [np.ascontiguousarray(Xb @ a[i] + 0.2 * i) for i in range(2)]
+    D = o.laplacian_pressure(P, Pb)
+    assert np.abs(D - (a @ a.T) * m.V.sum()).max() <= 1e-12 * np.abs(D).max()
+    assert np.array_equal(D, D.T)
+    # rigid rotation + translation: U = w x x + t, curl U = 2 w
+    w, t = np.array([0.4, -0.3, 0.9]), np.array([0.1, 0.2, -0.3])
+    A = np.array([[0, -w[2], w[1]], [w[2], 0, -w[0]], [-w[1], w[0], 0]])
+    U = [lin_vec(X, A, t), lin_vec(X, 2 * A, -t)]
+    Ub = [lin_vec(Xb, A, t), lin_vec(Xb, 2 * A, -t)]
+    T = o.grad_vec(U[0], Ub[0]).reshape(-1, 3, 3)
+    assert np.abs(T - A.T).max() <= 1e-12  # T[i][d] = d_i U_d
+    BC3 = o.pressure_bc3(U, Ub, P, Pb)
+    scale = 2 * np.linalg.norm(w) * np.linalg.norm(a[0]) * m.magSf[m.nInt:].sum()
+    assert np.abs(BC3).max() <= 1e-12 * scale
+    ones, onesb = np.ones(m.nCells), np.ones(m.nBnd)
+    BC4 = o.pressure_bc4(Ub, [onesb] + Pb)
+    Pm = o.divergence_term(U, Ub, [ones])
+    assert np.abs(BC4[0] - Pm[0]).max() <= 1e-12 * m.magSf.sum()
+    # non-trivial BC3 / G on the non-orthogonal cylinder mesh: definition-level cross-checks
+    m2 = cyl
+    o2 = fvc.Oracle(m2)
+    U2, Ub2, P2, Pb2 = fvc.synthetic_basis(m2, 3, 2, seed=8)
+    G = o2.div_momentum(U2, Ub2, P2, Pb2)
+    assert G.shape == (2, 3, 3)
+    phi = o2.flux(U2[1], Ub2[1])
+    d = o2.div_phi(phi, U2[2], Ub2[2])
+    g = o2.grad(P2[1], Pb2[1])
+    assert abs(G[1, 1, 2] - np.sum(np.repeat(m2.V, 3) * g * d)) <= 1e-13 * np.abs(G).max()
+    BC3 = o2.pressure_bc3(U2, Ub2, P2, Pb2)
+    BC3s = o2.pressure_bc3([U2[1] * 2.0], [Ub2[1] * 2.0], [P2[0] - 3.0 * P2[1]], [Pb2[0] - 3.0 * Pb2[1]])
+    assert abs(BC3s[0, 0] - 2.0 * (BC3[0, 1] - 3.0 * BC3[1, 1])) <= 1e-12 * np.abs(BC3).max()  # bilinear

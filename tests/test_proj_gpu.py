@@ -73,6 +73,18 @@ def test_projected_operators_match_oracle(case):
     assert t["contraction"] > 0 and t["face_records"] > 0
 
 
+def test_ppe_operators_match_oracle(case):
+    """steadyNS::projectPPE's additional operators (SURVEY 8(f) rank 1): D, G (divMomentum), BC3, BC4."""
+    mesh, orc, pr, (U, Ub, P, Pb) = case
+    D = pr.project("D")
+    assert rel(D, orc.laplacian_pressure(P, Pb)) <= TOL and np.array_equal(D, D.T)
+    assert rel(pr.project("BC4"), orc.pressure_bc4(Ub, Pb)) <= TOL
+    assert rel(pr.project("BC3"), orc.pressure_bc3(U, Ub, P, Pb)) <= TOL
+    G = pr.project("G")
+    Gr = orc.div_momentum(U, Ub, P, Pb)
+    assert G.shape == Gr.shape and rel(G, Gr) <= TOL
+
+
 def test_uncorrected_laplacian(pkg, pod):
     mesh = meshes()["cyl"]()
     U, Ub, _, _ = fvc.synthetic_basis(mesh, 5, 0, seed=2)
@@ -150,7 +162,9 @@ def test_sharded_projection_sums_to_the_global_operators(pkg, pod, nranks, name,
     U, Ub, P, Pb = fvc.synthetic_basis(mesh, N, Np, seed=13)
     orc = fvc.Oracle(mesh, corrected=True)
     ref = {"M": orc.mass_term(U), "B": orc.diffusive_term(U, Ub), "K": orc.pressure_gradient_term(U, P, Pb),
-           "P": orc.divergence_term(U, Ub, P), "C": orc.convective_term_tens(U, Ub, cache=True)}
+           "P": orc.divergence_term(U, Ub, P), "C": orc.convective_term_tens(U, Ub, cache=True),
+           "D": orc.laplacian_pressure(P, Pb), "G": orc.div_momentum(U, Ub, P, Pb), "BC3": orc.pressure_bc3(U, Ub, P, Pb),
+           "BC4": orc.pressure_bc4(Ub, Pb)}
     ref["Cmat"] = ref["C"]
     acc = {k: np.zeros_like(v) for k, v in ref.items()}
     pr = pkg.Projector(pod)
