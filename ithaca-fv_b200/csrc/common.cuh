@@ -116,10 +116,11 @@ struct ConvMesh {
     const unsigned char* cmask;   // per cell: 1 owned, 0 halo (null = all owned); scales U_i in d_i = U_i[own] - U_i[nei]
 };
 struct ConvBufs {
-    DevBuf Ucm, Ubcm, Aj, Bk, Dd, ws, chunks;
+    DevBuf Ucm, Ubcm, Dcm, Aj, Bk, Dd, ws, chunks;
 };
 int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long nCells, const double* U, long long ldU,
-                      const double* Ub, long long ldUb, int N, double* dC, double* ms_prep, double* ms_contract);
+                      const double* Ub, long long ldUb, int N, double* dC, double* ms_prep, double* ms_contract,
+                      const double* Dfm = nullptr, long long ldD = 0, int Ni = 0);   // Dfm: Ni test fields for d_i (null: the basis)
 void set_error(ithaca_b200* h, const std::string& msg);
 
 // cuTensorMapEncodeTiled through cudaGetDriverEntryPoint (no link-time libcuda dependency).

@@ -53,9 +53,11 @@ conv_transpose_kernel(const double* __restrict__ in, long long ld, long long row
 // Aj[f][NP], Bk[f][N][4] (component padded to 4: 32 B per mode, TMA-box friendly), Dd[f][3][NP]. One block = 4 faces,
 // lanes over the mode index (coalesced 8*NP-byte rows of the cell-major basis).
 __global__ void __launch_bounds__(256)
-conv_face_prep_kernel(ConvMesh m, const double* __restrict__ Ucm, const double* __restrict__ Ubcm, int N, int NP,
-                      double* __restrict__ Aj, double* __restrict__ Bk, double* __restrict__ Dd)
+conv_face_prep_kernel(ConvMesh m, const double* __restrict__ Ucm, const double* __restrict__ Ubcm, const double* __restrict__ Dcm,
+                      int N, int NP, double* __restrict__ Aj, double* __restrict__ Bk, double* __restrict__ Dd)
 {
+    // Dcm: cell-major test fields of the d_i records (null = the basis itself: the convective tensor; grad(P_i) padded
+    // to N fields: the divMomentum tensor)
     const long long f = (long long)blockIdx.x * 4 + threadIdx.y;
     const long long nF = m.nInt + m.nBnd;
     if (f >= nF) return;
@@ -76,7 +78,14 @@ conv_face_prep_kernel(ConvMesh m, const double* __restrict__ Ucm, const double* 
             a += b0 * s0; a += b1 * s1; a += b2 * s2;
             Aj[(size_t)f * NP + j] = a;
             double* d = Dd + (size_t)f * 3 * NP;
-            d[j] = mo * o0 - mn * n0; d[NP + j] = mo * o1 - mn * n1; d[2 * NP + j] = mo * o2 - mn * n2;
+            if (Dcm) {
+                const double* qo = Dcm + (size_t)o * 3 * NP;
+                const double* qn = Dcm + (size_t)nn * 3 * NP;
+                d[j] = mo * qo[j] - mn * qn[j]; d[NP + j] = mo * qo[NP + j] - mn * qn[NP + j];
+                d[2 * NP + j] = mo * qo[2 * NP + j] - mn * qn[2 * NP + j];
+            } else {
+                d[j] = mo * o0 - mn * n0; d[NP + j] = mo * o1 - mn * n1; d[2 * NP + j] = mo * o2 - mn * n2;
+            }
             if (j < N) {
                 double4* b = reinterpret_cast<double4*>(Bk + ((size_t)f * N + j) * 4);
                 *b = make_double4(b0, b1, b2, 0.0);
@@ -92,7 +101,8 @@ conv_face_prep_kernel(ConvMesh m, const double* __restrict__ Ucm, const double* 
             if (on) { a += b0 * s0; a += b1 * s1; a += b2 * s2; }
             Aj[(size_t)f * NP + j] = a;
             double* d = Dd + (size_t)f * 3 * NP;
-            d[j] = mo * uo[j]; d[NP + j] = mo * uo[NP + j]; d[2 * NP + j] = mo * uo[2 * NP + j];
+            const double* qo = Dcm ? Dcm + (size_t)o * 3 * NP : uo;
+            d[j] = mo * qo[j]; d[NP + j] = mo * qo[NP + j]; d[2 * NP + j] = mo * qo[2 * NP + j];
             if (j < N) {
                 double4* b = reinterpret_cast<double4*>(Bk + ((size_t)f * N + j) * 4);
                 *b = make_double4(b0, b1, b2, 0.0);
@@ -137,7 +147,7 @@ __device__ __forceinline__ void conv_stage(double (&acc)[2][CV_JF][2], const dou
 template <int KT>
 __global__ void __launch_bounds__(CV_THREADS, 1)
 conv_contract_kernel(const __grid_constant__ CUtensorMap tmB, const double* __restrict__ Aj, const double* __restrict__ Dd,
-                     const ConvChunk* __restrict__ chunks, int nchunks, int njblk, int N, int NP, int bp, int Jpad,
+                     const ConvChunk* __restrict__ chunks, int nchunks, int njblk, int N, int NI, int NP, int bp, int Jpad,
                      long long tiles_per_slab, long long ntiles, int nstages, double* __restrict__ ws)
 {
     extern __shared__ __align__(1024) unsigned char smem[];
@@ -187,8 +197,8 @@ conv_contract_kernel(const __grid_constant__ CUtensorMap tmB, const double* __re
     for (int r = 0; r < 2; r++) {
         const int row0 = ch.r_lo + 8 * (2 * warp + r);
         act[r] = row0 < ch.r_hi;                       // warp-uniform
-        const int row = min(row0 + g, N * N - 1);
-        const int k = row / N, i = row - k * N;
+        const int row = min(row0 + g, N * NI - 1);   // rows are (k, i) pairs, i < NI test fields
+        const int k = row / NI, i = row - k * NI;
         boff[r] = 4 * min(max(k - ch.k_lo, 0), CV_KC - 1);
         doff[r] = i;
     }
@@ -213,7 +223,7 @@ conv_contract_kernel(const __grid_constant__ CUtensorMap tmB, const double* __re
     }
 
     // ---------------- epilogue: partial rows -> workspace slab [row][Jpad] ----------------
-    double* out = ws + (size_t)slab * (size_t)N * N * Jpad;
+    double* out = ws + (size_t)slab * (size_t)N * NI * Jpad;
 #pragma unroll
     for (int r = 0; r < 2; r++) {
         const int row = ch.r_lo + 8 * (2 * warp + r) + g;
@@ -227,24 +237,25 @@ conv_contract_kernel(const __grid_constant__ CUtensorMap tmB, const double* __re
     }
 }
 
-// fixed-order split-K reduction and scatter into the Eigen tensor layout: C(i,j,k) at i + N*(j + N*k), row = k*N + i
-__global__ void conv_reduce_kernel(const double* __restrict__ ws, int nslabs, int N, int Jpad, double* __restrict__ C)
+// fixed-order split-K reduction and scatter into the Eigen tensor layout: C(i,j,k) at i + NI*(j + N*k), row = k*NI + i
+__global__ void conv_reduce_kernel(const double* __restrict__ ws, int nslabs, int N, int NI, int Jpad, double* __restrict__ C)
 {
-    const long long total = (long long)N * N * N;
-    const size_t slab = (size_t)N * N * Jpad;
+    const long long total = (long long)N * NI * N;
+    const size_t slab = (size_t)N * NI * Jpad;
     for (long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x; idx < total; idx += (long long)gridDim.x * blockDim.x) {
         const int j = (int)(idx % N);
         const long long row = idx / N;
-        const int k = (int)(row / N), i = (int)(row % N);
+        const int k = (int)(row / NI), i = (int)(row % NI);
         double s = 0.0;
         for (int q = 0; q < nslabs; q++) s += ws[q * slab + (size_t)row * Jpad + j];
-        C[(size_t)i + (size_t)N * (j + (size_t)N * k)] = s;
+        C[(size_t)i + (size_t)NI * (j + (size_t)N * k)] = s;
     }
 }
 
 // ---- host -------------------------------------------------------------------------------------------------------
 int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long nCells, const double* U, long long ldU,
-                      const double* Ub, long long ldUb, int N, double* dC, double* ms_prep, double* ms_contract)
+                      const double* Ub, long long ldUb, int N, double* dC, double* ms_prep, double* ms_contract, const double* Dfm,
+                      long long ldD, int Ni)
 {
     const int NP = (N + 3) / 8 * 8 + 4;  // smallest NP >= N with NP = 4 (mod 8): conflict-free smem pitches
     const long long nF = m.nInt + m.nBnd;
@@ -257,15 +268,17 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
     int rc;
     if ((rc = dev_ensure(h, cb->Ucm, (size_t)nCells * 3 * NP * 8))) return rc;
     if ((rc = dev_ensure(h, cb->Ubcm, (size_t)std::max<long long>(m.nBnd, 1) * 3 * NP * 8))) return rc;
+    if (Dfm && (rc = dev_ensure(h, cb->Dcm, (size_t)nCells * 3 * NP * 8))) return rc;
     if ((rc = dev_ensure(h, cb->Aj, (size_t)nFpad * NP * 8 + 1024))) return rc;
     if ((rc = dev_ensure(h, cb->Bk, (size_t)nFpad * N * 32))) return rc;
     if ((rc = dev_ensure(h, cb->Dd, (size_t)nFpad * 3 * NP * 8))) return rc;
 
     // output row chunks: <= CV_ROWS rows and <= CV_KC distinct k each
+    const int NI = Dfm ? Ni : N;   // test fields of the d_i records: rows of the contraction are (k, i), i < NI
     std::vector<ConvChunk> chunks;
-    for (int r = 0; r < N * N;) {
-        const int k_lo = r / N;
-        const int r_hi = std::min({r + CV_ROWS, (k_lo + CV_KC) * N, N * N});
+    for (int r = 0; r < N * NI;) {
+        const int k_lo = r / NI;
+        const int r_hi = std::min({r + CV_ROWS, (k_lo + CV_KC) * NI, N * NI});
         chunks.push_back({r, r_hi, k_lo, 0});
         r = r_hi;
     }
@@ -275,7 +288,7 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
     int nslabs = (int)std::max<long long>(1, std::min<long long>(h->num_sms / (nchunks * njblk), ntiles));
     const long long tps = (ntiles + nslabs - 1) / nslabs;
     nslabs = (int)((ntiles + tps - 1) / tps);
-    if ((rc = dev_ensure(h, cb->ws, (size_t)nslabs * N * N * Jpad * 8))) return rc;
+    if ((rc = dev_ensure(h, cb->ws, (size_t)nslabs * N * NI * Jpad * 8))) return rc;
 
     cudaEvent_t e0, e1, e2;
     cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
@@ -289,7 +302,10 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
     conv_transpose_kernel<<<(unsigned)((3 * nCells + 95) / 96), 256, 0, h->stream>>>(U, ldU, 3 * nCells, N, NP, cb->Ucm.as<double>());
     if (m.nBnd)
         conv_transpose_kernel<<<(unsigned)((3 * m.nBnd + 95) / 96), 256, 0, h->stream>>>(Ub, ldUb, 3 * m.nBnd, N, NP, cb->Ubcm.as<double>());
-    conv_face_prep_kernel<<<(unsigned)((nF + 3) / 4), dim3(64, 4), 0, h->stream>>>(m, cb->Ucm.as<double>(), cb->Ubcm.as<double>(), N, NP,
+    if (Dfm)   // Ni test fields, zero-padded to N by the transpose
+        conv_transpose_kernel<<<(unsigned)((3 * nCells + 95) / 96), 256, 0, h->stream>>>(Dfm, ldD, 3 * nCells, Ni, NP, cb->Dcm.as<double>());
+    conv_face_prep_kernel<<<(unsigned)((nF + 3) / 4), dim3(64, 4), 0, h->stream>>>(m, cb->Ucm.as<double>(), cb->Ubcm.as<double>(),
+                                                                                   Dfm ? cb->Dcm.as<double>() : nullptr, N, NP,
                                                                                    cb->Aj.as<double>(), cb->Bk.as<double>(), cb->Dd.as<double>());
     IB_CUDA(h, cudaGetLastError());
     cudaEventRecord(e1, h->stream);
@@ -304,10 +320,10 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
     auto kern = (CV_KT == 16) ? conv_contract_kernel<16> : conv_contract_kernel<32>;
     IB_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<nchunks * njblk * nslabs, CV_THREADS, smem, h->stream>>>(
-        tmB, cb->Aj.as<double>(), cb->Dd.as<double>(), cb->chunks.as<ConvChunk>(), nchunks, njblk, N, NP, bp, Jpad, tps, ntiles,
+        tmB, cb->Aj.as<double>(), cb->Dd.as<double>(), cb->chunks.as<ConvChunk>(), nchunks, njblk, N, NI, NP, bp, Jpad, tps, ntiles,
         nstages, cb->ws.as<double>());
     IB_CUDA(h, cudaGetLastError());
-    conv_reduce_kernel<<<std::min(4 * h->num_sms, (N * N * N + 255) / 256), 256, 0, h->stream>>>(cb->ws.as<double>(), nslabs, N, Jpad, dC);
+    conv_reduce_kernel<<<std::min(4 * h->num_sms, (N * NI * N + 255) / 256), 256, 0, h->stream>>>(cb->ws.as<double>(), nslabs, N, NI, Jpad, dC);
     IB_CUDA(h, cudaGetLastError());
     cudaEventRecord(e2, h->stream);
     IB_CUDA(h, cudaEventSynchronize(e2));

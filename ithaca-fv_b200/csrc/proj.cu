@@ -89,7 +89,7 @@ void proj_destroy(ithaca_b200* h)
     for (DevBuf* b : {&s->owner, &s->neigh, &s->Sf, &s->magSf, &s->w, &s->dc, &s->dcB, &s->corr, &s->V, &s->bmask,
                       &s->off, &s->ent, &s->other, &s->cnt, &s->blocksum, &s->U, &s->Ub, &s->P, &s->Pb, &s->flux,
                       &s->owner0, &s->neigh0, &s->off0, &s->ent0, &s->other0, &s->perm, &s->fperm, &s->stage, &s->Vw, &s->cmask, &s->Tcm, &s->Lcm, &s->gradP, &s->bndA, &s->bndB,
-                      &s->work, &s->T, &s->out, &s->conv.Ucm, &s->conv.Ubcm, &s->conv.Aj, &s->conv.Bk, &s->conv.Dd,
+                      &s->work, &s->T, &s->out, &s->conv.Ucm, &s->conv.Ubcm, &s->conv.Dcm, &s->conv.Aj, &s->conv.Bk, &s->conv.Dd,
                       &s->conv.ws, &s->conv.chunks})
         if (b->p) cudaFree(b->p);
     delete s;
@@ -1439,7 +1439,6 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
         nout = (size_t)Np * N * N;
         if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
         if ((rc = ensure(h, s->gradP, (size_t)Np * s->ldU * sizeof(double)))) return rc;
-        if ((rc = need_flux(h, s))) return rc;
         {
             StageTimer t(h->stream, &s->ms[3]);
             grad_scalar_kernel<<<dim3(gx(s->nCells), gy(Np)), PROJ_T, 0, h->stream>>>(m, s->P.as<double>(), s->ldP, s->Pb.as<double>(),
@@ -1447,6 +1446,19 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
             t.stop();
             h->launches += 1;
         }
+        // fused face-based form (conv.cu), as for C: G(i,j,k) = sum_f flux_j(f) (Uf_k(f) . (g_i[own] - g_i[nei])), g_i = grad(P_i);
+        // ITHACA_B200_G=mat keeps the materialised div(phi_j, U_k) fields (cross-check)
+        const char* gev = getenv("ITHACA_B200_G");
+        if (Np <= N && !(gev && strcmp(gev, "mat") == 0)) {
+            ConvMesh cm;
+            cm.nInt = s->nInt; cm.nBnd = s->nBnd; cm.owner = m.owner; cm.neigh = m.neigh; cm.Sf = m.Sf; cm.w = m.w; cm.bmask = m.bmask;
+            cm.cmask = shard ? s->cmask.as<unsigned char>() : nullptr;
+            rc = conv_fused_launch(h, &s->conv, cm, s->nCells, U, s->ldU, s->Ub.as<double>(), s->ldUb, N, s->out.as<double>(), &s->ms[6],
+                                   &s->ms[5], s->gradP.as<double>(), s->ldU, Np);   // writes G(i,j,k) at i + Np*(j + N*k)
+            if (rc) return rc;
+            break;
+        }
+        if ((rc = need_flux(h, s))) return rc;
         const size_t percol = (size_t)s->ldU * sizeof(double);
         int jb = (int)std::max<size_t>(1, std::min<size_t>({(size_t)N, 8, (size_t)12e9 / (percol * N)}));
         if ((rc = ensure(h, s->work, (size_t)jb * N * percol))) return rc;

@@ -73,16 +73,22 @@ def test_projected_operators_match_oracle(case):
     assert t["contraction"] > 0 and t["face_records"] > 0
 
 
-def test_ppe_operators_match_oracle(case):
+def test_ppe_operators_match_oracle(case, monkeypatch):
     """steadyNS::projectPPE's additional operators (SURVEY 8(f) rank 1): D, G (divMomentum), BC3, BC4."""
     mesh, orc, pr, (U, Ub, P, Pb) = case
+    monkeypatch.delenv("ITHACA_B200_G", raising=False)
     D = pr.project("D")
     assert rel(D, orc.laplacian_pressure(P, Pb)) <= TOL and np.array_equal(D, D.T)
     assert rel(pr.project("BC4"), orc.pressure_bc4(Ub, Pb)) <= TOL
     assert rel(pr.project("BC3"), orc.pressure_bc3(U, Ub, P, Pb)) <= TOL
     G = pr.project("G")
     Gr = orc.div_momentum(U, Ub, P, Pb)
-    assert G.shape == Gr.shape and rel(G, Gr) <= TOL
+    assert G.shape == Gr.shape and rel(G, Gr) <= TOL          # fused face-based contraction
+    assert pr.timings()["face_records"] > 0
+    monkeypatch.setenv("ITHACA_B200_G", "mat")
+    Gm = pr.project("G")                                        # materialised div(phi_j, U_k) fields
+    assert rel(Gm, Gr) <= TOL and pr.timings()["div_phi"] > 0
+    monkeypatch.delenv("ITHACA_B200_G", raising=False)
 
 
 def test_uncorrected_laplacian(pkg, pod):
