@@ -137,6 +137,27 @@ int ithaca_b200_pod_get_coeffs(ithaca_b200_t* h, int nmodes, double* out);
 int ithaca_b200_pod_reconstruct(ithaca_b200_t* h, int nmodes, const double* coeff, int k, int clip_negative,
                                 double* const* out_ptrs);
 
+/* ---- snapshot-blocked ("memory efficient") POD: ITHACAPOD::getModesMemoryEfficient (ITHACAPOD.C:344-628) -------
+ * For snapshot sets larger than HBM. The reference reads the snapshots pair by pair from disk and
+ * fills the correlation matrix one inner product at a time (:414-451), then accumulates the modes snapshot by snapshot;
+ * here the caller streams BLOCKS of snapshots (as many as fit: two blocks are resident at a time), G is filled one
+ * block pair per contraction launch on the device, and the modes are accumulated block by block.
+ *   block_begin(m_total, dim, nCells)            after pod_set_volumes; zeroes the device correlation matrix
+ *   block_upload(slot, ptrs, nb, first)          slot 0 or 1 <- snapshots [first, first+nb) (host or device pointers)
+ *   block_gram(slotI, slotJ, norm_kind)          G[I, J] (and G[J, I]) = S_I^T W S_J, W = diag(V) for norm_kind 0 ("L2",
+ *                                                computeInnerProduct) or I for 1 ("Frobenius", computeFrobeniusInnerProduct:
+ *                                                unlike getModes, this path does NOT weigh the Frobenius correlation)
+ *   block_gram_finish(G_out)                     all-reduce over ranks, install as the Gram of pod_eig; G_out may be NULL
+ *   pod_eig(...)                                 as for the resident path
+ *   block_lift(slot, r)                          Phi (+)= S_slot Q[first : first+nb, 0:r]   (first call after pod_eig starts a new sum)
+ *   block_lift_finish(r, norm_kind, mode_ptrs, normfact_out)   norms, scaling, download: as pod_lift */
+int ithaca_b200_pod_block_begin(ithaca_b200_t* h, int m_total, int dim, int64_t nCells);
+int ithaca_b200_pod_block_upload(ithaca_b200_t* h, int slot, const double* const* snap_ptrs, int nb, int first);
+int ithaca_b200_pod_block_gram(ithaca_b200_t* h, int slotI, int slotJ, int norm_kind);
+int ithaca_b200_pod_block_gram_finish(ithaca_b200_t* h, double* G_out);
+int ithaca_b200_pod_block_lift(ithaca_b200_t* h, int slot, int r);
+int ithaca_b200_pod_block_lift_finish(ithaca_b200_t* h, int r, int norm_kind, double* const* mode_ptrs, double* normfact_out);
+
 /* ---- Galerkin projection: steadyNS::projectSUP term builders ---------------------------------------
  * (src/ITHACA_FOMPROBLEMS/steadyNS/steadyNS.C:556-707 calls :883-1137; inherited by unsteadyNS,
  *  src/ITHACA_FOMPROBLEMS/unsteadyNS/unsteadyNS.H:61). Scheme set: Gauss linear (grad, div, interpolate),

@@ -25,6 +25,8 @@ SYMBOLS = [
     "ithaca_b200_dmma_peak",
     "ithaca_b200_pod_set_modes", "ithaca_b200_pod_project", "ithaca_b200_pod_modes_mass", "ithaca_b200_pod_get_coeffs",
     "ithaca_b200_pod_reconstruct",
+    "ithaca_b200_pod_block_begin", "ithaca_b200_pod_block_upload", "ithaca_b200_pod_block_gram",
+    "ithaca_b200_pod_block_gram_finish", "ithaca_b200_pod_block_lift", "ithaca_b200_pod_block_lift_finish",
     "ithaca_b200_mesh_upload", "ithaca_b200_mesh_addressing", "ithaca_b200_basis_upload", "ithaca_b200_project",
     "ithaca_b200_fvc_eval", "ithaca_b200_proj_timings",
     "ithaca_b200_partition_create", "ithaca_b200_partition_destroy", "ithaca_b200_partition_sizes",
@@ -71,6 +73,12 @@ def lib():
         L.ithaca_b200_pod_lift_patch.argtypes = [P, P, L64, P]
         L.ithaca_b200_dmma_peak.argtypes = [I, ctypes.POINTER(D)]
         L.ithaca_b200_pod_set_modes.argtypes = [P, P, I]
+        L.ithaca_b200_pod_block_begin.argtypes = [P, I, I, L64]
+        L.ithaca_b200_pod_block_upload.argtypes = [P, I, P, I, I]
+        L.ithaca_b200_pod_block_gram.argtypes = [P, I, I, I]
+        L.ithaca_b200_pod_block_gram_finish.argtypes = [P, P]
+        L.ithaca_b200_pod_block_lift.argtypes = [P, I, I]
+        L.ithaca_b200_pod_block_lift_finish.argtypes = [P, I, I, P, P]
         L.ithaca_b200_pod_project.argtypes = [P, I, I, P]
         L.ithaca_b200_pod_modes_mass.argtypes = [P, I, P]
         L.ithaca_b200_pod_get_coeffs.argtypes = [P, I, P]
@@ -430,6 +438,51 @@ class Projector:
         out = np.zeros(7)
         self.pod._chk(self.L.ithaca_b200_proj_timings(self.h, out.ctypes.data, 7))
         return dict(zip(self.TIMER_NAMES, out.tolist()))
+
+
+def getModesMemoryEfficient(pod, block_source, m, V, dim, nmodes=0, solver="spectra", norm="L2", block=64, want_modes=True):
+    """Snapshot-blocked POD (ITHACAPOD::getModesMemoryEfficient, ITHACAPOD.C:344-628) through the C ABI.
+    block_source(first, nb) -> list of nb snapshot buffers (numpy arrays or torch tensors, nCells*dim doubles each):
+    the caller streams them from disk / host / a generator; two blocks are resident on the device at a time."""
+    if norm not in ("L2", "Frobenius"):
+        raise IthacaB200Error("The PODnorm can be only L2 or Frobenius")
+    nmodes = check_nmodes(m, nmodes, solver)
+    nk = 0 if norm == "L2" else 1
+    L, h = pod.L, pod.h
+    nCells = V.shape[0]
+    pod.set_volumes(V)
+    pod._chk(L.ithaca_b200_pod_block_begin(h, m, dim, nCells))
+    pod.m, pod.dim = m, dim
+    starts = list(range(0, m, block))
+
+    def up(slot, first):
+        nb = min(block, m - first)
+        bufs = block_source(first, nb)
+        arr = (ctypes.c_void_p * nb)(*[_ptr(b) for b in bufs])
+        pod._chk(L.ithaca_b200_pod_block_upload(h, slot, arr, nb, first))
+        return bufs
+
+    for bi, fi in enumerate(starts):          # block pairs (I, J >= I): block I stays in slot 0, J streams through slot 1
+        keep = up(0, fi)
+        pod._chk(L.ithaca_b200_pod_block_gram(h, 0, 0, nk))
+        for fj in starts[bi + 1:]:
+            keep2 = up(1, fj)
+            pod._chk(L.ithaca_b200_pod_block_gram(h, 0, 1, nk))
+    G = np.zeros((m, m), order="F")
+    pod._chk(L.ithaca_b200_pod_block_gram_finish(h, G.ctypes.data))
+    ev_all, Q = pod.eig(nmodes)
+    for fi in starts:
+        keep = up(0, fi)
+        pod._chk(L.ithaca_b200_pod_block_lift(h, 0, nmodes))
+    nf = np.zeros(nmodes)
+    Phi = arr = None
+    if want_modes:
+        Phi = np.zeros((nCells * dim, nmodes), order="F")
+        arr = (ctypes.c_void_p * nmodes)(*[Phi.ctypes.data + i * Phi.strides[1] for i in range(nmodes)])
+    pod._chk(L.ithaca_b200_pod_block_lift_finish(h, nmodes, nk, arr, nf.ctypes.data))
+    pod.r = nmodes
+    evn, cum = postprocess_eigenvalues(ev_all, nmodes, solver)
+    return dict(G=G, evals_all=ev_all, evals_norm=evn, cum=cum, evecs=Q, normfact=nf, modes=Phi)
 
 
 def check_nmodes(m, nmodes, solver):

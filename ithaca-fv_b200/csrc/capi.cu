@@ -210,7 +210,7 @@ int ithaca_b200_destroy(ithaca_b200_t* h)
     if (h->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->nccl_comm);
     for (void* p : {(void*)h->dV, (void*)h->dS, (void*)h->dG, (void*)h->dWs, (void*)h->dQ, (void*)h->dW,
                     (void*)h->dEvals, (void*)h->dQr, (void*)h->dPhi, (void*)h->dNormPart, (void*)h->dNorm,
-                    h->dJobs, (void*)h->dFlags, h->wexp[0].p, h->wexp[1].p})
+                    h->dJobs, (void*)h->dFlags, h->wexp[0].p, h->wexp[1].p, (void*)h->dS2, (void*)h->dPhiTmp})
         if (p) cudaFree(p);
     for (int i = 0; i < T_COUNT; i++) {
         cudaEventDestroy(h->timers[i].a);
@@ -319,6 +319,7 @@ int ithaca_b200_pod_upload(ithaca_b200_t* h, const double* const* snap_ptrs, int
     tstop(h, T_UPLOAD);
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
     h->m = m; h->dim = dim; h->Nd = Nd; h->ld = ld;
+    h->block_mode = false;
     h->have_gram = h->have_eig = h->have_lift = h->have_modes = false;
     return IB200_OK;
 }
@@ -618,6 +619,145 @@ int ithaca_b200_pod_reconstruct(ithaca_b200_t* h, int nmodes, const double* coef
     cudaFree(dOut);
     if (rc) return rc;
     IB_CUDA(h, e);
+    return IB200_OK;
+}
+
+// ---- snapshot-blocked POD (getModesMemoryEfficient, ITHACAPOD.C:344-628) ----------------------------------------
+
+// G[J, I] = G[I, J]^T for an off-diagonal block pair (rows i0.., cols j0.. of the m x m col-major matrix)
+__global__ void mirror_block_kernel(double* __restrict__ G, int m, int i0, int ni, int j0, int nj)
+{
+    const int total = ni * nj;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+        const int i = idx % ni, j = idx / ni;
+        G[(size_t)(j0 + j) + (size_t)(i0 + i) * m] = G[(size_t)(i0 + i) + (size_t)(j0 + j) * m];
+    }
+}
+
+int ithaca_b200_pod_block_begin(ithaca_b200_t* h, int m_total, int dim, int64_t nCells)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (m_total <= 0 || dim <= 0 || nCells <= 0) { set_error(h, "pod_block_begin: bad argument"); return IB200_ERR_ARG; }
+    if (h->nCells != nCells) { set_error(h, "pod_block_begin: nCells differs from pod_set_volumes"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    int rc = ensure_mats(h, m_total);
+    if (rc) return rc;
+    h->m = m_total; h->dim = dim; h->Nd = nCells * dim; h->ld = (h->Nd + 15) / 16 * 16;
+    IB_CUDA(h, cudaMemsetAsync(h->dG, 0, (size_t)m_total * m_total * sizeof(double), h->stream));
+    h->blk_n[0] = h->blk_n[1] = 0;
+    h->blk_lifted = 0;
+    h->block_mode = true;
+    h->have_gram = h->have_eig = h->have_lift = h->have_modes = false;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_block_upload(ithaca_b200_t* h, int slot, const double* const* snap_ptrs, int nb, int first)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->block_mode) { set_error(h, "pod_block_upload: call pod_block_begin first"); return IB200_ERR_ARG; }
+    if ((slot != 0 && slot != 1) || !snap_ptrs || nb <= 0 || first < 0 || first + nb > h->m) {
+        set_error(h, "pod_block_upload: bad argument");
+        return IB200_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    double** buf = slot == 0 ? &h->dS : &h->dS2;
+    size_t* cap = slot == 0 ? &h->dS_cap : &h->dS2_cap;
+    int rc = ensure(h, buf, cap, (size_t)h->ld * nb * sizeof(double));
+    if (rc) return rc;
+    tstart(h, T_UPLOAD);
+    for (int j = 0; j < nb; j++) {
+        if (!snap_ptrs[j]) { set_error(h, "pod_block_upload: null snapshot pointer"); return IB200_ERR_ARG; }
+        IB_CUDA(h, cudaMemcpyAsync(*buf + (size_t)j * h->ld, snap_ptrs[j], (size_t)h->Nd * sizeof(double), cudaMemcpyDefault, h->stream));
+    }
+    tstop(h, T_UPLOAD);
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->blk_n[slot] = nb; h->blk_first[slot] = first;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_block_gram(ithaca_b200_t* h, int slotI, int slotJ, int norm_kind)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->block_mode || (slotI != 0 && slotI != 1) || (slotJ != 0 && slotJ != 1) || h->blk_n[slotI] <= 0 || h->blk_n[slotJ] <= 0) {
+        set_error(h, "pod_block_gram: upload both blocks first");
+        return IB200_ERR_ARG;
+    }
+    if (norm_kind != 0 && norm_kind != 1) { set_error(h, "pod_block_gram: The PODnorm can be only L2 or Frobenius"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    const double* SI = slotI == 0 ? h->dS : h->dS2;
+    const double* SJ = slotJ == 0 ? h->dS : h->dS2;
+    const int ni = h->blk_n[slotI], nj = h->blk_n[slotJ], i0 = h->blk_first[slotI], j0 = h->blk_first[slotJ];
+    tstart(h, T_GRAM);
+    int rc = atvb_launch(h, SI, h->ld, ni, SJ, h->ld, nj, h->Nd, norm_kind == 0 ? h->dV : nullptr, h->dim, slotI == slotJ ? 1 : 0,
+                         h->dG + (size_t)i0 + (size_t)j0 * h->m, 1, 0x7fffffff, 0, h->m);
+    if (rc) return rc;
+    if (slotI != slotJ) {
+        mirror_block_kernel<<<std::min(1024, (ni * nj + 255) / 256), 256, 0, h->stream>>>(h->dG, h->m, i0, ni, j0, nj);
+        h->launches += 1;
+    }
+    tstop(h, T_GRAM);
+    IB_CUDA(h, cudaGetLastError());
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_block_gram_finish(ithaca_b200_t* h, double* G_out)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->block_mode) { set_error(h, "pod_block_gram_finish: call pod_block_begin first"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    tstart(h, T_ALLREDUCE);
+    int rc = allreduce_sum(h, h->dG, (size_t)h->m * h->m);
+    tstop(h, T_ALLREDUCE);
+    if (rc) return rc;
+    if (G_out) IB_CUDA(h, cudaMemcpyAsync(G_out, h->dG, (size_t)h->m * h->m * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->have_gram = true;
+    h->have_eig = false;
+    h->blk_lifted = 0;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_block_lift(ithaca_b200_t* h, int slot, int r)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->block_mode || !h->have_eig || (slot != 0 && slot != 1) || h->blk_n[slot] <= 0) {
+        set_error(h, "pod_block_lift: needs pod_block_gram_finish, pod_eig and an uploaded block");
+        return IB200_ERR_ARG;
+    }
+    if (r <= 0 || r > h->m) { set_error(h, "pod_block_lift: The number of requested modes cannot be bigger than the number of Snapshots"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    const bool acc = h->blk_lifted > 0;
+    if (acc) {
+        int rc = ensure(h, &h->dPhiTmp, &h->dPhiTmp_cap, (size_t)h->ld * r * sizeof(double));
+        if (rc) return rc;
+    }
+    int rc = lift_block_launch(h, slot == 0 ? h->dS : h->dS2, h->blk_n[slot], h->blk_first[slot], r, acc, h->dPhiTmp);
+    if (rc) return rc;
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->blk_lifted++;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_block_lift_finish(ithaca_b200_t* h, int r, int norm_kind, double* const* mode_ptrs, double* normfact_out)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->block_mode || h->blk_lifted <= 0 || r != h->r) { set_error(h, "pod_block_lift_finish: call pod_block_lift for every block first (same r)"); return IB200_ERR_ARG; }
+    if (norm_kind != 0 && norm_kind != 1) { set_error(h, "pod_block_lift_finish: The PODnorm can be only L2 or Frobenius"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    int rc = lift_block_finish(h, r, norm_kind);
+    if (rc) return rc;
+    tstart(h, T_DOWNLOAD);
+    if (mode_ptrs)
+        for (int i = 0; i < r; i++) {
+            if (!mode_ptrs[i]) { set_error(h, "pod_block_lift_finish: null mode pointer"); return IB200_ERR_ARG; }
+            IB_CUDA(h, cudaMemcpyAsync(mode_ptrs[i], h->dPhi + (size_t)i * h->ld, (size_t)h->Nd * sizeof(double), cudaMemcpyDefault, h->stream));
+        }
+    if (normfact_out) IB_CUDA(h, cudaMemcpyAsync(normfact_out, h->dNorm, (size_t)r * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    tstop(h, T_DOWNLOAD);
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->have_modes = true;
+    h->blk_lifted = 0;
     return IB200_OK;
 }
 

@@ -145,6 +145,9 @@ int eig_launch(ithaca_b200* h, int* sweeps);
 // lift.cu
 int lift_launch(ithaca_b200* h, int r, int norm_kind);
 int lift_patch_launch(ithaca_b200* h, const double* dSbc, int64_t rows, double* dOut);
+// snapshot-blocked lift: Phi (+)= S Q[first : first+nb, 0:r] (dTmp: r columns of ld doubles when accumulating); finish = norms + scale
+int lift_block_launch(ithaca_b200* h, const double* S, int nb, int first, int r, bool accumulate, double* dTmp);
+int lift_block_finish(ithaca_b200* h, int r, int norm_kind);
 // out[:, j] = Phi[:, 0:nmodes] * C[:, j] for j < kc <= 8 (C: nmodes x kc col-major on the device); out columns of ld doubles
 int reconstruct_launch(ithaca_b200* h, int nmodes, const double* dC, int kc, int clip, double* dOut);
 // gram.cu: general weighted contraction  out(i,j) = sum_k A(k,i) * V[k/dim] * B(k,j)  (V == nullptr: unweighted).
@@ -201,7 +204,15 @@ struct ithaca_b200 {
     double* dNorm = nullptr;  // rpad doubles: squared norms then norm factors
     int norm_cap = 0;
     bool have_lift = false;
-    bool have_modes = false;   // dPhi holds h->r modes (from pod_lift or pod_set_modes)
+    bool have_modes = false;
+    // snapshot-blocked (memory-efficient) POD: two resident snapshot blocks, slot 0 = dS
+    double* dS2 = nullptr;
+    size_t dS2_cap = 0;
+    int blk_n[2] = {0, 0}, blk_first[2] = {0, 0};
+    bool block_mode = false;
+    int blk_lifted = 0;   // blocks accumulated into dPhi so far
+    double* dPhiTmp = nullptr;
+    size_t dPhiTmp_cap = 0;   // dPhi holds h->r modes (from pod_lift or pod_set_modes)
     void* dJobs = nullptr;
     size_t dJobs_cap = 0;
     // dim-times repeated weight vectors of the contraction kernel (gram.cu), keyed on (V, dim, K, vol_gen)

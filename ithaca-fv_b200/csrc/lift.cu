@@ -24,13 +24,13 @@ constexpr int LIFT_KT = 16;      // snapshots per stage
 constexpr int LIFT_SBOX = 16 * LIFT_KT * 8;  // bytes of one S box (16 rows x 16 snapshots)
 constexpr int LIFT_THREADS = 288;            // 8 MMA warps + 1 producer warp
 
-// Qr[k][n] = Q[k + n*m] for n < r, 0 for the padding columns; pitch = rpad + 2.
-__global__ void lift_prep_q_kernel(const double* __restrict__ Q, int m, int r, int pitch, double* __restrict__ Qr)
+// Qr[k][n] = Q[k + n*ldq] for k < m, n < r, 0 for the padding columns; pitch = rpad + 2.
+__global__ void lift_prep_q_kernel(const double* __restrict__ Q, int m, int ldq, int r, int pitch, double* __restrict__ Qr)
 {
     const int total = m * pitch;
     for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
         const int k = idx / pitch, n = idx % pitch;
-        Qr[idx] = (n < r) ? Q[(size_t)k + (size_t)n * m] : 0.0;
+        Qr[idx] = (n < r) ? Q[(size_t)k + (size_t)n * ldq] : 0.0;
     }
 }
 
@@ -214,7 +214,7 @@ __global__ void lift_patch_kernel(const double* __restrict__ Sbc, long long rows
 }
 
 template <int NB>
-static int lift_run(ithaca_b200* h, int r, int norm_kind, const CUtensorMap& tmS, const CUtensorMap& tmQ,
+static int lift_run(ithaca_b200* h, int m, double* Phi, int r, int norm_kind, const CUtensorMap& tmS, const CUtensorMap& tmQ,
                     int pitch, int qstage_bytes, long long ntiles, int* grid_out)
 {
     const int stage_bytes = 8 * LIFT_SBOX + qstage_bytes;
@@ -234,16 +234,15 @@ static int lift_run(ithaca_b200* h, int r, int norm_kind, const CUtensorMap& tmS
         h->dNormPart_cap = need;
     }
     lift_kernel<NB><<<grid, LIFT_THREADS, smem, h->stream>>>(tmS, tmQ, h->dV, h->dim, norm_kind, h->Nd, h->ld,
-                                                             h->m, r, pitch, qstage_bytes, nstages, ntiles,
-                                                             h->dPhi, h->dNormPart);
+                                                             m, r, pitch, qstage_bytes, nstages, ntiles,
+                                                             Phi, h->dNormPart);
     IB_CUDA(h, cudaGetLastError());
     *grid_out = grid;
     return IB200_OK;
 }
 
-int lift_launch(ithaca_b200* h, int r, int norm_kind)
+static int lift_ensure(ithaca_b200* h, int m, int r, int* NB_out)
 {
-    const int m = h->m;
     if (r > 104) { set_error(h, "pod_lift: at most 104 modes per call are supported"); return IB200_ERR_ARG; }
     const int nbs[] = {2, 3, 4, 7, 13};
     int NB = 13;
@@ -269,28 +268,39 @@ int lift_launch(ithaca_b200* h, int r, int norm_kind)
         IB_CUDA(h, cudaMalloc(&h->dNorm, 104 * sizeof(double)));
         h->norm_cap = 104;
     }
-    h->r = r; h->rpad = rpad;
+    *NB_out = NB;
+    return IB200_OK;
+}
 
-    cudaEventRecord(h->timers[T_LIFT].a, h->stream);
-    lift_prep_q_kernel<<<std::min(1024, (m * pitch + 255) / 256), 256, 0, h->stream>>>(h->dQ, m, r, pitch, h->dQr);
+// Phi = S Q: S = m columns of h->ld doubles, Q = rows [0, m) and columns [0, r) of a col-major matrix with leading
+// dimension ldq. The kernel also leaves the partial squared norms of what it wrote in h->dNormPart (grid x rpad).
+static int lift_core(ithaca_b200* h, const double* S, int m, const double* Q, int ldq, int r, int NB, int norm_kind, double* Phi,
+                     int* grid_out)
+{
+    const int rpad = NB * 8, pitch = rpad + 2;
+    lift_prep_q_kernel<<<std::min(1024, (m * pitch + 255) / 256), 256, 0, h->stream>>>(Q, m, ldq, r, pitch, h->dQr);
     CUtensorMap tmS, tmQ;
-    int rc = make_tmap_2d(h, &tmS, h->dS, (uint64_t)h->Nd, (uint64_t)m, (uint64_t)h->ld * 8, 16, LIFT_KT, true);
+    int rc = make_tmap_2d(h, &tmS, S, (uint64_t)h->Nd, (uint64_t)m, (uint64_t)h->ld * 8, 16, LIFT_KT, true);
     if (rc) return rc;
     rc = make_tmap_2d(h, &tmQ, h->dQr, (uint64_t)pitch, (uint64_t)m, (uint64_t)pitch * 8, (uint32_t)pitch, LIFT_KT, false);
     if (rc) return rc;
     const int qstage_bytes = (LIFT_KT * pitch * 8 + 1023) / 1024 * 1024;
     const long long ntiles = (h->Nd + LIFT_ROWS - 1) / LIFT_ROWS;
-    int grid = 0;
     switch (NB) {
-        case 2: rc = lift_run<2>(h, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, &grid); break;
-        case 3: rc = lift_run<3>(h, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, &grid); break;
-        case 4: rc = lift_run<4>(h, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, &grid); break;
-        case 7: rc = lift_run<7>(h, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, &grid); break;
-        default: rc = lift_run<13>(h, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, &grid); break;
+        case 2: rc = lift_run<2>(h, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
+        case 3: rc = lift_run<3>(h, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
+        case 4: rc = lift_run<4>(h, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
+        case 7: rc = lift_run<7>(h, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
+        default: rc = lift_run<13>(h, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
     }
-    if (rc) return rc;
-    lift_norm_reduce_kernel<<<r, 256, 0, h->stream>>>(h->dNormPart, grid, rpad, h->dNorm);
-    rc = allreduce_sum(h, h->dNorm, (size_t)r);
+    h->launches += 2;
+    return rc;
+}
+
+// squared norms (already in h->dNorm, per rank) -> all-reduce -> sqrt -> Phi(:, c) /= n_c
+static int lift_finalize(ithaca_b200* h, int r)
+{
+    int rc = allreduce_sum(h, h->dNorm, (size_t)r);
     if (rc) return rc;
     lift_sqrt_kernel<<<1, 128, 0, h->stream>>>(h->dNorm, r);
     cudaEventRecord(h->timers[T_LIFT].b, h->stream);
@@ -301,8 +311,86 @@ int lift_launch(ithaca_b200* h, int r, int norm_kind)
     cudaEventRecord(h->timers[T_SCALE].b, h->stream);
     h->timers[T_SCALE].used = true;
     IB_CUDA(h, cudaGetLastError());
-    h->launches += 5;
+    h->launches += 2;
     return IB200_OK;
+}
+
+int lift_launch(ithaca_b200* h, int r, int norm_kind)
+{
+    int NB = 0;
+    int rc = lift_ensure(h, h->m, r, &NB);
+    if (rc) return rc;
+    h->r = r; h->rpad = NB * 8;
+    cudaEventRecord(h->timers[T_LIFT].a, h->stream);
+    int grid = 0;
+    if ((rc = lift_core(h, h->dS, h->m, h->dQ, h->m, r, NB, norm_kind, h->dPhi, &grid))) return rc;
+    lift_norm_reduce_kernel<<<r, 256, 0, h->stream>>>(h->dNormPart, grid, h->rpad, h->dNorm);
+    h->launches += 1;
+    return lift_finalize(h, r);
+}
+
+// ---- snapshot-blocked lift (memory-efficient POD, ITHACAPOD.C:344-628): Phi (+)= S_block Q[first : first+nb, 0:r] ----
+__global__ void axpy_cols_kernel(double* __restrict__ y, const double* __restrict__ x, long long Nd, long long ld, int r)
+{
+    const int c = blockIdx.y;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < Nd; i += (long long)gridDim.x * blockDim.x)
+        y[(size_t)c * ld + i] += x[(size_t)c * ld + i];
+}
+
+// part[blockIdx.x][c] = sum over this block's rows of w_k Phi(k,c)^2, w = V[k/dim] (L2) or 1 (Frobenius)
+__global__ void __launch_bounds__(256)
+phi_norm_part_kernel(const double* __restrict__ Phi, long long Nd, long long ld, int r, const double* __restrict__ V, int dim,
+                     int norm_kind, double* __restrict__ part)
+{
+    __shared__ double sh[256];
+    const int c = blockIdx.y;
+    const double* col = Phi + (size_t)c * ld;
+    double s = 0.0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < Nd; i += (long long)gridDim.x * blockDim.x) {
+        const double v = col[i];
+        s += (norm_kind == 0 ? V[i / dim] : 1.0) * v * v;
+    }
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) part[(size_t)blockIdx.x * r + c] = sh[0];
+}
+
+int lift_block_launch(ithaca_b200* h, const double* S, int nb, int first, int r, bool accumulate, double* dTmp)
+{
+    int NB = 0;
+    int rc = lift_ensure(h, nb, r, &NB);
+    if (rc) return rc;
+    h->r = r; h->rpad = NB * 8;
+    int grid = 0;
+    if ((rc = lift_core(h, S, nb, h->dQ + first, h->m, r, NB, 1, accumulate ? dTmp : h->dPhi, &grid))) return rc;
+    if (accumulate) {
+        dim3 g((unsigned)std::min<long long>((h->Nd + 1023) / 1024, 4LL * h->num_sms), (unsigned)r);
+        axpy_cols_kernel<<<g, 256, 0, h->stream>>>(h->dPhi, dTmp, h->Nd, h->ld, r);
+        h->launches += 1;
+    }
+    IB_CUDA(h, cudaGetLastError());
+    return IB200_OK;
+}
+
+int lift_block_finish(ithaca_b200* h, int r, int norm_kind)
+{
+    const int nblk = (int)std::min<long long>((h->Nd + 4095) / 4096, 4LL * h->num_sms);
+    const size_t need = (size_t)nblk * r * sizeof(double);
+    if (need > h->dNormPart_cap) {
+        if (h->dNormPart) cudaFree(h->dNormPart);
+        h->dNormPart = nullptr; h->dNormPart_cap = 0;
+        IB_CUDA(h, cudaMalloc(&h->dNormPart, need));
+        h->dNormPart_cap = need;
+    }
+    cudaEventRecord(h->timers[T_LIFT].a, h->stream);
+    phi_norm_part_kernel<<<dim3(nblk, r), 256, 0, h->stream>>>(h->dPhi, h->Nd, h->ld, r, h->dV, h->dim, norm_kind, h->dNormPart);
+    lift_norm_reduce_kernel<<<r, 256, 0, h->stream>>>(h->dNormPart, nblk, r, h->dNorm);
+    h->launches += 2;
+    return lift_finalize(h, r);
 }
 
 // ---- Modes::reconstruct (Containers/Modes.C:294-305): out_j = Phi[:, 0:n] c_j, up to RC_K columns per launch -------------

@@ -223,3 +223,34 @@ def test_project_getcoeffs_reconstruct_match_oracle(pkg, pod, Nc, dim, m, r):
         assert rel_max(back, S) <= 1e-8
     with pytest.raises(pkg.IthacaB200Error):
         pod.get_coeffs(r + 1)
+
+
+@pytest.mark.parametrize("Nc,dim,m,r,block,solver,norm", [(4099, 3, 37, 6, 16, "eigen", "L2"), (3001, 1, 50, 8, 7, "spectra", "Frobenius"),
+                                                          (777, 3, 20, 5, 64, "eigen", "L2")])
+def test_memory_efficient_blocked_pod_matches_oracle(pkg, pod, Nc, dim, m, r, block, solver, norm):
+    """getModesMemoryEfficient (ITHACAPOD.C:344-628) with the snapshots streamed in blocks (two
+    resident at a time); ragged last block, one-block case, both norms (Frobenius: unweighted correlation here)."""
+    S = synth.snapshots(Nc, dim, m, 2 * r, 91)
+    V = synth.volumes(Nc, 91)
+    calls = []
+
+    def source(first, nb):
+        calls.append((first, nb))
+        return [np.ascontiguousarray(S[:, j]) for j in range(first, first + nb)]
+
+    out = pkg.getModesMemoryEfficient(pod, source, m, V, dim, r, solver, norm, block=block)
+    ref = po.getmodes_memory_efficient(S, V, dim, r, solver, norm)
+    assert rel_max(out["G"], ref["G"]) <= 1e-13
+    assert np.array_equal(out["G"], out["G"].T)
+    assert len(out["evals_norm"]) == len(ref["evals_norm"])
+    assert np.all(np.abs(out["evals_norm"][:r] - ref["evals_norm"][:r]) <= 1e-10 * ref["evals_norm"][:r])
+    assert np.all(np.abs(out["normfact"] - ref["normfact"]) <= 1e-9 * ref["normfact"])
+    assert modes_rel(out["modes"], ref["modes"]) <= 1e-8
+    assert max(nb for _, nb in calls) <= block
+    if norm == "L2":   # same numbers as the resident path
+        res = pkg.getModes(pod, S, V, dim, r, solver, norm)
+        assert rel_max(out["G"], res["G"]) <= 1e-13 and modes_rel(out["modes"], res["modes"]) <= 1e-8
+    # the resident-mode follow-ups work on the blocked result too
+    pod.upload(S, dim)
+    pod.set_modes(np.asfortranarray(out["modes"]))
+    assert rel_max(pod.project(0, "G"), po.project(S, V, dim, out["modes"], 0, "G")) <= 1e-12
