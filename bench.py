@@ -23,6 +23,9 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# stdout carries ONE JSON line: keep NCCL's version banner (NCCL_DEBUG=VERSION prints it on stdout) out of it
+if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+    os.environ["NCCL_DEBUG"] = "WARN"
 
 import numpy as np  # noqa: E402
 
@@ -34,6 +37,9 @@ WORKLOADS = {
                  name="C3/8: one rank's shard of C3 at 8 GPUs, 2.5M cells x 1000 vector FP64 snapshots (60 GB), 50 modes (per rank)"),
     "c3": dict(cells=20_000_000, dim=3, m=1000, r=50, sharded=True,
                name="C3 20M cells x 1000 vector FP64 snapshots, 50 modes (cell-sharded over ranks)"),
+    "c3blk": dict(cells=20_000_000, dim=3, m=1000, r=50, sharded=True, blocked=True,
+                  name="C3 20M cells x 1000 vector FP64 snapshots, 50 modes, cell-sharded over ranks, snapshots streamed in "
+                       "blocks (getModesMemoryEfficient path: for N = 1, 2 where 480 GB / N exceeds HBM)"),
 }
 METRIC = "pod_time_to_modes"
 UNIT = "s"
@@ -214,6 +220,121 @@ def run_reference_arm(args, wl, rank, world):
 # ------------------------------------------------------------------------------------------------
 # B200 arm
 # ------------------------------------------------------------------------------------------------
+def run_blocked(args, wl, rank, local_rank, world, torch, dist, pkg, pod, dev):
+    """C3 with the snapshots streamed in blocks through the ithaca_b200_pod_block_* calls. The block source is a device-side
+    synthetic generator (stand-in for the reference's readFieldByIndex from disk, which is excluded from its timing story
+    too): `value` is the summed device time of the LIBRARY calls (block Grams, all-reduce, eigensolve, block lifts, norms +
+    scale), measured with CUDA events on the library's stream; generation and the D2D block copies are reported apart."""
+    import ctypes
+    dim, m, r = wl["dim"], wl["m"], wl["r"]
+    b, e = pkg.cell_range(wl["cells"], rank, world)
+    cells = e - b
+    Nd = cells * dim
+    nbk = int(os.environ.get("ITHACA_B200_BENCH_BLOCK", str(min(200, 80 * world))))   # 3 block buffers + 2 mode buffers must fit HBM
+    g = torch.Generator(device=dev)
+    g.manual_seed(20251104 + 17 * rank)
+    R = 64
+    coef, _ = torch.linalg.qr(torch.randn(m, R, generator=g, device=dev, dtype=torch.float64))
+    sig = 1.0 / torch.arange(1, R + 1, device=dev, dtype=torch.float64)
+    V = torch.exp(0.5 * torch.randn(cells, generator=g, device=dev, dtype=torch.float64))
+    V /= V.sum() * world
+    blk = torch.empty((nbk, Nd), device=dev, dtype=torch.float64)
+    kk = torch.arange(1, R + 1, device=dev, dtype=torch.float64)
+
+    def gen(first, nb):   # rows = snapshots [first, first+nb) of this rank's cells; deterministic in (rank, first)
+        gb = torch.Generator(device=dev)
+        gb.manual_seed(977 * rank + first + 1)
+        chunk = 1 << 20
+        for r0 in range(0, Nd, chunk):
+            r1 = min(Nd, r0 + chunk)
+            x = (torch.arange(r0, r1, device=dev, dtype=torch.float64) + 0.5) / Nd
+            U = torch.sin(x[:, None] * kk[None, :] * 3.141592653589793) * torch.cos(x[:, None] * (kk[None, :] + 1.0))
+            part = (coef[first:first + nb] * sig) @ U.T
+            part += 1e-6 * torch.randn(nb, r1 - r0, generator=gb, device=dev, dtype=torch.float64)
+            blk[:nb, r0:r1] = part
+        return [blk[j] for j in range(nb)]
+
+    L, h = pod.L, pod.h
+    stream = torch.cuda.ExternalStream(pod.stream, device=dev)
+    peak_dmma = pkg.dmma_peak(local_rank)
+    starts = list(range(0, m, nbk))
+    acc = {"gram": 0.0, "allreduce": 0.0, "eig": 0.0, "lift": 0.0, "scale": 0.0, "gram_kernel": 0.0}
+    t_gen = 0.0
+
+    def up(slot, first):
+        nonlocal t_gen
+        nb = min(nbk, m - first)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        bufs = gen(first, nb)
+        torch.cuda.synchronize()
+        arr = (ctypes.c_void_p * nb)(*[x.data_ptr() for x in bufs])
+        pod._chk(L.ithaca_b200_pod_block_upload(h, slot, arr, nb, first))
+        t_gen += time.perf_counter() - t0
+
+    def timed(fn, key):   # device time of one library call on its own stream
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        fn()
+        e1.record(stream)
+        e1.synchronize()
+        acc[key] += e0.elapsed_time(e1)
+
+    pod.set_volumes(V)
+    # untimed warm-up of the communicator (the first collective sets up the NVLink connections) and of the kernels' first launch
+    pod._chk(L.ithaca_b200_pod_block_begin(h, m, dim, cells))
+    up(0, 0)
+    pod._chk(L.ithaca_b200_pod_block_gram(h, 0, 0, 0))
+    pod._chk(L.ithaca_b200_pod_block_gram_finish(h, None))
+    t_gen = 0.0
+    launches0 = pod.launch_count(reset=True)
+    t_wall = time.perf_counter()
+    pod._chk(L.ithaca_b200_pod_block_begin(h, m, dim, cells))
+    pod.m, pod.dim = m, dim
+    for bi, fi in enumerate(starts):
+        up(0, fi)
+        timed(lambda: pod._chk(L.ithaca_b200_pod_block_gram(h, 0, 0, 0)), "gram")
+        acc["gram_kernel"] += pod.timings()["gram_kernel"]
+        for fj in starts[bi + 1:]:
+            up(1, fj)
+            timed(lambda: pod._chk(L.ithaca_b200_pod_block_gram(h, 0, 1, 0)), "gram")
+            acc["gram_kernel"] += pod.timings()["gram_kernel"]
+    timed(lambda: pod._chk(L.ithaca_b200_pod_block_gram_finish(h, None)), "allreduce")
+    timed(lambda: pod.eig(r), "eig")
+    for fi in starts:
+        up(0, fi)
+        timed(lambda: pod._chk(L.ithaca_b200_pod_block_lift(h, 0, r)), "lift")
+    nf = np.zeros(r)
+    timed(lambda: pod._chk(L.ithaca_b200_pod_block_lift_finish(h, r, 0, None, nf.ctypes.data)), "scale")
+    torch.cuda.synchronize()
+    wall = time.perf_counter() - t_wall
+    lib_ms = acc["gram"] + acc["allreduce"] + acc["eig"] + acc["lift"] + acc["scale"]
+    tt = torch.tensor([lib_ms, wall, t_gen], device=dev, dtype=torch.float64)
+    if dist is not None:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    if rank != 0:
+        return
+    gram_flops = float(Nd) * m * (m + 1)
+    line = {
+        "metric": METRIC, "value": tt[0].item() / 1e3, "unit": UNIT, "n_gpus": world, "steps": 1, "warmup": 0,
+        "ms_per_step": tt[0].item(), "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic", "config": {"workload": wl["name"], "cells_total": wl["cells"], "cells_per_rank": cells, "dim": dim,
+                                        "snapshots": m, "modes": r, "block": nbk, "blocks": len(starts),
+                                        "block_pairs": len(starts) * (len(starts) + 1) // 2,
+                                        "l2": "every block (%.1f GB) larger than L2" % (nbk * Nd * 8 / 1e9),
+                                        "eigensolver": "one-sided Jacobi (%d sweeps)" % pod.sweeps},
+        "roofline": {"bound": "tensor", "kernel": "gram_kernel (block pairs)", "achieved": gram_flops / (acc["gram"] * 1e-3) / 1e12,
+                     "peak": peak_dmma, "unit": "TFLOP/s", "frac": gram_flops / (acc["gram"] * 1e-3) / 1e12 / peak_dmma, "traffic": None,
+                     "algorithmic_flops_per_launch": gram_flops / (len(starts) * (len(starts) + 1) // 2),
+                     "note": "SYRK flop count of the whole m x m matrix over the summed device time of all block-pair calls "
+                             "(off-diagonal pairs compute full nb x nb blocks)"},
+        "stages_ms": acc, "wall_s_including_generation": tt[1].item(), "generation_and_d2d_copy_s": tt[2].item(),
+        "gpu_launches": int(pod.launch_count()), "e2e": None,
+        "normfact_first": float(nf[0]),
+    }
+    print(json.dumps(line), flush=True)
+
+
 def run_b200(args, wl, rank, local_rank, world):
     import torch
     import torch.distributed as dist
@@ -241,6 +362,11 @@ def run_b200(args, wl, rank, local_rank, world):
         pod.comm_init(bytes(idt.cpu().numpy().tobytes()), rank, world)
 
     dim, m, r = wl["dim"], wl["m"], wl["r"]
+    if wl.get("blocked"):
+        run_blocked(args, wl, rank, local_rank, world, torch, dist if multi else None, pkg, pod, dev)
+        if multi:
+            dist.destroy_process_group()
+        return
     if wl["sharded"]:
         b, e = pkg.cell_range(wl["cells"], rank, world)
         cells = e - b
