@@ -106,6 +106,12 @@ int ithaca_b200_pod_postprocess_eigenvalues(const double* evals_all, int m, int 
 int ithaca_b200_pod_lift(ithaca_b200_t* h, int r, int norm_kind, double* const* mode_ptrs,
                          double* normfact_out);
 
+/* Lift with caller-given column factors instead of the norm normalisation: modes_i = (S q_i) * factors[i].
+ * ITHACAPOD::getWeightedModes (ITHACAPOD.C:715-845) is this with factors[i] = lambda_i^(-1/2) * lambda_i (:771-777,
+ * eigenvalues of pod_eig, spectra convention); pod_lift_patch afterwards applies the same factors to the boundary rows
+ * (:780-785). factors: r doubles, host. mode_ptrs as in pod_lift. */
+int ithaca_b200_pod_lift_scaled(ithaca_b200_t* h, int r, const double* factors, double* const* mode_ptrs);
+
 /* Boundary rows: out = (Sbc * Q_r) with column i divided by normfact_i. Replaces ITHACAPOD.C:245-264
  * (modesEigBC). Sbc: rows*m col-major (what Foam2Eigen::PtrList2EigenBC returns for one patch,
  * Foam2Eigen.C:272-411); out: rows*r col-major. Host pointers. Must follow pod_lift. */
@@ -191,7 +197,7 @@ int ithaca_b200_basis_upload(ithaca_b200_t* h, int which, const double* const* i
                              const double* const* bnd_ptrs, int n);
 
 enum { IB200_OP_M = 0, IB200_OP_B = 1, IB200_OP_K = 2, IB200_OP_P = 3, IB200_OP_C = 4, IB200_OP_C_MATERIALISED = 5,
-       IB200_OP_D = 6, IB200_OP_G = 7, IB200_OP_BC3 = 8, IB200_OP_BC4 = 9 };
+       IB200_OP_D = 6, IB200_OP_G = 7, IB200_OP_BC3 = 8, IB200_OP_BC4 = 9, IB200_OP_BC1 = 10 };
 /* One projected operator, laid out as the reference's Eigen object (column-major):
  *   IB200_OP_M  mass_term              steadyNS.C:1085-1108   N x N        M(i,j) = int U_i . U_j
  *   IB200_OP_B  diffusive_term         steadyNS.C:883-907     N x N        B(i,j) = int U_i . laplacian(1, U_j)
@@ -209,9 +215,19 @@ enum { IB200_OP_M = 0, IB200_OP_B = 1, IB200_OP_K = 2, IB200_OP_P = 3, IB200_OP_
  *   IB200_OP_BC3  pressure_BC3         steadyNS.C:1439-1475   Np x N       sum over boundary faces of
  *                 (interpolate(curl U_j) & (n ^ interpolate(grad P_i))) |Sf|
  *   IB200_OP_BC4  pressure_BC4         steadyNS.C:1477-1513   Np x N       sum over boundary faces of P_i (n & U_j) |Sf|
- * BC3 and BC4 are returned for ALL N velocity fields; the reference keeps the leading lift + NUmodes columns
+ *   IB200_OP_BC1  pressure_BC1         steadyNS.C:1319-1354   Np x N       sum over boundary faces of
+ *                 (interpolate(laplacian(U_j)) & Sf) P_i: the boundary value of an fvc::laplacian result is the owner cell's
+ *                 value (extrapolatedCalculated patch of fvc::surfaceIntegrate)
+ * BC1, BC3 and BC4 are returned for ALL N velocity fields; the reference keeps the leading lift + NUmodes columns
  * (P_BC2size = NUmodes + liftfield.size()): take leftCols. Faces of masked (`empty`) patches do not contribute. */
 int ithaca_b200_project(ithaca_b200_t* h, int op, double* out);
+
+/* Background ("large scale") convection with an external advecting field vls (host or device: 3*nCells internal values
+ * and 3*nBnd boundary values, the caller's order):
+ *   kind 0  convective_background            steadyNS.C:1256-1273   N x N    L(i,j)   = - int U_i . div(interpolate(vls) & Sf, U_j)
+ *   kind 1  divergent_convective_background  steadyNS.C:1275-1293   Np x N   L_D(i,j) = - int grad(P_i) . div(interpolate(vls) & Sf, U_j)
+ * for ALL N velocity fields (the reference keeps the leading NUmodes + liftfield.size() rows / columns). */
+int ithaca_b200_project_background(ithaca_b200_t* h, int kind, const double* vls_int, const double* vls_bnd, double* out);
 
 enum { IB200_FVC_FLUX = 0, IB200_FVC_DIV_PHI = 1, IB200_FVC_LAPLACIAN = 2, IB200_FVC_GRAD_P = 3, IB200_FVC_DIV_U = 4 };
 /* One materialised fvc operator field (used by the parity tests of the gather kernels):

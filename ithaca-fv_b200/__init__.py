@@ -24,11 +24,11 @@ SYMBOLS = [
     "ithaca_b200_pod_postprocess_eigenvalues", "ithaca_b200_pod_lift", "ithaca_b200_pod_lift_patch",
     "ithaca_b200_dmma_peak",
     "ithaca_b200_pod_set_modes", "ithaca_b200_pod_project", "ithaca_b200_pod_modes_mass", "ithaca_b200_pod_get_coeffs",
-    "ithaca_b200_pod_reconstruct",
+    "ithaca_b200_pod_reconstruct", "ithaca_b200_pod_lift_scaled",
     "ithaca_b200_pod_block_begin", "ithaca_b200_pod_block_upload", "ithaca_b200_pod_block_gram",
     "ithaca_b200_pod_block_gram_finish", "ithaca_b200_pod_block_lift", "ithaca_b200_pod_block_lift_finish",
     "ithaca_b200_mesh_upload", "ithaca_b200_mesh_addressing", "ithaca_b200_basis_upload", "ithaca_b200_project",
-    "ithaca_b200_fvc_eval", "ithaca_b200_proj_timings",
+    "ithaca_b200_fvc_eval", "ithaca_b200_proj_timings", "ithaca_b200_project_background",
     "ithaca_b200_partition_create", "ithaca_b200_partition_destroy", "ithaca_b200_partition_sizes",
     "ithaca_b200_partition_addressing", "ithaca_b200_partition_gather", "ithaca_b200_mesh_upload_shard",
     "ithaca_b200_mesh_set_owned", "ithaca_b200_mesh_renumbering",
@@ -73,6 +73,7 @@ def lib():
         L.ithaca_b200_pod_lift_patch.argtypes = [P, P, L64, P]
         L.ithaca_b200_dmma_peak.argtypes = [I, ctypes.POINTER(D)]
         L.ithaca_b200_pod_set_modes.argtypes = [P, P, I]
+        L.ithaca_b200_pod_lift_scaled.argtypes = [P, I, P, P]
         L.ithaca_b200_pod_block_begin.argtypes = [P, I, I, L64]
         L.ithaca_b200_pod_block_upload.argtypes = [P, I, P, I, I]
         L.ithaca_b200_pod_block_gram.argtypes = [P, I, I, I]
@@ -89,6 +90,7 @@ def lib():
         L.ithaca_b200_project.argtypes = [P, I, P]
         L.ithaca_b200_fvc_eval.argtypes = [P, I, I, I, P]
         L.ithaca_b200_proj_timings.argtypes = [P, P, I]
+        L.ithaca_b200_project_background.argtypes = [P, I, P, P, P]
         L.ithaca_b200_partition_create.argtypes = [ctypes.POINTER(P), L64, L64, L64, P, P, I, I, I, I]
         L.ithaca_b200_mesh_renumbering.argtypes = [L64, L64, P, P, P]
         L.ithaca_b200_partition_destroy.argtypes = [P]
@@ -294,6 +296,18 @@ class Pod:
         self._chk(self.L.ithaca_b200_pod_reconstruct(self.h, n, coeff.ctypes.data, k, 1 if clip_negative else 0, arr))
         return R
 
+    def lift_scaled(self, factors, want=True):
+        """modes_i = (S q_i) * factors[i] (getWeightedModes, ITHACAPOD.C:771-777)."""
+        f = np.ascontiguousarray(factors, dtype=np.float64)
+        r = f.shape[0]
+        Phi = arr = None
+        if want:
+            Phi = np.zeros((self.nCells * self.dim, r), order="F")
+            arr = (ctypes.c_void_p * r)(*[Phi.ctypes.data + i * Phi.strides[1] for i in range(r)])
+        self._chk(self.L.ithaca_b200_pod_lift_scaled(self.h, r, f.ctypes.data, arr))
+        self.r = r
+        return Phi
+
     def lift_patch(self, Sbc, r):
         Sbc = np.asfortranarray(Sbc, dtype=np.float64)
         out = np.zeros((Sbc.shape[0], r), order="F")
@@ -361,7 +375,7 @@ class Partition:
             pass
 
 
-OPS = {"M": 0, "B": 1, "K": 2, "P": 3, "C": 4, "Cmat": 5, "D": 6, "G": 7, "BC3": 8, "BC4": 9}
+OPS = {"M": 0, "B": 1, "K": 2, "P": 3, "C": 4, "Cmat": 5, "D": 6, "G": 7, "BC3": 8, "BC4": 9, "BC1": 10}
 FVC = {"flux": 0, "div_phi": 1, "laplacian": 2, "grad_p": 3, "div_u": 4}
 
 
@@ -422,9 +436,17 @@ class Projector:
     def project(self, op):
         N, Np = self.N, self.Np
         shape = {"M": (N, N), "B": (N, N), "K": (N, Np), "P": (Np, N), "C": (N, N, N), "Cmat": (N, N, N), "D": (Np, Np),
-                 "G": (Np, N, N), "BC3": (Np, N), "BC4": (Np, N)}[op]
+                 "G": (Np, N, N), "BC3": (Np, N), "BC4": (Np, N), "BC1": (Np, N)}[op]
         out = np.zeros(shape, order="F")
         self.pod._chk(self.L.ithaca_b200_project(self.h, OPS[op], out.ctypes.data))
+        return out
+
+    def project_background(self, vls, vlsb, divergent=False):
+        """convective_background (L, N x N) or divergent_convective_background (L_D, Np x N), steadyNS.C:1256-1293."""
+        vls = np.ascontiguousarray(vls, dtype=np.float64) if isinstance(vls, np.ndarray) else vls
+        vlsb = np.ascontiguousarray(vlsb, dtype=np.float64) if isinstance(vlsb, np.ndarray) else vlsb
+        out = np.zeros((self.Np if divergent else self.N, self.N), order="F")
+        self.pod._chk(self.L.ithaca_b200_project_background(self.h, 1 if divergent else 0, _ptr(vls), _ptr(vlsb), out.ctypes.data))
         return out
 
     def fvc(self, op, j, k=0):
@@ -438,6 +460,27 @@ class Projector:
         out = np.zeros(7)
         self.pod._chk(self.L.ithaca_b200_proj_timings(self.h, out.ctypes.data, 7))
         return dict(zip(self.TIMER_NAMES, out.tolist()))
+
+
+def getWeightedModes(pod, snapshots, V, dim, nmodes=0, solver="spectra", Sbc=None):
+    """ITHACAPOD::getWeightedModes (ITHACAPOD.C:715-845): same Gram and eigensolve, modes_i = (S q_i) lambda_i^(-1/2) lambda_i.
+    nmodes rule of this variant: at most m - 2 whatever the solver (:723-729)."""
+    m = snapshots.shape[1] if isinstance(snapshots, np.ndarray) else len(snapshots)
+    if nmodes == 0:
+        nmodes = m - 2
+    if nmodes > m - 2:
+        raise IthacaB200Error("The number of requested modes cannot be bigger than the number of Snapshots - 2")
+    pod.set_volumes(V)
+    pod.upload(snapshots, dim)
+    G = pod.gram()
+    ev_all, Q = pod.eig(nmodes)
+    ev = ev_all[:nmodes] if solver == "spectra" else ev_all
+    lam = 1.0 / np.sqrt(ev[:nmodes])
+    factors = lam * ev[:nmodes]
+    Phi = pod.lift_scaled(factors)
+    Pbc = pod.lift_patch(Sbc, nmodes) if Sbc is not None else None
+    evn = ev / ev.sum()
+    return dict(G=G, evals=ev, evals_norm=evn, cum=np.cumsum(evn), evecs=Q, factors=factors, modes=Phi, modes_bc=Pbc)
 
 
 def getModesMemoryEfficient(pod, block_source, m, V, dim, nmodes=0, solver="spectra", norm="L2", block=64, want_modes=True):

@@ -431,6 +431,29 @@ int ithaca_b200_pod_lift(ithaca_b200_t* h, int r, int norm_kind, double* const* 
     return IB200_OK;
 }
 
+int ithaca_b200_pod_lift_scaled(ithaca_b200_t* h, int r, const double* factors, double* const* mode_ptrs)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->have_eig || h->Nd <= 0 || h->block_mode) { set_error(h, "pod_lift_scaled: call pod_upload, pod_gram and pod_eig first"); return IB200_ERR_ARG; }
+    if (r <= 0 || r > h->m || r > 104 || !factors) { set_error(h, "pod_lift_scaled: bad argument"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    double* dF = nullptr;
+    IB_CUDA(h, cudaMalloc(&dF, 104 * sizeof(double)));
+    cudaError_t e = cudaMemcpyAsync(dF, factors, (size_t)r * sizeof(double), cudaMemcpyDefault, h->stream);
+    int rc = e == cudaSuccess ? lift_scaled_launch(h, r, dF) : IB200_ERR_CUDA;
+    if (!rc && mode_ptrs)
+        for (int i = 0; i < r && e == cudaSuccess; i++)
+            e = mode_ptrs[i] ? cudaMemcpyAsync(mode_ptrs[i], h->dPhi + (size_t)i * h->ld, (size_t)h->Nd * sizeof(double), cudaMemcpyDefault, h->stream)
+                             : cudaErrorInvalidValue;
+    if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);
+    cudaFree(dF);
+    if (rc) return rc;
+    IB_CUDA(h, e);
+    h->have_lift = true;
+    h->have_modes = true;
+    return IB200_OK;
+}
+
 int ithaca_b200_pod_lift_patch(ithaca_b200_t* h, const double* Sbc, int64_t rows, double* out)
 {
     if (!h || !Sbc || !out || rows <= 0) return IB200_ERR_ARG;

@@ -145,6 +145,7 @@ int eig_launch(ithaca_b200* h, int* sweeps);
 // lift.cu
 int lift_launch(ithaca_b200* h, int r, int norm_kind);
 int lift_patch_launch(ithaca_b200* h, const double* dSbc, int64_t rows, double* dOut);
+int lift_scaled_launch(ithaca_b200* h, int r, const double* dF);   // modes_i = (S q_i) * dF[i]
 // snapshot-blocked lift: Phi (+)= S Q[first : first+nb, 0:r] (dTmp: r columns of ld doubles when accumulating); finish = norms + scale
 int lift_block_launch(ithaca_b200* h, const double* S, int nb, int first, int r, bool accumulate, double* dTmp);
 int lift_block_finish(ithaca_b200* h, int r, int norm_kind);

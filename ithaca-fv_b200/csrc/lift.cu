@@ -329,6 +329,44 @@ int lift_launch(ithaca_b200* h, int r, int norm_kind)
     return lift_finalize(h, r);
 }
 
+// Phi(:,c) *= f[c]; nrm[c] = 1 / f[c] (so that lift_patch's division applies the same factor)
+__global__ void lift_mul_kernel(double* __restrict__ Phi, long long Nd, long long ld, int r, const double* __restrict__ f)
+{
+    const int c = blockIdx.y;
+    const double v = f[c];
+    double* col = Phi + (size_t)c * ld;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < Nd; i += (long long)gridDim.x * blockDim.x)
+        col[i] = col[i] * v;
+}
+__global__ void lift_inv_kernel(const double* __restrict__ f, int r, double* __restrict__ nrm)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < r) nrm[i] = 1.0 / f[i];
+}
+
+// modes_i = (S q_i) * factors[i] (getWeightedModes, ITHACAPOD.C:771-777). dF: r factors on the device.
+int lift_scaled_launch(ithaca_b200* h, int r, const double* dF)
+{
+    int NB = 0;
+    int rc = lift_ensure(h, h->m, r, &NB);
+    if (rc) return rc;
+    h->r = r; h->rpad = NB * 8;
+    cudaEventRecord(h->timers[T_LIFT].a, h->stream);
+    int grid = 0;
+    if ((rc = lift_core(h, h->dS, h->m, h->dQ, h->m, r, NB, 1, h->dPhi, &grid))) return rc;
+    cudaEventRecord(h->timers[T_LIFT].b, h->stream);
+    h->timers[T_LIFT].used = true;
+    cudaEventRecord(h->timers[T_SCALE].a, h->stream);
+    dim3 sg((unsigned)std::min<long long>((h->Nd + 1023) / 1024, 4LL * h->num_sms), (unsigned)r);
+    lift_mul_kernel<<<sg, 256, 0, h->stream>>>(h->dPhi, h->Nd, h->ld, r, dF);
+    lift_inv_kernel<<<1, 128, 0, h->stream>>>(dF, r, h->dNorm);
+    cudaEventRecord(h->timers[T_SCALE].b, h->stream);
+    h->timers[T_SCALE].used = true;
+    IB_CUDA(h, cudaGetLastError());
+    h->launches += 2;
+    return IB200_OK;
+}
+
 // ---- snapshot-blocked lift (memory-efficient POD, ITHACAPOD.C:344-628): Phi (+)= S_block Q[first : first+nb, 0:r] ----
 __global__ void axpy_cols_kernel(double* __restrict__ y, const double* __restrict__ x, long long Nd, long long ld, int r)
 {

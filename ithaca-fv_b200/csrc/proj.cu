@@ -597,6 +597,24 @@ bnd_normal_flux_kernel(MeshDev m, const unsigned char* __restrict__ cmask, const
     out[(size_t)j * ldo + b] = v;
 }
 
+// Lb[j][b] = laplacian(U_j)[owner(b)] . Sf_b   (BC1 = Pb^T Lb; lap: N columns of ldl doubles)
+__global__ void __launch_bounds__(PROJ_T)
+bnd_owner_dot_sf_kernel(MeshDev m, const unsigned char* __restrict__ cmask, const double* __restrict__ lap, long long ldl, int N,
+                        double* __restrict__ out, long long ldo)
+{
+    const long long b = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    if (b >= m.nBnd) return;
+    const int j = blockIdx.y;
+    const long long f = m.nInt + b;
+    const int c = m.owner[f];
+    double v = 0.0;
+    if (bnd_face_active(m, cmask, b, c)) {
+        const double* l = lap + (size_t)j * ldl + 3 * (size_t)c;
+        v = l[0] * m.Sf[3 * f] + l[1] * m.Sf[3 * f + 1] + l[2] * m.Sf[3 * f + 2];
+    }
+    out[(size_t)j * ldo + b] = v;
+}
+
 // Cb[j][3b+d] = curl(U_j) on boundary face b = 2 *skew(grad_b): (g_yz - g_zy, g_zx - g_xz, g_xy - g_yx), g_id = d_i U_d
 __global__ void __launch_bounds__(PROJ_T)
 bnd_curl_kernel(MeshDev m, const unsigned char* __restrict__ cmask, const double* __restrict__ U, long long ldU,
@@ -896,6 +914,12 @@ __global__ void owned_mask_kernel(const int* __restrict__ perm, long long nCells
         cmask[n] = own ? 1 : 0;
         Vw[n] = own ? V[n] : 0.0;
     }
+}
+
+__global__ void negate_kernel(double* __restrict__ x, long long n)
+{
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i < n) x[i] = -x[i];
 }
 
 static inline long long pad16(long long n) { return (n + 15) / 16 * 16; }
@@ -1310,7 +1334,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
     PROJ_REQUIRE(s && s->have_mesh && s->nU > 0, "project: call mesh_upload and basis_upload(U) first");
     PROJ_REQUIRE(out, "project: null output");
     PROJ_REQUIRE((op != IB200_OP_K && op != IB200_OP_P && op != IB200_OP_D && op != IB200_OP_G && op != IB200_OP_BC3 &&
-                  op != IB200_OP_BC4) || s->nP > 0, "project: K, P, D, G, BC3 and BC4 need basis_upload(P)");
+                  op != IB200_OP_BC4 && op != IB200_OP_BC1) || s->nP > 0, "project: K, P, D, G, BC1, BC3 and BC4 need basis_upload(P)");
     cudaSetDevice(h->device);
     const MeshDev m = mesh_dev(s);
     const int N = s->nU, Np = s->nP, BIG = 0x7fffffff;
@@ -1505,6 +1529,26 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
         }
         break;
     }
+    case IB200_OP_BC1: {  // pressure_BC1, steadyNS.C:1319-1354: Np x N, boundary-face sum of (lap(U_j)[owner] . Sf) P_i
+        nout = (size_t)Np * N;
+        if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
+        IB_CUDA(h, cudaMemsetAsync(s->out.p, 0, nout * sizeof(double), h->stream));
+        if (s->nBnd > 0) {
+            const long long ldB = pad16(s->nBnd);
+            if ((rc = ensure(h, s->work, (size_t)N * s->ldU * sizeof(double))) || (rc = ensure(h, s->bndA, (size_t)N * ldB * sizeof(double))))
+                return rc;
+            if ((rc = run_laplacians(h, s, s->work.as<double>()))) return rc;
+            bnd_owner_dot_sf_kernel<<<dim3(gx(s->nBnd), N), PROJ_T, 0, h->stream>>>(m, shard ? s->cmask.as<unsigned char>() : nullptr,
+                                                                                     s->work.as<double>(), s->ldU, N, s->bndA.as<double>(), ldB);
+            h->launches += 1;
+            StageTimer t(h->stream, &s->ms[5]);
+            rc = atvb_launch(h, s->Pb.as<double>(), s->ldPb, Np, s->bndA.as<double>(), ldB, N, s->nBnd, nullptr, 1, 0, s->out.as<double>(), 1,
+                             BIG, 0, Np);
+            t.stop();
+            if (rc) return rc;
+        }
+        break;
+    }
     case IB200_OP_BC3: {  // pressure_BC3, steadyNS.C:1439-1475: Np x N, boundary-face sum of curl(U_j) . (n x grad P_i) |Sf|
         nout = (size_t)Np * N;
         if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
@@ -1542,6 +1586,72 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
         t.stop();
         if (rc) return rc;
     }
+    IB_CUDA(h, cudaMemcpyAsync(out, s->out.p, nout * sizeof(double), cudaMemcpyDefault, h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return IB200_OK;
+}
+
+int ithaca_b200_project_background(ithaca_b200_t* h, int kind, const double* vls_int, const double* vls_bnd, double* out)
+{
+    if (!h) return IB200_ERR_ARG;
+    ProjState* s = h->proj;
+    PROJ_REQUIRE(s && s->have_mesh && s->nU > 0, "project_background: call mesh_upload and basis_upload(U) first");
+    PROJ_REQUIRE((kind == 0 || kind == 1) && vls_int && (vls_bnd || s->nBnd == 0) && out, "project_background: bad argument");
+    PROJ_REQUIRE(kind == 0 || s->nP > 0, "project_background: L_D needs basis_upload(P)");
+    cudaSetDevice(h->device);
+    const MeshDev m = mesh_dev(s);
+    const int N = s->nU, Np = s->nP, BIG = 0x7fffffff;
+    const long long K3 = 3 * s->nCells;
+    const bool shard = s->nOwned < s->nCells;
+    const double* V = shard ? s->Vw.as<double>() : s->V.as<double>();
+    const int rows = kind == 0 ? N : Np;
+    const size_t nout = (size_t)rows * N;
+    for (double& x : s->ms) x = 0.0;
+    int rc;
+    // buffers: vls (internal order) + its boundary values + its face flux in bndB; div fields in work
+    const long long ldv = s->ldU, ldvb = s->ldUb, ldF = s->ldF;
+    if ((rc = ensure(h, s->bndB, (size_t)(ldv + ldvb + ldF) * sizeof(double))) || (rc = ensure(h, s->work, (size_t)N * s->ldU * sizeof(double))) ||
+        (rc = ensure(h, s->out, nout * sizeof(double))))
+        return rc;
+    double* vl = s->bndB.as<double>();
+    double* vb = vl + ldv;
+    double* phi = vb + ldvb;
+    IB_CUDA(h, cudaMemcpyAsync(s->stage.p, vls_int, (size_t)3 * s->nCells * sizeof(double), cudaMemcpyDefault, h->stream));
+    permute_cells_kernel<<<(unsigned)std::min<long long>((3 * s->nCells + 255) / 256, 64LL * h->num_sms), 256, 0, h->stream>>>(
+        s->stage.as<double>(), s->perm.as<int>(), s->nCells, 3, vl);
+    if (s->nBnd) IB_CUDA(h, cudaMemcpyAsync(vb, vls_bnd, (size_t)3 * s->nBnd * sizeof(double), cudaMemcpyDefault, h->stream));
+    {
+        StageTimer t(h->stream, &s->ms[0]);
+        face_flux_kernel<<<dim3(gx(s->nInt + s->nBnd), gy(1)), PROJ_T, 0, h->stream>>>(m, vl, ldv, vb, ldvb, 1, phi, ldF);
+        t.stop();
+    }
+    {
+        StageTimer t(h->stream, &s->ms[1]);
+        div_phi_kernel<<<dim3(gx(s->nCells), gy(N)), PROJ_T, 0, h->stream>>>(m, phi, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb, N,
+                                                                             s->work.as<double>(), s->ldU);
+        t.stop();
+    }
+    h->launches += 3;
+    const double* A = s->U.as<double>();
+    if (kind == 1) {
+        if ((rc = ensure(h, s->gradP, (size_t)Np * s->ldU * sizeof(double)))) return rc;
+        StageTimer t(h->stream, &s->ms[3]);
+        grad_scalar_kernel<<<dim3(gx(s->nCells), gy(Np)), PROJ_T, 0, h->stream>>>(m, s->P.as<double>(), s->ldP, s->Pb.as<double>(), s->ldPb, Np,
+                                                                                   s->gradP.as<double>(), s->ldU);
+        t.stop();
+        h->launches += 1;
+        A = s->gradP.as<double>();
+    }
+    {
+        StageTimer t(h->stream, &s->ms[5]);
+        rc = atvb_launch(h, A, s->ldU, rows, s->work.as<double>(), s->ldU, N, K3, V, 3, 0, s->out.as<double>(), 1, BIG, 0, rows);
+        t.stop();
+    }
+    if (rc) return rc;
+    negate_kernel<<<(unsigned)((nout + 255) / 256), 256, 0, h->stream>>>(s->out.as<double>(), (long long)nout);
+    h->launches += 1;
+    IB_CUDA(h, cudaGetLastError());
+    if (h->nccl_comm && h->nranks > 1 && (rc = allreduce_sum(h, s->out.as<double>(), nout))) return rc;
     IB_CUDA(h, cudaMemcpyAsync(out, s->out.p, nout * sizeof(double), cudaMemcpyDefault, h->stream));
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
     return IB200_OK;

@@ -165,6 +165,32 @@ class Oracle:
         self.L.fvo_pressure_bc3(self._ref(), len(fs), len(fp), pu, pub, pp, ppb, P(out.ctypes.data))
         return out
 
+    def pressure_bc1(self, U, Ub, Pb):
+        fs, pu = self._ptrs(U)
+        fb, pub = self._ptrs(Ub)
+        fpb, ppb = self._ptrs(Pb)
+        out = np.zeros((len(fpb), len(fs)), order="F")
+        self.L.fvo_pressure_bc1(self._ref(), len(fs), len(fpb), pu, pub, ppb, P(out.ctypes.data))
+        return out
+
+    def convective_background(self, U, Ub, vls, vlsb, Pm=None, Pb=None):
+        """Pm None: L (N x N, steadyNS.C:1256-1273); else L_D (Np x N, :1275-1293)."""
+        fs, pu = self._ptrs(U)
+        fb, pub = self._ptrs(Ub)
+        vls, vlsb = _c(vls), _c(vlsb)
+        kind = 0 if Pm is None else 1
+        if kind:
+            fp, pp = self._ptrs(Pm)
+            fpb, ppb = self._ptrs(Pb)
+            rows, npm = len(fp), len(fp)
+        else:
+            pp = ppb = None
+            rows, npm = len(fs), 0
+        out = np.zeros((rows, len(fs)), order="F")
+        self.L.fvo_convective_background(self._ref(), kind, len(fs), npm, pu, pub, pp, ppb, P(vls.ctypes.data), P(vlsb.ctypes.data),
+                                         P(out.ctypes.data))
+        return out
+
     def cell_faces(self):
         nnz = 2 * self.mesh.nInt + self.mesh.nBnd
         off = np.zeros(self.mesh.nCells + 1, dtype=np.int32)

@@ -414,6 +414,49 @@ void fvo_pressure_bc3(const fvo_mesh* m, int N, int Np, const double* const* U, 
     free(T); free(gp); free(curl); free(ngp);
 }
 
+/* steadyNS::pressure_BC1, steadyNS.C:1319-1354: BC1(i,j) = sum over boundary faces of
+ * (interpolate(laplacian(U_j)) & Sf) * interpolate(P_i). The boundary value of the fvc::laplacian result is the owner
+ * cell's value (fvc::surfaceIntegrate builds its result with extrapolatedCalculated patches). BC1: Np x N. */
+void fvo_pressure_bc1(const fvo_mesh* m, int N, int Np, const double* const* U, const double* const* Ub, const double* const* Pb,
+                      double* BC1)
+{
+    double* L = (double*)malloc(sizeof(double) * 3 * m->nCells);
+    for (int j = 0; j < N; j++) {
+        fvo_laplacian_vec(m, U[j], Ub[j], L);
+        for (int i = 0; i < Np; i++) {
+            double s = 0.0;
+            for (long long b = 0; b < m->nBnd; b++) {
+                if (!m->bmask[b]) continue;
+                const long long f = m->nInt + b, c = m->owner[f];
+                s += (L[3 * c] * m->Sf[3 * f] + L[3 * c + 1] * m->Sf[3 * f + 1] + L[3 * c + 2] * m->Sf[3 * f + 2]) * Pb[i][b];
+            }
+            BC1[i + (size_t)j * Np] = s;
+        }
+    }
+    free(L);
+}
+
+/* steadyNS::convective_background (kind 0, steadyNS.C:1256-1273): L(i,j) = -domainIntegrate(U_i & div(interpolate(vls) & Sf, U_j)),
+ * N x N; steadyNS::divergent_convective_background (kind 1, :1275-1293): L_D(i,j) = -domainIntegrate(grad(P_i) & div(...)), Np x N. */
+void fvo_convective_background(const fvo_mesh* m, int kind, int N, int Np, const double* const* U, const double* const* Ub,
+                               const double* const* P, const double* const* Pb, const double* vls, const double* vlsb, double* out)
+{
+    const int rows = kind == 0 ? N : Np;
+    double* phi = (double*)malloc(sizeof(double) * (m->nInt + m->nBnd));
+    double* D = (double*)malloc(sizeof(double) * 3 * m->nCells);
+    double* g = (double*)malloc(sizeof(double) * 3 * m->nCells);
+    fvo_flux(m, vls, vlsb, phi);
+    for (int j = 0; j < N; j++) {
+        fvo_div_phi_vec(m, phi, U[j], Ub[j], D);
+        for (int i = 0; i < rows; i++) {
+            const double* a = U ? U[i] : 0;
+            if (kind == 1) { fvo_grad_scalar(m, P[i], Pb[i], g); a = g; }
+            out[i + (size_t)j * rows] = -fvo_domain_integrate_dot(m, a, D, 3);
+        }
+    }
+    free(phi); free(D); free(g);
+}
+
 /* ---- addressing: cell -> face CSR in ascending face order (= primitiveMesh::cells() order) -------------
  * entry = +(f+1) when the cell owns face f (Sf points outwards), -(f+1) when it is the neighbour.
  * off: nCells+1, ent/other: 2*nInt+nBnd. other = the cell across the face, or -(b+1) for boundary face b. */

@@ -178,3 +178,21 @@ def test_ppe_operators_known_answers(box, cyl):
     BC3 = o2.pressure_bc3(U2, Ub2, P2, Pb2)
     BC3s = o2.pressure_bc3([U2[1] * 2.0], [Ub2[1] * 2.0], [P2[0] - 3.0 * P2[1]], [Pb2[0] - 3.0 * Pb2[1]])
     assert abs(BC3s[0, 0] - 2.0 * (BC3[0, 1] - 3.0 * BC3[1, 1])) <= 1e-12 * np.abs(BC3).max()  # bilinear
+
+
+def test_background_convection_and_bc1_definitions(cyl):
+    """convective_background / divergent_convective_background are slices of -C / -G with vls as the advecting field
+    (steadyNS.C:1256-1293 against :1038-1083 and :1207-1254); BC1 with P = 1 is the boundary sum of lap(U)[owner] . Sf."""
+    m = cyl
+    o = fvc.Oracle(m)
+    U, Ub, P, Pb = fvc.synthetic_basis(m, 3, 2, seed=8)
+    C = o.convective_term_tens(U, Ub)
+    assert np.array_equal(o.convective_background(U, Ub, U[1], Ub[1]), -C[:, 1, :])
+    G = o.div_momentum(U, Ub, P, Pb)
+    assert np.array_equal(o.convective_background(U, Ub, U[2], Ub[2], P, Pb), -G[:, 2, :])
+    BC1 = o.pressure_bc1(U, Ub, [np.ones(m.nBnd)] + Pb)
+    lap = o.laplacian(U[0], Ub[0]).reshape(-1, 3)
+    act = m.bmask.astype(bool)
+    own = m.owner[m.nInt:]
+    want = np.sum((lap[own] * m.Sf[m.nInt:]).sum(axis=1)[act])
+    assert abs(BC1[0, 0] - want) <= 1e-12 * np.abs(BC1).max()

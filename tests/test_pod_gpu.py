@@ -254,3 +254,21 @@ def test_memory_efficient_blocked_pod_matches_oracle(pkg, pod, Nc, dim, m, r, bl
     pod.upload(S, dim)
     pod.set_modes(np.asfortranarray(out["modes"]))
     assert rel_max(pod.project(0, "G"), po.project(S, V, dim, out["modes"], 0, "G")) <= 1e-12
+
+
+@pytest.mark.parametrize("solver", ["spectra", "eigen"])
+def test_weighted_modes_match_oracle(pkg, pod, solver):
+    """getWeightedModes (ITHACAPOD.C:715-845): modes_i = (S q_i) lambda_i^(-1/2) lambda_i, boundary rows alike."""
+    Nc, dim, m, r = 3001, 3, 30, 6
+    S = synth.snapshots(Nc, dim, m, 2 * r, 55)
+    V = synth.volumes(Nc, 55)
+    Sbc = np.asfortranarray(np.random.default_rng(3).standard_normal((21, m)))
+    out = pkg.getWeightedModes(pod, S, V, dim, r, solver, Sbc)
+    ref = po.getweightedmodes(S, V, dim, r, solver, Sbc)
+    assert len(out["evals_norm"]) == len(ref["evals_norm"])
+    assert np.all(np.abs(out["evals_norm"][:r] - ref["evals_norm"][:r]) <= 1e-10 * ref["evals_norm"][:r])
+    assert modes_rel(out["modes"], ref["modes"]) <= 1e-8
+    s = np.sign(np.einsum("ij,ij->j", out["modes"], ref["modes"]))
+    assert rel_max(out["modes_bc"] * s, ref["modes_bc"]) <= 1e-8
+    with pytest.raises(pkg.IthacaB200Error):
+        pkg.getWeightedModes(pod, S, V, dim, m - 1, solver)

@@ -81,6 +81,10 @@ def test_ppe_operators_match_oracle(case, monkeypatch):
     assert rel(D, orc.laplacian_pressure(P, Pb)) <= TOL and np.array_equal(D, D.T)
     assert rel(pr.project("BC4"), orc.pressure_bc4(Ub, Pb)) <= TOL
     assert rel(pr.project("BC3"), orc.pressure_bc3(U, Ub, P, Pb)) <= TOL
+    assert rel(pr.project("BC1"), orc.pressure_bc1(U, Ub, Pb)) <= TOL
+    vls, vlsb = U[1] + 0.5 * U[2], Ub[1] + 0.5 * Ub[2]
+    assert rel(pr.project_background(vls, vlsb), orc.convective_background(U, Ub, vls, vlsb)) <= TOL
+    assert rel(pr.project_background(vls, vlsb, divergent=True), orc.convective_background(U, Ub, vls, vlsb, P, Pb)) <= TOL
     G = pr.project("G")
     Gr = orc.div_momentum(U, Ub, P, Pb)
     assert G.shape == Gr.shape and rel(G, Gr) <= TOL          # fused face-based contraction
@@ -170,7 +174,7 @@ def test_sharded_projection_sums_to_the_global_operators(pkg, pod, nranks, name,
     ref = {"M": orc.mass_term(U), "B": orc.diffusive_term(U, Ub), "K": orc.pressure_gradient_term(U, P, Pb),
            "P": orc.divergence_term(U, Ub, P), "C": orc.convective_term_tens(U, Ub, cache=True),
            "D": orc.laplacian_pressure(P, Pb), "G": orc.div_momentum(U, Ub, P, Pb), "BC3": orc.pressure_bc3(U, Ub, P, Pb),
-           "BC4": orc.pressure_bc4(Ub, Pb)}
+           "BC4": orc.pressure_bc4(Ub, Pb), "BC1": orc.pressure_bc1(U, Ub, Pb)}
     ref["Cmat"] = ref["C"]
     acc = {k: np.zeros_like(v) for k, v in ref.items()}
     pr = pkg.Projector(pod)
