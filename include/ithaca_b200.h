@@ -229,6 +229,15 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out);
  * for ALL N velocity fields (the reference keeps the leading NUmodes + liftfield.size() rows / columns). */
 int ithaca_b200_project_background(ithaca_b200_t* h, int kind, const double* vls_int, const double* vls_bnd, double* out);
 
+/* Penalty-method boundary terms of one (patch, component) pair (steadyNS::bcVelocityVec / bcVelocityMat,
+ * steadyNS.C:1515-1582; inletIndex(k,0) = patch, inletIndex(k,1) = component):
+ *   vec_out[i]    = sum over the patch faces of U_i.boundaryField()[patch].component(comp)              (N)
+ *   mat_out(i,j)  = sum over the patch faces of U_i...component(comp) * U_j...component(comp)           (N x N)
+ * for ALL N velocity fields (the reference skips the lift fields: BCsize = NUmodes + NSUPmodes; take the trailing block).
+ * The patch is the boundary-face range [patch_start, patch_start + patch_size) (patch.start() - nInternalFaces). */
+int ithaca_b200_project_bc_velocity(ithaca_b200_t* h, int64_t patch_start, int64_t patch_size, int comp, double* vec_out,
+                                    double* mat_out);
+
 enum { IB200_FVC_FLUX = 0, IB200_FVC_DIV_PHI = 1, IB200_FVC_LAPLACIAN = 2, IB200_FVC_GRAD_P = 3, IB200_FVC_DIV_U = 4 };
 /* One materialised fvc operator field (used by the parity tests of the gather kernels):
  *   FLUX      linearInterpolate(U_j) & Sf                 nInt+nBnd doubles

@@ -28,7 +28,7 @@ SYMBOLS = [
     "ithaca_b200_pod_block_begin", "ithaca_b200_pod_block_upload", "ithaca_b200_pod_block_gram",
     "ithaca_b200_pod_block_gram_finish", "ithaca_b200_pod_block_lift", "ithaca_b200_pod_block_lift_finish",
     "ithaca_b200_mesh_upload", "ithaca_b200_mesh_addressing", "ithaca_b200_basis_upload", "ithaca_b200_project",
-    "ithaca_b200_fvc_eval", "ithaca_b200_proj_timings", "ithaca_b200_project_background",
+    "ithaca_b200_fvc_eval", "ithaca_b200_proj_timings", "ithaca_b200_project_background", "ithaca_b200_project_bc_velocity",
     "ithaca_b200_partition_create", "ithaca_b200_partition_destroy", "ithaca_b200_partition_sizes",
     "ithaca_b200_partition_addressing", "ithaca_b200_partition_gather", "ithaca_b200_mesh_upload_shard",
     "ithaca_b200_mesh_set_owned", "ithaca_b200_mesh_renumbering",
@@ -91,6 +91,7 @@ def lib():
         L.ithaca_b200_fvc_eval.argtypes = [P, I, I, I, P]
         L.ithaca_b200_proj_timings.argtypes = [P, P, I]
         L.ithaca_b200_project_background.argtypes = [P, I, P, P, P]
+        L.ithaca_b200_project_bc_velocity.argtypes = [P, L64, L64, I, P, P]
         L.ithaca_b200_partition_create.argtypes = [ctypes.POINTER(P), L64, L64, L64, P, P, I, I, I, I]
         L.ithaca_b200_mesh_renumbering.argtypes = [L64, L64, P, P, P]
         L.ithaca_b200_partition_destroy.argtypes = [P]
@@ -448,6 +449,13 @@ class Projector:
         out = np.zeros((self.Np if divergent else self.N, self.N), order="F")
         self.pod._chk(self.L.ithaca_b200_project_background(self.h, 1 if divergent else 0, _ptr(vls), _ptr(vlsb), out.ctypes.data))
         return out
+
+    def bc_velocity(self, patch_start, patch_size, comp):
+        """bcVelocityVec / bcVelocityMat of one (patch, component) pair (steadyNS.C:1515-1582): (vec[N], mat[N, N])."""
+        vec = np.zeros(self.N)
+        mat = np.zeros((self.N, self.N), order="F")
+        self.pod._chk(self.L.ithaca_b200_project_bc_velocity(self.h, patch_start, patch_size, comp, vec.ctypes.data, mat.ctypes.data))
+        return vec, mat
 
     def fvc(self, op, j, k=0):
         n = {"flux": self.nInt + self.nBnd, "div_phi": 3 * self.nCells, "laplacian": 3 * self.nCells,

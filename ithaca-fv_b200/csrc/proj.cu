@@ -615,6 +615,19 @@ bnd_owner_dot_sf_kernel(MeshDev m, const unsigned char* __restrict__ cmask, cons
     out[(size_t)j * ldo + b] = v;
 }
 
+// Xp[j][b] = component `comp` of U_j on patch face start+b (j < N), Xp[N][b] = 1   (bcVelocityVec / bcVelocityMat)
+__global__ void __launch_bounds__(PROJ_T)
+bnd_patch_component_kernel(MeshDev m, const unsigned char* __restrict__ cmask, const double* __restrict__ Ub, long long ldUb, int N,
+                           long long start, long long size, int comp, double* __restrict__ out, long long ldo)
+{
+    const long long b = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    if (b >= size) return;
+    const int j = blockIdx.y;
+    const long long bf = start + b;
+    const bool on = !cmask || cmask[m.owner[m.nInt + bf]] != 0;   // shard: faces of halo cells belong to another rank
+    out[(size_t)j * ldo + b] = !on ? 0.0 : (j < N ? Ub[(size_t)j * ldUb + 3 * bf + comp] : 1.0);
+}
+
 // Cb[j][3b+d] = curl(U_j) on boundary face b = 2 *skew(grad_b): (g_yz - g_zy, g_zx - g_xz, g_xy - g_yx), g_id = d_i U_d
 __global__ void __launch_bounds__(PROJ_T)
 bnd_curl_kernel(MeshDev m, const unsigned char* __restrict__ cmask, const double* __restrict__ U, long long ldU,
@@ -1588,6 +1601,40 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
     }
     IB_CUDA(h, cudaMemcpyAsync(out, s->out.p, nout * sizeof(double), cudaMemcpyDefault, h->stream));
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return IB200_OK;
+}
+
+int ithaca_b200_project_bc_velocity(ithaca_b200_t* h, int64_t patch_start, int64_t patch_size, int comp, double* vec_out, double* mat_out)
+{
+    if (!h) return IB200_ERR_ARG;
+    ProjState* s = h->proj;
+    PROJ_REQUIRE(s && s->have_mesh && s->nU > 0, "project_bc_velocity: call mesh_upload and basis_upload(U) first");
+    PROJ_REQUIRE(patch_start >= 0 && patch_size > 0 && patch_start + patch_size <= s->nBnd && comp >= 0 && comp < 3 && (vec_out || mat_out),
+                 "project_bc_velocity: bad argument");
+    cudaSetDevice(h->device);
+    const MeshDev m = mesh_dev(s);
+    const int N = s->nU, N1 = N + 1;
+    const bool shard = s->nOwned < s->nCells;
+    const long long ldp = pad16(patch_size);
+    int rc;
+    if ((rc = ensure(h, s->bndA, (size_t)N1 * ldp * sizeof(double))) || (rc = ensure(h, s->out, (size_t)N1 * N1 * sizeof(double)))) return rc;
+    bnd_patch_component_kernel<<<dim3(gx(patch_size), N1), PROJ_T, 0, h->stream>>>(m, shard ? s->cmask.as<unsigned char>() : nullptr,
+                                                                                  s->Ub.as<double>(), s->ldUb, N, patch_start, patch_size, comp,
+                                                                                  s->bndA.as<double>(), ldp);
+    h->launches += 1;
+    // Gram of [X, 1]: the N x N block is bcVelMat, the last column bcVelVec
+    rc = atvb_launch(h, s->bndA.as<double>(), ldp, N1, s->bndA.as<double>(), ldp, N1, patch_size, nullptr, 1, 1, s->out.as<double>(), 1,
+                     0x7fffffff, 0, N1);
+    if (rc) return rc;
+    if (h->nccl_comm && h->nranks > 1 && (rc = allreduce_sum(h, s->out.as<double>(), (size_t)N1 * N1))) return rc;
+    std::vector<double> hM((size_t)N1 * N1);
+    IB_CUDA(h, cudaMemcpyAsync(hM.data(), s->out.p, hM.size() * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    for (int j = 0; j < N; j++) {
+        if (vec_out) vec_out[j] = hM[(size_t)j + (size_t)N * N1];
+        if (mat_out)
+            for (int i = 0; i < N; i++) mat_out[(size_t)i + (size_t)j * N] = hM[(size_t)i + (size_t)j * N1];
+    }
     return IB200_OK;
 }
 

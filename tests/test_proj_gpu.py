@@ -85,6 +85,12 @@ def test_ppe_operators_match_oracle(case, monkeypatch):
     vls, vlsb = U[1] + 0.5 * U[2], Ub[1] + 0.5 * Ub[2]
     assert rel(pr.project_background(vls, vlsb), orc.convective_background(U, Ub, vls, vlsb)) <= TOL
     assert rel(pr.project_background(vls, vlsb, divergent=True), orc.convective_background(U, Ub, vls, vlsb, P, Pb)) <= TOL
+    # penalty terms of one (patch, component) pair: plain patch sums (steadyNS.C:1515-1582)
+    name, typ, sl = [p for p in mesh.patch_slices() if p[1] != "empty" and p[2].stop > p[2].start][0]
+    X = np.stack([u.reshape(-1, 3)[sl, 1] for u in Ub], axis=1)
+    vec, mat = pr.bc_velocity(sl.start, sl.stop - sl.start, 1)
+    assert np.abs(vec - X.sum(axis=0)).max() <= 1e-12 * np.abs(X).sum(axis=0).max()
+    assert rel(mat, X.T @ X) <= 1e-12
     G = pr.project("G")
     Gr = orc.div_momentum(U, Ub, P, Pb)
     assert G.shape == Gr.shape and rel(G, Gr) <= TOL          # fused face-based contraction
