@@ -33,7 +33,9 @@ def launches(src, dst):
         a = agg.setdefault(row["Kernel Name"][:90], [0, 0.0])
         a[0] += 1
         a[1] += v
-    ours = {k: v for k, v in agg.items() if "ib200::" in k and "dmma_peak" not in k}
+    foreign = ("at::", "cutlass", "geqr2", "larft", "lacpy", "orgqr", "batch_eye", "copy_info", "gemmcn", "elementwise_kernel", "nccl")
+    ours = {k: v for k, v in agg.items()
+            if "dmma_peak" not in k and ("ib200::" in k or not any(f in k for f in foreign))}
     tot = sum(v[1] for v in ours.values())
     with open(dst, "w") as f:
         f.write("# ncu launch list (gpu__time_duration.sum, --clock-control none; cold-cache, serialised)\n\n")
