@@ -21,11 +21,20 @@
 #include <cstring>
 #include <vector>
 
+#ifndef LAP_UNROLL_N
+#define LAP_UNROLL_N 2
+#endif
+
 namespace ib200 {
+
+constexpr int LAP_UNROLL = LAP_UNROLL_N;   // faces per trip of the K7 face loops: the loads of that many faces are in flight together
+
 
 // renumber.cu
 void mesh_renumber(long long nCells, long long nInt, const int* owner, const int* neigh, std::vector<int>& old2new,
                    std::vector<int>& fnew2old);
+void mesh_renumber_blocked(long long nCells, long long nInt, const int* owner, const int* neigh, int block, std::vector<int>& old2new,
+                           std::vector<int>& fnew2old);
 
 struct MeshDev {
     long long nCells, nInt, nBnd;
@@ -465,6 +474,7 @@ grad_vec_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const do
 #pragma unroll
     for (int i = 0; i < 3; i++) acc[i][0] = acc[i][1] = acc[i][2] = 0.0;
     const int e0 = m.off[c], e1 = m.off[c + 1];
+#pragma unroll LAP_UNROLL
     for (int e = e0; e < e1; e++) {
         const int en = m.ent[e], ot = m.other[e];
         const long long f = abs(en) - 1;
@@ -523,6 +533,7 @@ laplacian_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const d
         for (int k = 0; k < 9; k++) tc[k] = t[k * ldc + c];
     double acc[3] = {0.0, 0.0, 0.0};
     const int e0 = m.off[c], e1 = m.off[c + 1];
+#pragma unroll LAP_UNROLL
     for (int e = e0; e < e1; e++) {
         const int en = m.ent[e], ot = m.other[e];
         const long long f = abs(en) - 1;
@@ -1133,7 +1144,14 @@ int ithaca_b200_mesh_upload(ithaca_b200_t* h, int64_t nCells, int64_t nIntFaces,
             for (long long c = 0; c < nCells; c++) old2new[c] = (int)c;
             for (long long f = 0; f < nIntFaces; f++) fnew2old[f] = (int)f;
         } else {
-            mesh_renumber(nCells, nIntFaces, ho.data(), hn.data(), old2new, fnew2old);
+            // ITHACA_B200_RENUMBER_BLOCK: cells per compact cluster of the two-level ordering (renumber.cu); 0 = plain
+            // Cuthill-McKee, the default: measured at C4, clusters of 64..4096 cells make every gather stage SLOWER
+            // (laplacian 15.7 -> 17.8..25.2 ms): inside a breadth-first ball the neighbours of consecutive cells are no
+            // longer consecutive, and coalescing matters more than L1 reuse
+            int blk = 0;
+            if (const char* e = getenv("ITHACA_B200_RENUMBER_BLOCK")) blk = std::max(0, atoi(e));
+            if (blk > 1) mesh_renumber_blocked(nCells, nIntFaces, ho.data(), hn.data(), blk, old2new, fnew2old);
+            else mesh_renumber(nCells, nIntFaces, ho.data(), hn.data(), old2new, fnew2old);
         }
     }
     if ((rc = upload(h, s->perm, old2new.data(), nCells * sizeof(int))) ||

@@ -16,6 +16,30 @@
 
 namespace ib200 {
 
+// internal faces sorted by (lower new label, higher new label): counting sort on the lower label, then the (few)
+// faces of one cell by the higher label
+static void sort_faces(long long nCells, long long nInt, const int* owner, const int* neigh, const std::vector<int>& old2new,
+                       std::vector<int>& fnew2old)
+{
+    const size_t nC = (size_t)nCells, nF = (size_t)nInt;
+    std::vector<int> lo(nF), hi(nF), cnt(nC + 1, 0);
+    for (size_t f = 0; f < nF; f++) {
+        const int a = old2new[owner[f]], b = old2new[neigh[f]];
+        lo[f] = std::min(a, b);
+        hi[f] = std::max(a, b);
+        cnt[lo[f] + 1]++;
+    }
+    for (size_t c = 0; c < nC; c++) cnt[c + 1] += cnt[c];
+    fnew2old.assign(nF, 0);
+    {
+        std::vector<int> pos(cnt.begin(), cnt.end() - 1);
+        for (size_t f = 0; f < nF; f++) fnew2old[pos[lo[f]]++] = (int)f;
+    }
+    for (size_t c = 0; c < nC; c++)
+        std::sort(fnew2old.begin() + cnt[c], fnew2old.begin() + cnt[c + 1],
+                  [&](int x, int y) { return hi[x] != hi[y] ? hi[x] < hi[y] : x < y; });
+}
+
 // old2new[c] = new label of cell c; fnew2old[f'] = original index of the internal face at new position f'.
 void mesh_renumber(long long nCells, long long nInt, const int* owner, const int* neigh, std::vector<int>& old2new,
                    std::vector<int>& fnew2old)
@@ -63,24 +87,49 @@ void mesh_renumber(long long nCells, long long nInt, const int* owner, const int
     old2new.assign(nC, 0);
     for (size_t k = 0; k < nC; k++) old2new[order[k]] = (int)k;
 
-    // internal faces sorted by (lower new label, higher new label): counting sort on the lower label, then the (few)
-    // faces of one cell by the higher label
-    std::vector<int> lo(nF), hi(nF), cnt(nC + 1, 0);
+    sort_faces(nCells, nInt, owner, neigh, old2new, fnew2old);
+}
+
+// Two-level ordering for the gather kernels: the Cuthill-McKee sequence is cut into compact clusters of <= `block` cells
+// (a breadth-first ball grown from the first still unassigned cell of the sequence, over unassigned cells only), and the
+// clusters are numbered in the order their seeds appear. A thread block of the cell kernels then covers one cluster, most
+// of whose face neighbours lie INSIDE it (L1 hits), instead of a 1-D run of a breadth-first level whose neighbours in the
+// levels before and after are an L2 round trip away.
+void mesh_renumber_blocked(long long nCells, long long nInt, const int* owner, const int* neigh, int block, std::vector<int>& old2new,
+                           std::vector<int>& fnew2old)
+{
+    const size_t nC = (size_t)nCells, nF = (size_t)nInt;
+    std::vector<int> cm, ftmp;
+    mesh_renumber(nCells, nInt, owner, neigh, cm, ftmp);
+    std::vector<int> seq(nC);
+    for (size_t c = 0; c < nC; c++) seq[cm[c]] = (int)c;
+    std::vector<int> off(nC + 1, 0);
+    for (size_t f = 0; f < nF; f++) { off[owner[f] + 1]++; off[neigh[f] + 1]++; }
+    for (size_t c = 0; c < nC; c++) off[c + 1] += off[c];
+    std::vector<int> adj(2 * nF), cur(off.begin(), off.end() - 1);
     for (size_t f = 0; f < nF; f++) {
-        const int a = old2new[owner[f]], b = old2new[neigh[f]];
-        lo[f] = std::min(a, b);
-        hi[f] = std::max(a, b);
-        cnt[lo[f] + 1]++;
+        adj[cur[owner[f]]++] = neigh[f];
+        adj[cur[neigh[f]]++] = owner[f];
     }
-    for (size_t c = 0; c < nC; c++) cnt[c + 1] += cnt[c];
-    fnew2old.assign(nF, 0);
-    {
-        std::vector<int> pos(cnt.begin(), cnt.end() - 1);
-        for (size_t f = 0; f < nF; f++) fnew2old[pos[lo[f]]++] = (int)f;
+    old2new.assign(nC, -1);
+    std::vector<int> ball;
+    ball.reserve((size_t)block);
+    int next = 0;
+    for (size_t k = 0; k < nC; k++) {
+        const int seed = seq[k];
+        if (old2new[seed] >= 0) continue;
+        ball.clear();
+        ball.push_back(seed);
+        old2new[seed] = next++;
+        for (size_t head = 0; head < ball.size() && (int)ball.size() < block; head++) {
+            const int c = ball[head];
+            for (int e = off[c]; e < off[c + 1] && (int)ball.size() < block; e++) {
+                const int x = adj[e];
+                if (old2new[x] < 0) { old2new[x] = next++; ball.push_back(x); }
+            }
+        }
     }
-    for (size_t c = 0; c < nC; c++)
-        std::sort(fnew2old.begin() + cnt[c], fnew2old.begin() + cnt[c + 1],
-                  [&](int x, int y) { return hi[x] != hi[y] ? hi[x] < hi[y] : x < y; });
+    sort_faces(nCells, nInt, owner, neigh, old2new, fnew2old);
 }
 
 }  // namespace ib200

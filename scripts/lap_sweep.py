@@ -15,7 +15,7 @@ pr = pkg.Projector(pod)
 pr.set_mesh(mesh, corrected=True)
 pr.set_basis("U", U, Ub)
 ref = None
-for batch in (25, 8, 50, 0):   # 0 = cell-major pass, else field-major with that batch
+for batch in [int(x) for x in os.environ.get("LAP_SWEEP", "25,8,50,0").split(",")]:   # 0 = cell-major pass, else field-major with that batch
     os.environ["ITHACA_B200_LAP"] = "fm" if batch else "cm"
     if batch:
         os.environ["ITHACA_B200_LAP_BATCH"] = str(batch)
