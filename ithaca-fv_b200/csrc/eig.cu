@@ -244,14 +244,14 @@ __global__ void eig_jacobi_block_kernel(double* X, int m, int b, int nb, double 
     if (blockIdx.x == 0 && threadIdx.x == 0) flags[EIG_MAX_SWEEPS] = sweep;
 }
 
-// ---- register-resident variant for m <= 32*NE <= 1024 -------------------------------------------------------------
+// ---- register-resident variant for m <= 32*NE <= 2048 -------------------------------------------------------------
 // Same ordering as eig_jacobi_block_kernel, but in a block pair (I, J) warp i keeps column i of block I in REGISTERS for
 // all b inner rounds (it meets columns i, i+1, ... of block J in turn), only block J lives in shared memory (padded to
 // 32*NE doubles per column, so the hot loop has no bounds checks), and the squared norms travel with the columns and
 // are updated by the rotation (|x'|^2 = a - t c, |y'|^2 = b + t c; recomputed from scratch at every block-pair visit),
 // so a rotation costs ONE warp reduction (the dot product) instead of three.
 template <int NE>
-__global__ void __launch_bounds__(NE > 16 ? 320 : 512, 1) eig_jacobi_reg_kernel(double* X, int m, int b, int nb, double tol, int* flags)
+__global__ void __launch_bounds__(NE > 32 ? 256 : NE > 16 ? 320 : 512, 1) eig_jacobi_reg_kernel(double* X, int m, int b, int nb, double tol, int* flags)
 {
     cg::grid_group grid = cg::this_grid();
     extern __shared__ double sx[];           // b columns of LDC doubles | b squared norms
@@ -343,12 +343,14 @@ __global__ void __launch_bounds__(NE > 16 ? 320 : 512, 1) eig_jacobi_reg_kernel(
                     const int j = (warp + s) % b;
                     if (warp < ni && j < nj) {
                         double* y = sx + (size_t)j * LDC + lane;
-                        double yr[NE];
+                        constexpr bool YREG = NE <= 32;   // NE = 64 (m <= 2048): x alone fills the registers, y is re-read
+                        double yr[YREG ? NE : 1];
                         double c0 = 0.0, c1 = 0.0;
 #pragma unroll
                         for (int e = 0; e < NE; e++) {
-                            yr[e] = y[32 * e];
-                            if (e & 1) c1 += xr[e] * yr[e]; else c0 += xr[e] * yr[e];
+                            const double yv = y[32 * e];
+                            if (YREG) yr[e] = yv;
+                            if (e & 1) c1 += xr[e] * yv; else c0 += xr[e] * yv;
                         }
                         const double c = warp_sum(c0 + c1);
                         const double bn = nrm[j];
@@ -362,8 +364,9 @@ __global__ void __launch_bounds__(NE > 16 ? 320 : 512, 1) eig_jacobi_reg_kernel(
 #pragma unroll
                             for (int e = 0; e < NE; e++) {
                                 const double xv = xr[e];
-                                xr[e] = cs * xv - sn * yr[e];
-                                y[32 * e] = sn * xv + cs * yr[e];
+                                const double yv = YREG ? yr[e] : y[32 * e];
+                                xr[e] = cs * xv - sn * yv;
+                                y[32 * e] = sn * xv + cs * yv;
                             }
                             a -= tt * c;
                             if (lane == 0) nrm[j] = bn + tt * c;
@@ -523,7 +526,7 @@ int eig_launch(ithaca_b200* h, int* sweeps)
     double* X = h->dW;
     const char* ev = getenv("ITHACA_B200_EIG");       // "block" selects the shared-memory kernel (A/B measurements)
     const char* evb = getenv("ITHACA_B200_EIG_B");    // columns per block (tuning)
-    const bool use_reg = m <= 1024 && !(ev && strcmp(ev, "block") == 0);
+    const bool use_reg = m <= 2048 && !(ev && strcmp(ev, "block") == 0);
     int b, threads;
     size_t smem;
     void* kern = nullptr;
@@ -531,7 +534,7 @@ int eig_launch(ithaca_b200* h, int* sweeps)
         // register-resident kernel: one block of b padded columns (+ b squared norms) in shared memory
         int NE = 2;
         while (32 * NE < m) NE *= 2;
-        const int bmax = NE > 16 ? 10 : 16;
+        const int bmax = NE > 32 ? 8 : NE > 16 ? 10 : 16;
         b = std::min(8, m);   // measured (scripts/eig_bench.py): b = 8 beats 4, 12, 16 at m = 200 and m = 1000
         if (evb) b = std::max(2, std::min({atoi(evb), bmax, m}));
         if (b < 2 && m >= 2) b = 2;
@@ -542,7 +545,8 @@ int eig_launch(ithaca_b200* h, int* sweeps)
             case 4: kern = (void*)eig_jacobi_reg_kernel<4>; break;
             case 8: kern = (void*)eig_jacobi_reg_kernel<8>; break;
             case 16: kern = (void*)eig_jacobi_reg_kernel<16>; break;
-            default: kern = (void*)eig_jacobi_reg_kernel<32>; break;
+            case 32: kern = (void*)eig_jacobi_reg_kernel<32>; break;
+            default: kern = (void*)eig_jacobi_reg_kernel<64>; break;
         }
     } else {
         // block size: 2b columns of m doubles must fit shared memory; one warp per pair of an inner round

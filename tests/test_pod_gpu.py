@@ -72,13 +72,21 @@ def test_gram_vs_reference_build(pkg, pod):
     assert rel_max(G, po.ref_gram(S, V, dim, 1)) <= 1e-13
 
 
-@pytest.mark.parametrize("m", [2, 3, 16, 57, 200, 333])
+@pytest.mark.parametrize("m", [2, 3, 16, 57, 200, 333, 600, 1100, 2100])
 def test_eig_matches_numpy(pkg, pod, m):
+    """Every kernel variant: register-resident NE = 2..64 (m <= 2048) and the shared-memory block kernel (m = 2100)."""
     rng = np.random.default_rng(m)
     A = rng.standard_normal((m + 5, m))
     G = A.T @ A
     pod.set_gram(G)
-    ev, Q = pod.eig(m)
+    ev, Q = pod.eig(min(m, 104) if m > 400 else m)
+    m_full, m = m, Q.shape[1]
+    if m < m_full:
+        w = np.linalg.eigvalsh(G)[::-1]
+        assert np.abs(ev - w).max() <= 1e-12 * w[0]
+        assert np.abs(Q.T @ Q - np.eye(m)).max() <= 1e-12
+        assert np.abs(G @ Q - Q * ev[:m]).max() <= 1e-12 * w[0]
+        return
     w = np.linalg.eigvalsh(G)[::-1]
     assert np.abs(ev - w).max() <= 1e-12 * w[0]
     assert np.abs(Q.T @ Q - np.eye(m)).max() <= 1e-12
