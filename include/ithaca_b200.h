@@ -197,7 +197,8 @@ int ithaca_b200_basis_upload(ithaca_b200_t* h, int which, const double* const* i
                              const double* const* bnd_ptrs, int n);
 
 enum { IB200_OP_M = 0, IB200_OP_B = 1, IB200_OP_K = 2, IB200_OP_P = 3, IB200_OP_C = 4, IB200_OP_C_MATERIALISED = 5,
-       IB200_OP_D = 6, IB200_OP_G = 7, IB200_OP_BC3 = 8, IB200_OP_BC4 = 9, IB200_OP_BC1 = 10 };
+       IB200_OP_D = 6, IB200_OP_G = 7, IB200_OP_BC3 = 8, IB200_OP_BC4 = 9, IB200_OP_BC1 = 10, IB200_OP_BC2 = 11,
+       IB200_OP_BP = 12, IB200_OP_CF = 13 };
 /* One projected operator, laid out as the reference's Eigen object (column-major):
  *   IB200_OP_M  mass_term              steadyNS.C:1085-1108   N x N        M(i,j) = int U_i . U_j
  *   IB200_OP_B  diffusive_term         steadyNS.C:883-907     N x N        B(i,j) = int U_i . laplacian(1, U_j)
@@ -218,6 +219,16 @@ enum { IB200_OP_M = 0, IB200_OP_B = 1, IB200_OP_K = 2, IB200_OP_P = 3, IB200_OP_
  *   IB200_OP_BC1  pressure_BC1         steadyNS.C:1319-1354   Np x N       sum over boundary faces of
  *                 (interpolate(laplacian(U_j)) & Sf) P_i: the boundary value of an fvc::laplacian result is the owner cell's
  *                 value (extrapolatedCalculated patch of fvc::surfaceIntegrate)
+ *   IB200_OP_BC2  pressureBC2          steadyNS.C:1396-1437   Np x N x N   BC2(i,j,k) = sum over boundary faces of
+ *                 (interpolate(div(interpolate(U_j) & Sf, U_k)) & Sf) P_i, i fastest (Eigen::Tensor; slice i = the List entry
+ *                 BC2_matrix[i] of pressure_BC2 :1356-1394); the boundary value of the fvc::div result is the owner cell's
+ * The fvc-only operators of steadyNS::discretizeThenProject (steadyNS.C:709-881, "inconsistent" flux method):
+ *   IB200_OP_BP   diffusive_term_flux_method  steadyNS.C:1584-1610  Np x N      BP(i,j) = int P_i div(laplacian(1, U_j))
+ *   IB200_OP_CF   convective_term_flux_tens   steadyNS.C:1704-1746  Np x N x N  Cf(i,j,k) = int P_i div(div(flux(U_j), U_k)),
+ *                 i fastest. The inner fvc:: result is assigned to a volVectorField before the outer div, so its boundary
+ *                 value is the owner cell's (extrapolatedCalculated patch copied by GeometricField::operator=). Computed
+ *                 through the adjoint of the outer div: int P_i div(A) = int t_i . A with one precomputed vector field t_i
+ *                 per pressure mode, so BP is one contraction and Cf is the fused face-based contraction of G.
  * BC1, BC3 and BC4 are returned for ALL N velocity fields; the reference keeps the leading lift + NUmodes columns
  * (P_BC2size = NUmodes + liftfield.size()): take leftCols. Faces of masked (`empty`) patches do not contribute. */
 int ithaca_b200_project(ithaca_b200_t* h, int op, double* out);

@@ -376,7 +376,7 @@ class Partition:
             pass
 
 
-OPS = {"M": 0, "B": 1, "K": 2, "P": 3, "C": 4, "Cmat": 5, "D": 6, "G": 7, "BC3": 8, "BC4": 9, "BC1": 10}
+OPS = {"M": 0, "B": 1, "K": 2, "P": 3, "C": 4, "Cmat": 5, "D": 6, "G": 7, "BC3": 8, "BC4": 9, "BC1": 10, "BC2": 11, "BP": 12, "Cf": 13}
 FVC = {"flux": 0, "div_phi": 1, "laplacian": 2, "grad_p": 3, "div_u": 4}
 
 
@@ -437,7 +437,7 @@ class Projector:
     def project(self, op):
         N, Np = self.N, self.Np
         shape = {"M": (N, N), "B": (N, N), "K": (N, Np), "P": (Np, N), "C": (N, N, N), "Cmat": (N, N, N), "D": (Np, Np),
-                 "G": (Np, N, N), "BC3": (Np, N), "BC4": (Np, N), "BC1": (Np, N)}[op]
+                 "G": (Np, N, N), "BC3": (Np, N), "BC4": (Np, N), "BC1": (Np, N), "BC2": (Np, N, N), "BP": (Np, N), "Cf": (Np, N, N)}[op]
         out = np.zeros(shape, order="F")
         self.pod._chk(self.L.ithaca_b200_project(self.h, OPS[op], out.ctypes.data))
         return out

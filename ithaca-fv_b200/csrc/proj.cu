@@ -457,6 +457,55 @@ grad_scalar_kernel(MeshDev m, const double* __restrict__ P, long long ldP, const
             for (int d = 0; d < 3; d++) out[(size_t)(j0 + jj) * ldo + 3 * c + d] = acc[jj][d] / V;
 }
 
+// Adjoint of `fvc::div` with owner-extrapolated boundary values: int P_i div(A) = sum_c V_c A[c] . t_i[c] for every vector
+// field A whose boundary value is its owner cell's (the fvc:: results of the flux-method operators BP / Cf), with
+//   t_i[c] = ( sum_{f in c, internal} wc(f) Sf (P_i[own(f)] - P_i[nei(f)]) + sum_{b in c} Sf_b P_i[c] ) / V_c,
+// wc(f) = w_f when c owns f, 1 - w_f otherwise. Same cell walk as grad_scalar_kernel.
+__global__ void __launch_bounds__(PROJ_T)
+div_adjoint_kernel(MeshDev m, const double* __restrict__ P, long long ldP, int np, double* __restrict__ out, long long ldo)
+{
+    const long long c = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    if (c >= m.nCells) return;
+    const int j0 = blockIdx.y * FB;
+    double pc[FB], acc[FB][3];
+#pragma unroll
+    for (int jj = 0; jj < FB; jj++) {
+        pc[jj] = P[(size_t)min(j0 + jj, np - 1) * ldP + c];
+        acc[jj][0] = acc[jj][1] = acc[jj][2] = 0.0;
+    }
+    const int e0 = m.off[c], e1 = m.off[c + 1];
+    for (int e = e0; e < e1; e++) {
+        const int en = m.ent[e], ot = m.other[e];
+        const long long f = abs(en) - 1;
+        const double s[3] = {m.Sf[3 * f], m.Sf[3 * f + 1], m.Sf[3 * f + 2]};
+        if (ot >= 0) {
+            const double w = m.w[f];
+            const bool own = en > 0;
+            const double wc = own ? w : 1.0 - w;
+#pragma unroll
+            for (int jj = 0; jj < FB; jj++) {
+                const double x = P[(size_t)min(j0 + jj, np - 1) * ldP + ot];
+                const double dp = wc * (own ? pc[jj] - x : x - pc[jj]);
+#pragma unroll
+                for (int d = 0; d < 3; d++) acc[jj][d] += s[d] * dp;
+            }
+        } else {
+            const long long b = -(long long)ot - 1;
+            if (!m.bmask[b]) continue;
+#pragma unroll
+            for (int jj = 0; jj < FB; jj++)
+#pragma unroll
+                for (int d = 0; d < 3; d++) acc[jj][d] += s[d] * pc[jj];
+        }
+    }
+    const double V = m.V[c];
+#pragma unroll
+    for (int jj = 0; jj < FB; jj++)
+        if (j0 + jj < np)
+#pragma unroll
+            for (int d = 0; d < 3; d++) out[(size_t)(j0 + jj) * ldo + 3 * c + d] = acc[jj][d] / V;
+}
+
 // K7a: T_j = fvc::grad(U_j), Gauss linear: T[c][i][d] = sum_f +-Sf_i * Uf_d / V. One field per block.
 __global__ void __launch_bounds__(PROJ_T)
 grad_vec_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const double* __restrict__ Ub, long long ldUb,
@@ -624,6 +673,74 @@ bnd_owner_dot_sf_kernel(MeshDev m, const unsigned char* __restrict__ cmask, cons
         v = l[0] * m.Sf[3 * f] + l[1] * m.Sf[3 * f + 1] + l[2] * m.Sf[3 * f + 2];
     }
     out[(size_t)j * ldo + b] = v;
+}
+
+// Db[k][b] = fvc::div(phi, U_k)[owner(b)] . Sf_b for the boundary faces b (BC2 = Pb^T Db per flux field): the div(phi_j, U_k)
+// value of the owner cell is recomputed from the cell's CSR segment with div_phi_kernel's own arithmetic (same order, same
+// rounding), so only the N_b boundary-owner cells are visited instead of materialising N^2 whole div fields.
+__global__ void __launch_bounds__(PROJ_T)
+bnd_div_phi_dot_sf_kernel(MeshDev m, const unsigned char* __restrict__ cmask, const double* __restrict__ phi,
+                          const double* __restrict__ U, long long ldU, const double* __restrict__ Ub, long long ldUb, int nk,
+                          double* __restrict__ out, long long ldo)
+{
+    const long long bf = blockIdx.x * (long long)PROJ_T + threadIdx.x;
+    if (bf >= m.nBnd) return;
+    const int k0 = blockIdx.y * FB;
+    const long long fb = m.nInt + bf;
+    const int c = m.owner[fb];
+    if (!bnd_face_active(m, cmask, bf, c)) {
+#pragma unroll
+        for (int kk = 0; kk < FB; kk++)
+            if (k0 + kk < nk) out[(size_t)(k0 + kk) * ldo + bf] = 0.0;
+        return;
+    }
+    double uc[FB][3], acc[FB][3];
+#pragma unroll
+    for (int kk = 0; kk < FB; kk++) {
+        const int k = min(k0 + kk, nk - 1);
+#pragma unroll
+        for (int d = 0; d < 3; d++) { uc[kk][d] = U[(size_t)k * ldU + 3 * (size_t)c + d]; acc[kk][d] = 0.0; }
+    }
+    const int e0 = m.off[c], e1 = m.off[c + 1];
+    for (int e = e0; e < e1; e++) {
+        const int en = m.ent[e], ot = m.other[e];
+        const long long f = abs(en) - 1;
+        const double ph = phi[f];
+        if (ot >= 0) {
+            const double w = m.w[f], w1 = 1.0 - w;
+            const bool own = en > 0;
+#pragma unroll
+            for (int kk = 0; kk < FB; kk++) {
+                const int k = min(k0 + kk, nk - 1);
+                const double* un = U + (size_t)k * ldU + 3 * (size_t)ot;
+#pragma unroll
+                for (int d = 0; d < 3; d++) {
+                    const double x = un[d];
+                    const double uf = own ? (w * uc[kk][d] + w1 * x) : (w * x + w1 * uc[kk][d]);
+                    const double v = ph * uf;
+                    acc[kk][d] += own ? v : -v;
+                }
+            }
+        } else {
+            const long long b = -(long long)ot - 1;
+            if (!m.bmask[b]) continue;
+#pragma unroll
+            for (int kk = 0; kk < FB; kk++) {
+                const int k = min(k0 + kk, nk - 1);
+                const double* ub = Ub + (size_t)k * ldUb + 3 * b;
+#pragma unroll
+                for (int d = 0; d < 3; d++) acc[kk][d] += ph * ub[d];
+            }
+        }
+    }
+    const double V = m.V[c];
+    const double sx = m.Sf[3 * fb], sy = m.Sf[3 * fb + 1], sz = m.Sf[3 * fb + 2];
+#pragma unroll
+    for (int kk = 0; kk < FB; kk++) {
+        const int k = k0 + kk;
+        if (k >= nk) break;
+        out[(size_t)k * ldo + bf] = (acc[kk][0] / V) * sx + (acc[kk][1] / V) * sy + (acc[kk][2] / V) * sz;
+    }
 }
 
 // Xp[j][b] = component `comp` of U_j on patch face start+b (j < N), Xp[N][b] = 1   (bcVelocityVec / bcVelocityMat)
@@ -1365,7 +1482,8 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
     PROJ_REQUIRE(s && s->have_mesh && s->nU > 0, "project: call mesh_upload and basis_upload(U) first");
     PROJ_REQUIRE(out, "project: null output");
     PROJ_REQUIRE((op != IB200_OP_K && op != IB200_OP_P && op != IB200_OP_D && op != IB200_OP_G && op != IB200_OP_BC3 &&
-                  op != IB200_OP_BC4 && op != IB200_OP_BC1) || s->nP > 0, "project: K, P, D, G, BC1, BC3 and BC4 need basis_upload(P)");
+                  op != IB200_OP_BC4 && op != IB200_OP_BC1 && op != IB200_OP_BC2 && op != IB200_OP_BP && op != IB200_OP_CF) || s->nP > 0,
+                 "project: K, P, D, G, BC1-BC4, BP and Cf need basis_upload(P)");
     cudaSetDevice(h->device);
     const MeshDev m = mesh_dev(s);
     const int N = s->nU, Np = s->nP, BIG = 0x7fffffff;
@@ -1601,6 +1719,91 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
             StageTimer t(h->stream, &s->ms[5]);
             rc = atvb_launch(h, s->bndB.as<double>(), ld3, Np, s->bndA.as<double>(), ld3, N, 3 * s->nBnd, nullptr, 1, 0, s->out.as<double>(), 1,
                              BIG, 0, Np);
+            t.stop();
+            if (rc) return rc;
+        }
+        break;
+    }
+    case IB200_OP_BC2: {  // pressureBC2 (== pressure_BC2), steadyNS.C:1356-1437: Np x N x N, i fastest; boundary-face sum of
+                          // (div(interpolate(U_j) & Sf, U_k)[owner] . Sf) P_i
+        nout = (size_t)Np * N * N;
+        if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
+        IB_CUDA(h, cudaMemsetAsync(s->out.p, 0, nout * sizeof(double), h->stream));
+        if (s->nBnd > 0) {
+            if ((rc = need_flux(h, s))) return rc;
+            const long long ldB = pad16(s->nBnd);
+            const int jb = (int)std::max<size_t>(1, std::min<size_t>((size_t)N, (size_t)2e9 / ((size_t)ldB * N * sizeof(double))));
+            if ((rc = ensure(h, s->bndA, (size_t)jb * N * ldB * sizeof(double)))) return rc;
+            for (int j0 = 0; j0 < N; j0 += jb) {
+                const int nj = std::min(jb, N - j0);
+                {
+                    StageTimer t(h->stream, &s->ms[1]);
+                    for (int jj = 0; jj < nj; jj++) {
+                        bnd_div_phi_dot_sf_kernel<<<dim3(gx(s->nBnd), gy(N)), PROJ_T, 0, h->stream>>>(
+                            m, shard ? s->cmask.as<unsigned char>() : nullptr, s->flux.as<double>() + (size_t)(j0 + jj) * s->ldF, U, s->ldU,
+                            s->Ub.as<double>(), s->ldUb, N, s->bndA.as<double>() + (size_t)jj * N * ldB, ldB);
+                        h->launches += 1;
+                    }
+                    t.stop();
+                }
+                StageTimer t(h->stream, &s->ms[5]);
+                // column jj*N + k of bndA = div(phi_{j0+jj}, U_k)[owner] . Sf  ->  BC2(i, j0+jj, k) at i + Np*(j + N*k)
+                rc = atvb_launch(h, s->Pb.as<double>(), s->ldPb, Np, s->bndA.as<double>(), ldB, nj * N, s->nBnd, nullptr, 1, 0,
+                                 s->out.as<double>() + (size_t)Np * j0, 1, N, Np, (long long)Np * N);
+                t.stop();
+                if (rc) return rc;
+            }
+        }
+        break;
+    }
+    case IB200_OP_BP:    // diffusive_term_flux_method, steadyNS.C:1584-1610: Np x N, int P_i div(laplacian(U_j))
+    case IB200_OP_CF: {  // convective_term_flux_tens, steadyNS.C:1704-1746: Np x N x N, int P_i div(div(flux(U_j), U_k)), i fastest
+        // both through the adjoint of the outer div (div_adjoint_kernel): int P_i div(A) = int t_i . A, so BP is one
+        // contraction against the laplacian fields and Cf is the fused face-based contraction of G with t_i as test fields
+        nout = op == IB200_OP_BP ? (size_t)Np * N : (size_t)Np * N * N;
+        if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
+        if ((rc = ensure(h, s->gradP, (size_t)Np * s->ldU * sizeof(double)))) return rc;
+        {
+            StageTimer t(h->stream, &s->ms[3]);
+            div_adjoint_kernel<<<dim3(gx(s->nCells), gy(Np)), PROJ_T, 0, h->stream>>>(m, s->P.as<double>(), s->ldP, Np,
+                                                                                       s->gradP.as<double>(), s->ldU);
+            t.stop();
+            h->launches += 1;
+        }
+        if (op == IB200_OP_BP) {
+            if ((rc = ensure(h, s->work, (size_t)N * s->ldU * sizeof(double)))) return rc;
+            if ((rc = run_laplacians(h, s, s->work.as<double>()))) return rc;
+            StageTimer t(h->stream, &s->ms[5]);
+            rc = atvb_launch(h, s->gradP.as<double>(), s->ldU, Np, s->work.as<double>(), s->ldU, N, K3, V, 3, 0, s->out.as<double>(), 1,
+                             BIG, 0, Np);
+            t.stop();
+            if (rc) return rc;
+            break;
+        }
+        if (Np <= N) {
+            ConvMesh cm;
+            cm.nInt = s->nInt; cm.nBnd = s->nBnd; cm.owner = m.owner; cm.neigh = m.neigh; cm.Sf = m.Sf; cm.w = m.w; cm.bmask = m.bmask;
+            cm.cmask = shard ? s->cmask.as<unsigned char>() : nullptr;
+            rc = conv_fused_launch(h, &s->conv, cm, s->nCells, U, s->ldU, s->Ub.as<double>(), s->ldUb, N, s->out.as<double>(), &s->ms[6],
+                                   &s->ms[5], s->gradP.as<double>(), s->ldU, Np);   // writes Cf(i,j,k) at i + Np*(j + N*k)
+            if (rc) return rc;
+            break;
+        }
+        if ((rc = need_flux(h, s))) return rc;
+        const size_t percol = (size_t)s->ldU * sizeof(double);
+        int jb = (int)std::max<size_t>(1, std::min<size_t>({(size_t)N, 8, (size_t)12e9 / (percol * N)}));
+        if ((rc = ensure(h, s->work, (size_t)jb * N * percol))) return rc;
+        for (int j0 = 0; j0 < N; j0 += jb) {
+            const int nj = std::min(jb, N - j0);
+            for (int jj = 0; jj < nj; jj++) {
+                div_phi_kernel<<<dim3(gx(s->nCells), gy(N)), PROJ_T, 0, h->stream>>>(
+                    m, s->flux.as<double>() + (size_t)(j0 + jj) * s->ldF, U, s->ldU, s->Ub.as<double>(), s->ldUb, N,
+                    s->work.as<double>() + (size_t)jj * N * s->ldU, s->ldU);
+                h->launches += 1;
+            }
+            StageTimer t(h->stream, &s->ms[5]);
+            rc = atvb_launch(h, s->gradP.as<double>(), s->ldU, Np, s->work.as<double>(), s->ldU, nj * N, K3, V, 3, 0,
+                             s->out.as<double>() + (size_t)Np * j0, 1, N, Np, (long long)Np * N);
             t.stop();
             if (rc) return rc;
         }

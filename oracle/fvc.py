@@ -173,6 +173,33 @@ class Oracle:
         self.L.fvo_pressure_bc1(self._ref(), len(fs), len(fpb), pu, pub, ppb, P(out.ctypes.data))
         return out
 
+    def pressure_bc2(self, U, Ub, Pb):
+        """pressureBC2 (steadyNS.C:1396-1437): Np x N x N, i fastest."""
+        fs, pu = self._ptrs(U)
+        fb, pub = self._ptrs(Ub)
+        fpb, ppb = self._ptrs(Pb)
+        out = np.zeros((len(fpb), len(fs), len(fs)), order="F")
+        self.L.fvo_pressure_bc2(self._ref(), len(fs), len(fpb), pu, pub, ppb, P(out.ctypes.data))
+        return out
+
+    def diffusive_term_flux_method(self, U, Ub, Pm):
+        """BP (steadyNS.C:1584-1610): Np x N."""
+        fs, pu = self._ptrs(U)
+        fb, pub = self._ptrs(Ub)
+        fp, pp = self._ptrs(Pm)
+        out = np.zeros((len(fp), len(fs)), order="F")
+        self.L.fvo_diffusive_term_flux_method(self._ref(), len(fs), len(fp), pu, pub, pp, P(out.ctypes.data))
+        return out
+
+    def convective_term_flux_tens(self, U, Ub, Pm):
+        """Cf (steadyNS.C:1704-1746, inconsistent flux method): Np x N x N, i fastest."""
+        fs, pu = self._ptrs(U)
+        fb, pub = self._ptrs(Ub)
+        fp, pp = self._ptrs(Pm)
+        out = np.zeros((len(fp), len(fs), len(fs)), order="F")
+        self.L.fvo_convective_term_flux_tens(self._ref(), len(fs), len(fp), pu, pub, pp, P(out.ctypes.data))
+        return out
+
     def convective_background(self, U, Ub, vls, vlsb, Pm=None, Pb=None):
         """Pm None: L (N x N, steadyNS.C:1256-1273); else L_D (Np x N, :1275-1293)."""
         fs, pu = self._ptrs(U)

@@ -436,6 +436,81 @@ void fvo_pressure_bc1(const fvo_mesh* m, int N, int Np, const double* const* U, 
     free(L);
 }
 
+/* steadyNS::pressureBC2 / pressure_BC2, steadyNS.C:1356-1437: BC2(i,j,k) = sum over boundary faces of
+ * interpolate(div(interpolate(U_j) & Sf, U_k)) & (Sf * interpolate(P_i))  (C++ precedence: `*` binds before `&`). The
+ * boundary value of the fvc::div result is the owner cell's value (extrapolatedCalculated patch of surfaceIntegrate).
+ * Np x N x N with i fastest (Eigen::Tensor storage; slice i is BC2_matrix[i] of the List form). */
+void fvo_pressure_bc2(const fvo_mesh* m, int N, int Np, const double* const* U, const double* const* Ub, const double* const* Pb,
+                      double* BC2)
+{
+    double* phi = (double*)malloc(sizeof(double) * (m->nInt + m->nBnd));
+    double* D = (double*)malloc(sizeof(double) * 3 * m->nCells);
+    for (int i = 0; i < Np; i++)
+        for (int j = 0; j < N; j++)
+            for (int k = 0; k < N; k++) {
+                fvo_flux(m, U[j], Ub[j], phi);
+                fvo_div_phi_vec(m, phi, U[k], Ub[k], D);
+                double s = 0.0;
+                for (long long b = 0; b < m->nBnd; b++) {
+                    if (!m->bmask[b]) continue;
+                    const long long f = m->nInt + b, c = m->owner[f];
+                    const double p = Pb[i][b];
+                    s += D[3 * c] * (m->Sf[3 * f] * p) + D[3 * c + 1] * (m->Sf[3 * f + 1] * p) + D[3 * c + 2] * (m->Sf[3 * f + 2] * p);
+                }
+                BC2[i + (size_t)Np * (j + (size_t)N * k)] = s;
+            }
+    free(phi); free(D);
+}
+
+/* fvc::div(A) of a vector field A that came out of another fvc:: operator and was assigned to a volVectorField
+ * (`L_U_SUPmodesaux = dt_dummy * fvc::laplacian(...)`, steadyNS.C:1598-1601, :1727-1736): GeometricField::operator=
+ * copies the result's extrapolatedCalculated patch values, i.e. the boundary value is the owner cell's. out: nCells. */
+static void div_vec_extrapolated(const fvo_mesh* m, const double* A, double* Ab, double* out)
+{
+    for (long long b = 0; b < m->nBnd; b++) {
+        const long long c = m->owner[m->nInt + b];
+        for (int d = 0; d < 3; d++) Ab[3 * b + d] = A[3 * c + d];
+    }
+    fvo_div_vec(m, A, Ab, out);
+}
+
+/* steadyNS::diffusive_term_flux_method, steadyNS.C:1584-1610: BP(i,j) = domainIntegrate(P_i * div(dt_dummy *
+ * laplacian(nu_dummy, U_j))), dt_dummy = nu_dummy = 1. BP: Np x N. */
+void fvo_diffusive_term_flux_method(const fvo_mesh* m, int N, int Np, const double* const* U, const double* const* Ub,
+                                    const double* const* P, double* BP)
+{
+    double* L = (double*)malloc(sizeof(double) * 3 * m->nCells);
+    double* Lb = (double*)malloc(sizeof(double) * 3 * (m->nBnd + 1));
+    double* D = (double*)malloc(sizeof(double) * m->nCells);
+    for (int i = 0; i < Np; i++)
+        for (int j = 0; j < N; j++) {
+            fvo_laplacian_vec(m, U[j], Ub[j], L);
+            div_vec_extrapolated(m, L, Lb, D);
+            BP[i + (size_t)j * Np] = fvo_domain_integrate_dot(m, P[i], D, 1);
+        }
+    free(L); free(Lb); free(D);
+}
+
+/* steadyNS::convective_term_flux_tens, steadyNS.C:1704-1746 (fluxMethod != "consistent"): Cf(i,j,k) =
+ * domainIntegrate(P_i * div(dt_dummy * div(flux(U_j), U_k))), fvc::flux(U) = interpolate(U) & Sf. Np x N x N, i fastest. */
+void fvo_convective_term_flux_tens(const fvo_mesh* m, int N, int Np, const double* const* U, const double* const* Ub,
+                                   const double* const* P, double* Cf)
+{
+    double* phi = (double*)malloc(sizeof(double) * (m->nInt + m->nBnd));
+    double* A = (double*)malloc(sizeof(double) * 3 * m->nCells);
+    double* Ab = (double*)malloc(sizeof(double) * 3 * (m->nBnd + 1));
+    double* D = (double*)malloc(sizeof(double) * m->nCells);
+    for (int j = 0; j < N; j++) {
+        fvo_flux(m, U[j], Ub[j], phi);
+        for (int k = 0; k < N; k++) {
+            fvo_div_phi_vec(m, phi, U[k], Ub[k], A);
+            div_vec_extrapolated(m, A, Ab, D);
+            for (int i = 0; i < Np; i++) Cf[i + (size_t)Np * (j + (size_t)N * k)] = fvo_domain_integrate_dot(m, P[i], D, 1);
+        }
+    }
+    free(phi); free(A); free(Ab); free(D);
+}
+
 /* steadyNS::convective_background (kind 0, steadyNS.C:1256-1273): L(i,j) = -domainIntegrate(U_i & div(interpolate(vls) & Sf, U_j)),
  * N x N; steadyNS::divergent_convective_background (kind 1, :1275-1293): L_D(i,j) = -domainIntegrate(grad(P_i) & div(...)), Np x N. */
 void fvo_convective_background(const fvo_mesh* m, int kind, int N, int Np, const double* const* U, const double* const* Ub,

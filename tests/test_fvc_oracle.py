@@ -196,3 +196,48 @@ def test_background_convection_and_bc1_definitions(cyl):
     own = m.owner[m.nInt:]
     want = np.sum((lap[own] * m.Sf[m.nInt:]).sum(axis=1)[act])
     assert abs(BC1[0, 0] - want) <= 1e-12 * np.abs(BC1).max()
+
+
+def test_bc2_definition(cyl):
+    """pressureBC2 (steadyNS.C:1396-1437): slice (i, j, k) = boundary sum of div(phi_j, U_k)[owner] . Sf P_i -- restated here
+    from the oracle's own flux / div_phi fields; linear in P_i and U_k."""
+    m = cyl
+    o = fvc.Oracle(m)
+    U, Ub, P, Pb = fvc.synthetic_basis(m, 3, 2, seed=9)
+    BC2 = o.pressure_bc2(U, Ub, Pb)
+    assert BC2.shape == (2, 3, 3)
+    act = m.bmask.astype(bool)
+    own = m.owner[m.nInt:]
+    Sb = m.Sf[m.nInt:]
+    for (i, j, k) in [(0, 0, 0), (1, 2, 1), (0, 1, 2)]:
+        d = o.div_phi(o.flux(U[j], Ub[j]), U[k], Ub[k]).reshape(-1, 3)
+        want = np.sum(((d[own] * Sb).sum(axis=1) * Pb[i])[act])
+        assert abs(BC2[i, j, k] - want) <= 1e-12 * np.abs(BC2).max()
+    lin = o.pressure_bc2([U[0], U[1] - 2.0 * U[2]], [Ub[0], Ub[1] - 2.0 * Ub[2]], [Pb[0] + 0.5 * Pb[1]])
+    want = BC2[0, 0, 1] - 2.0 * BC2[0, 0, 2] + 0.5 * (BC2[1, 0, 1] - 2.0 * BC2[1, 0, 2])
+    assert abs(lin[0, 0, 1] - want) <= 1e-12 * np.abs(BC2).max()
+
+
+def test_flux_method_operators_definitions(cyl):
+    """diffusive_term_flux_method / convective_term_flux_tens (steadyNS.C:1584-1610, :1704-1746): int P_i div(A) with A an
+    fvc:: result whose boundary value is its owner cell's. Known answer (Gauss theorem): with P = 1 the volume integral of
+    div(A) is the boundary sum of A[owner] . Sf, i.e. BP[P=1] == BC1[P=1] and Cf[P=1] == BC2[P=1]."""
+    m = cyl
+    o = fvc.Oracle(m)
+    U, Ub, P, Pb = fvc.synthetic_basis(m, 3, 2, seed=10)
+    one_c, one_b = np.ones(m.nCells), np.ones(m.nBnd)
+    BP = o.diffusive_term_flux_method(U, Ub, [one_c] + P)
+    Cf = o.convective_term_flux_tens(U, Ub, [one_c] + P)
+    BC1 = o.pressure_bc1(U, Ub, [one_b])
+    BC2 = o.pressure_bc2(U, Ub, [one_b])
+    assert BP.shape == (3, 3) and Cf.shape == (3, 3, 3)
+    assert np.abs(BP[0] - BC1[0]).max() <= 1e-11 * max(np.abs(BC1).max(), np.abs(BP).max())
+    assert np.abs(Cf[0] - BC2[0]).max() <= 1e-11 * max(np.abs(BC2).max(), np.abs(Cf).max())
+    # definition, restated from the oracle's own fields
+    own = m.owner[m.nInt:]
+    L = o.laplacian(U[1], Ub[1])
+    d = o.div(L, np.ascontiguousarray(L.reshape(-1, 3)[own].ravel()))
+    assert abs(BP[2, 1] - np.sum(m.V * P[1] * d)) <= 1e-12 * np.abs(BP).max()
+    A = o.div_phi(o.flux(U[2], Ub[2]), U[0], Ub[0])
+    d = o.div(A, np.ascontiguousarray(A.reshape(-1, 3)[own].ravel()))
+    assert abs(Cf[1, 2, 0] - np.sum(m.V * P[0] * d)) <= 1e-12 * np.abs(Cf).max()

@@ -82,6 +82,14 @@ def test_ppe_operators_match_oracle(case, monkeypatch):
     assert rel(pr.project("BC4"), orc.pressure_bc4(Ub, Pb)) <= TOL
     assert rel(pr.project("BC3"), orc.pressure_bc3(U, Ub, P, Pb)) <= TOL
     assert rel(pr.project("BC1"), orc.pressure_bc1(U, Ub, Pb)) <= TOL
+    BC2 = pr.project("BC2")
+    BC2r = orc.pressure_bc2(U, Ub, Pb)
+    assert BC2.shape == BC2r.shape and rel(BC2, BC2r) <= TOL
+    # fvc-only operators of discretizeThenProject (flux method): adjoint of the outer div on the device
+    assert rel(pr.project("BP"), orc.diffusive_term_flux_method(U, Ub, P)) <= TOL
+    Cf = pr.project("Cf")
+    Cfr = orc.convective_term_flux_tens(U, Ub, P)
+    assert Cf.shape == Cfr.shape and rel(Cf, Cfr) <= TOL
     vls, vlsb = U[1] + 0.5 * U[2], Ub[1] + 0.5 * Ub[2]
     assert rel(pr.project_background(vls, vlsb), orc.convective_background(U, Ub, vls, vlsb)) <= TOL
     assert rel(pr.project_background(vls, vlsb, divergent=True), orc.convective_background(U, Ub, vls, vlsb, P, Pb)) <= TOL
@@ -180,7 +188,8 @@ def test_sharded_projection_sums_to_the_global_operators(pkg, pod, nranks, name,
     ref = {"M": orc.mass_term(U), "B": orc.diffusive_term(U, Ub), "K": orc.pressure_gradient_term(U, P, Pb),
            "P": orc.divergence_term(U, Ub, P), "C": orc.convective_term_tens(U, Ub, cache=True),
            "D": orc.laplacian_pressure(P, Pb), "G": orc.div_momentum(U, Ub, P, Pb), "BC3": orc.pressure_bc3(U, Ub, P, Pb),
-           "BC4": orc.pressure_bc4(Ub, Pb), "BC1": orc.pressure_bc1(U, Ub, Pb)}
+           "BC4": orc.pressure_bc4(Ub, Pb), "BC1": orc.pressure_bc1(U, Ub, Pb), "BC2": orc.pressure_bc2(U, Ub, Pb),
+           "BP": orc.diffusive_term_flux_method(U, Ub, P), "Cf": orc.convective_term_flux_tens(U, Ub, P)}
     ref["Cmat"] = ref["C"]
     acc = {k: np.zeros_like(v) for k, v in ref.items()}
     pr = pkg.Projector(pod)
