@@ -82,6 +82,15 @@ int ithaca_b200_pod_upload(ithaca_b200_t* h, const double* const* snap_ptrs, int
  * (ITHACAcoeffsMass.C:87-105 ignores consider_volumes for vol fields). G_out: m*m doubles, host, or NULL. */
 int ithaca_b200_pod_gram(ithaca_b200_t* h, double* G_out);
 
+/* Correlation matrix of the moving-mesh getModes overload, one volume field PER SNAPSHOT
+ * (getModes(snapshots, modes, Volumes, ...), ITHACAPOD.C:1392-1541, loop :1425-1445):
+ *   G(i,j) = S_i^T diag(sqrt|V_i V_j|) S_j  =  (S_i sqrt|V_i|)^T (S_j sqrt|V_j|),
+ * formed as ONE unweighted symmetric contraction of the row-scaled snapshot matrix (the reference: m(m+1)/2 weighted dot
+ * products, each building an N_d temporary), all-reduced over ranks. vol_ptrs[j]: as many doubles as snapshot j (the
+ * reference multiplies V.col(j) and SnapMatrix.col(j) coefficient-wise: scalar fields in practice), host or device.
+ * Follow with pod_eig and pod_lift_scaled(factors = lambda^-1/2) (:1481-1484). G_out: m*m doubles, host, or NULL. */
+int ithaca_b200_pod_gram_volumes(ithaca_b200_t* h, const double* const* vol_ptrs, double* G_out);
+
 /* Symmetric eigensolve of the Gram by one-sided Jacobi; replaces Spectra::SymEigsSolver /
  * Eigen::SelfAdjointEigenSolver at ITHACAPOD.C:157-180. evals_out: ALL m eigenvalues, descending
  * (algebraic), un-shifted, un-normalised: the caller applies the reference's solver-dependent

@@ -24,7 +24,7 @@ SYMBOLS = [
     "ithaca_b200_pod_postprocess_eigenvalues", "ithaca_b200_pod_lift", "ithaca_b200_pod_lift_patch",
     "ithaca_b200_dmma_peak",
     "ithaca_b200_pod_set_modes", "ithaca_b200_pod_project", "ithaca_b200_pod_modes_mass", "ithaca_b200_pod_get_coeffs",
-    "ithaca_b200_pod_reconstruct", "ithaca_b200_pod_lift_scaled",
+    "ithaca_b200_pod_reconstruct", "ithaca_b200_pod_lift_scaled", "ithaca_b200_pod_gram_volumes",
     "ithaca_b200_pod_block_begin", "ithaca_b200_pod_block_upload", "ithaca_b200_pod_block_gram",
     "ithaca_b200_pod_block_gram_finish", "ithaca_b200_pod_block_lift", "ithaca_b200_pod_block_lift_finish",
     "ithaca_b200_mesh_upload", "ithaca_b200_mesh_addressing", "ithaca_b200_basis_upload", "ithaca_b200_project",
@@ -66,6 +66,7 @@ def lib():
         L.ithaca_b200_pod_set_volumes.argtypes = [P, P, L64]
         L.ithaca_b200_pod_upload.argtypes = [P, P, I, I, L64]
         L.ithaca_b200_pod_gram.argtypes = [P, P]
+        L.ithaca_b200_pod_gram_volumes.argtypes = [P, P, P]
         L.ithaca_b200_pod_eig.argtypes = [P, I, P, P, ctypes.POINTER(I)]
         L.ithaca_b200_pod_set_gram.argtypes = [P, P, I]
         L.ithaca_b200_pod_postprocess_eigenvalues.argtypes = [P, I, I, I, P, P, ctypes.POINTER(I)]
@@ -215,6 +216,20 @@ class Pod:
     def gram(self, want=True):
         G = np.zeros((self.m, self.m), order="F") if want else None
         self._chk(self.L.ithaca_b200_pod_gram(self.h, _ptr(G)))
+        return G
+
+    def gram_volumes(self, vols, want=True):
+        """Correlation matrix with one volume field per snapshot (ITHACAPOD.C:1425-1445). vols: Fortran (Nd, m) array or a
+        list of m buffers."""
+        if isinstance(vols, np.ndarray) and vols.ndim == 2:
+            assert vols.flags.f_contiguous and vols.dtype == np.float64 and vols.shape[1] == self.m
+            ptrs = [vols.ctypes.data + j * vols.strides[1] for j in range(vols.shape[1])]
+        else:
+            assert len(vols) == self.m
+            ptrs = [_ptr(v) for v in vols]
+        arr = (ctypes.c_void_p * self.m)(*ptrs)
+        G = np.zeros((self.m, self.m), order="F") if want else None
+        self._chk(self.L.ithaca_b200_pod_gram_volumes(self.h, arr, _ptr(G)))
         return G
 
     def set_gram(self, G):
@@ -489,6 +504,50 @@ def getWeightedModes(pod, snapshots, V, dim, nmodes=0, solver="spectra", Sbc=Non
     Pbc = pod.lift_patch(Sbc, nmodes) if Sbc is not None else None
     evn = ev / ev.sum()
     return dict(G=G, evals=ev, evals_norm=evn, cum=np.cumsum(evn), evecs=Q, factors=factors, modes=Phi, modes_bc=Pbc)
+
+
+def getModesSVD(pod, snapshots, V, dim, nmodes):
+    """ITHACAPOD::getModesSVD (ITHACAPOD.C:858-941) without forming the N_d x m SVD: the left singular vectors of
+    diag(sqrt V) S are diag(sqrt V) S q_i / sigma_i with (sigma_i^2, q_i) the eigenpairs of the Gram matrix, so
+    modes_i = diag(1/sqrt V) u_i = (S q_i) / sigma_i: one Gram, one eigensolve, one scaled lift. The exported "eigenvalues"
+    are ALL m singular values over their sum (:905). Singular values below sqrt(eps) sigma_0 carry the squaring's loss."""
+    m = snapshots.shape[1] if isinstance(snapshots, np.ndarray) else len(snapshots)
+    if nmodes <= 0 or nmodes > m:
+        raise IthacaB200Error("The number of requested modes cannot be bigger than the number of Snapshots")
+    pod.set_volumes(V)
+    pod.upload(snapshots, dim)
+    G = pod.gram()
+    ev_all, Q = pod.eig(nmodes)
+    sv = np.sqrt(np.maximum(ev_all, 0.0))
+    Phi = pod.lift_scaled(1.0 / sv[:nmodes])
+    evn = sv / sv.sum()
+    return dict(G=G, sv=sv, evals_norm=evn, cum=np.cumsum(evn), evecs=Q, modes=Phi)
+
+
+def getModesVolumes(pod, snapshots, volumes, nmodes=0, solver="spectra", Sbc=None):
+    """getModes(snapshots, modes, Volumes, ...) for moving meshes (ITHACAPOD.C:1392-1541): one volume field per snapshot,
+    G(i,j) = S_i^T diag(sqrt|V_i V_j|) S_j, no negative shift, modes = (S Q) diag(lambda^-1/2), eigenvalues of the kept
+    modes over their sum. Scalar fields (the reference multiplies volume and snapshot columns coefficient-wise)."""
+    m = snapshots.shape[1] if isinstance(snapshots, np.ndarray) else len(snapshots)
+    nmodes = check_nmodes(m, nmodes, solver)
+    v0 = volumes[:, 0] if isinstance(volumes, np.ndarray) and volumes.ndim == 2 else volumes[0]
+    pod.set_volumes(np.ascontiguousarray(v0))
+    pod.upload(snapshots, 1)
+    G = pod.gram_volumes(volumes)
+    ev_all, Q = pod.eig(nmodes)
+    ev = ev_all[:nmodes]
+    factors = 1.0 / np.sqrt(ev)
+    Phi = pod.lift_scaled(factors)
+    Pbc = pod.lift_patch(Sbc, nmodes) if Sbc is not None else None   # same factors applied to the boundary rows
+    evn = ev / ev.sum()
+    return dict(G=G, evals=ev, evals_norm=evn, cum=np.cumsum(evn), evecs=Q, modes=Phi, modes_bc=Pbc)
+
+
+def DEIMmodes(pod, snapshots, V, dim, nmodes=0, solver="spectra", norm="L2", Sbc=None):
+    """ITHACAPOD::DEIMmodes (ITHACAPOD.C:1739-1937): the dense arithmetic is getModes' own (same correlation matrix,
+    eigensolve, negative shift, norm factors and boundary lift, :1774-1885); only the export folder differs
+    (./ITHACAoutput/DEIM/<FunctionName>), which stays with the caller."""
+    return getModes(pod, snapshots, V, dim, nmodes, solver, norm, Sbc)
 
 
 def getModesMemoryEfficient(pod, block_source, m, V, dim, nmodes=0, solver="spectra", norm="L2", block=64, want_modes=True):

@@ -210,7 +210,7 @@ int ithaca_b200_destroy(ithaca_b200_t* h)
     if (h->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->nccl_comm);
     for (void* p : {(void*)h->dV, (void*)h->dS, (void*)h->dG, (void*)h->dWs, (void*)h->dQ, (void*)h->dW,
                     (void*)h->dEvals, (void*)h->dQr, (void*)h->dPhi, (void*)h->dNormPart, (void*)h->dNorm,
-                    h->dJobs, (void*)h->dFlags, h->wexp[0].p, h->wexp[1].p, (void*)h->dS2, (void*)h->dPhiTmp})
+                    h->dJobs, (void*)h->dFlags, h->wexp[0].p, h->wexp[1].p, (void*)h->dS2, (void*)h->dPhiTmp, h->volT.p})
         if (p) cudaFree(p);
     for (int i = 0; i < T_COUNT; i++) {
         cudaEventDestroy(h->timers[i].a);
@@ -333,6 +333,52 @@ int ithaca_b200_pod_gram(ithaca_b200_t* h, double* G_out)
     if (rc) return rc;
     tstart(h, T_GRAM);
     rc = gram_launch(h);
+    if (rc) return rc;
+    tstop(h, T_GRAM);
+    tstart(h, T_ALLREDUCE);
+    rc = allreduce_sum(h, h->dG, (size_t)h->m * h->m);
+    if (rc) return rc;
+    tstop(h, T_ALLREDUCE);
+    if (G_out)
+        IB_CUDA(h, cudaMemcpyAsync(G_out, h->dG, (size_t)h->m * h->m * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->have_gram = true;
+    h->have_eig = h->have_lift = false;
+    return IB200_OK;
+}
+
+// T[:, j] = S[:, j] * sqrt|Vs[:, j]| in place over the uploaded volume columns (pad rows -> 0)
+__global__ void __launch_bounds__(256)
+scale_by_sqrt_abs_kernel(const double* __restrict__ S, double* __restrict__ T, long long Nd, long long ld, int m)
+{
+    const long long n = ld * m;
+    for (long long i = blockIdx.x * 256LL + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
+        const long long k = i % ld;
+        T[i] = k < Nd ? S[i] * sqrt(fabs(T[i])) : 0.0;
+    }
+}
+
+int ithaca_b200_pod_gram_volumes(ithaca_b200_t* h, const double* const* vol_ptrs, double* G_out)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->dS || h->m <= 0 || h->block_mode) { set_error(h, "pod_gram_volumes: upload snapshots first"); return IB200_ERR_ARG; }
+    if (!vol_ptrs) { set_error(h, "pod_gram_volumes: null volume list"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    int rc = ensure_mats(h, h->m);
+    if (rc) return rc;
+    if ((rc = dev_ensure(h, h->volT, (size_t)h->ld * h->m * sizeof(double)))) return rc;
+    double* T = h->volT.as<double>();
+    tstart(h, T_UPLOAD);
+    for (int j = 0; j < h->m; j++) {
+        if (!vol_ptrs[j]) { set_error(h, "pod_gram_volumes: null volume pointer"); return IB200_ERR_ARG; }
+        IB_CUDA(h, cudaMemcpyAsync(T + (size_t)j * h->ld, vol_ptrs[j], (size_t)h->Nd * sizeof(double), cudaMemcpyDefault, h->stream));
+    }
+    tstop(h, T_UPLOAD);
+    tstart(h, T_GRAM);
+    scale_by_sqrt_abs_kernel<<<8 * h->num_sms, 256, 0, h->stream>>>(h->dS, T, h->Nd, h->ld, h->m);
+    IB_CUDA(h, cudaGetLastError());
+    h->launches += 1;
+    rc = atvb_launch(h, T, h->ld, h->m, T, h->ld, h->m, h->Nd, nullptr, 1, 1, h->dG, 1, 0x7fffffff, 0, h->m);
     if (rc) return rc;
     tstop(h, T_GRAM);
     tstart(h, T_ALLREDUCE);

@@ -17,6 +17,8 @@
 //   eigenvalue normalisation / cumulative sum: ITHACAPOD/ITHACAPOD.C:281-287
 //   getCoeffs   : ITHACAutilities/ITHACAcoeffsMass.C:348-388, :424-443
 //   Modes::project / reconstruct: Containers/Modes.C:228-290, :294-305
+//   getModesSVD : ITHACAPOD/ITHACAPOD.C:858-941               (JacobiSVD of diag(sqrt V) S)
+//   getModes with per-snapshot Volumes: ITHACAPOD/ITHACAPOD.C:1392-1541
 //
 // Used by: tests/ (checker), tests/golden/make_golden.py (fixture generator),
 // bench.py cpu_baseline / --impl reference (timed CPU baseline). Nothing else.
@@ -263,6 +265,103 @@ int podref_reconstruct(const double* modes, i64 Nd, int nmodes_avail, const doub
         if (clip) InField = (InField.array() < 0).select(0, InField);
         std::memcpy(out + (size_t)j * Nd, InField.data(), sizeof(double) * Nd);
     }
+    return 0;
+}
+
+// getModesSVD (ITHACAPOD.C:872-905): thin JacobiSVD of diag(sqrt(V)) * S; modes = diag(1/sqrt(V)) * U.leftCols(nmodes);
+// "eigenvalues" = ALL singular values / their sum, then the running sum.
+// sv_norm_out, cum_out: min(Nd, m) doubles; modes_out: Nd x nmodes col-major.
+int podref_getmodes_svd(const double* S, i64 Nc, int dim, int m, const double* Vc, int nmodes, double* sv_norm_out,
+                        double* cum_out, double* modes_out)
+{
+    const i64 Nd = Nc * dim;
+    Eigen::MatrixXd SnapMatrix = CMap(S, Nd, m);
+    Eigen::VectorXd V = mass_fv(Vc, Nc, dim);
+    Eigen::VectorXd V3dSqrt = V.array().sqrt();
+    Eigen::VectorXd V3dInv = V3dSqrt.array().cwiseInverse();
+    auto VMsqr = V3dSqrt.asDiagonal();
+    auto VMsqrInv = V3dInv.asDiagonal();
+    Eigen::MatrixXd SnapMatrix2 = VMsqr * SnapMatrix;
+    Eigen::JacobiSVD<Eigen::MatrixXd> svd(SnapMatrix2, Eigen::ComputeThinU | Eigen::ComputeThinV);
+    Eigen::VectorXd eigenValueseig;
+    Eigen::MatrixXd eigenVectoreig;
+    eigenValueseig = svd.singularValues().real();
+    eigenVectoreig = svd.matrixU().real();
+    Eigen::MatrixXd modesEig = VMsqrInv * eigenVectoreig;
+    for (int i = 0; i < nmodes; i++)
+        std::memcpy(modes_out + (size_t)i * Nd, modesEig.col(i).data(), sizeof(double) * Nd);
+    eigenValueseig = eigenValueseig / eigenValueseig.sum();
+    Eigen::VectorXd cumEigenValues(eigenValueseig);
+    for (int j = 1; j < cumEigenValues.size(); ++j)
+    {
+        cumEigenValues(j) += cumEigenValues(j - 1);
+    }
+    std::memcpy(sv_norm_out, eigenValueseig.data(), sizeof(double) * eigenValueseig.size());
+    std::memcpy(cum_out, cumEigenValues.data(), sizeof(double) * cumEigenValues.size());
+    return 0;
+}
+
+// getModes with one volume field per snapshot (moving meshes; ITHACAPOD.C:1392-1541):
+//   _corMatrix(i,j) = S_i^T diag(sqrt|V_i V_j|) S_j (:1425-1435), mirrored; eigensolve as getModes WITHOUT the negative
+//   shift; modesEig = (S Q) diag(lambda^-1/2) (:1481-1484); eigenvalues / sum of the KEPT ones (eigen solver: head(nmodes),
+//   :1476). Vs: Nd x m col-major (the reference multiplies V.col(i) and SnapMatrix.col(i) coefficient-wise, so the
+//   volume fields must have as many rows as the snapshots: scalar fields in practice).
+int podref_getmodes_volumes(const double* S, i64 Nd, int m, const double* Vs, int nmodes, int solver, double* G_out,
+                            double* evals_norm_out, double* cum_out, double* evecs_out, double* modes_out)
+{
+    CMap SnapMatrix(S, Nd, m);
+    CMap V(Vs, Nd, m);
+    Eigen::MatrixXd _corMatrix(m, m);
+    for (int i = 0; i < m; i++)
+    {
+        for (int j = 0; j <= i; j++)
+        {
+            Eigen::VectorXd Mij = (V.col(i).array() * V.col(j).array());
+            Mij = Mij.array().abs().sqrt();
+            _corMatrix(i, j) = SnapMatrix.col(i).transpose() * Mij.asDiagonal() * SnapMatrix.col(j);
+        }
+    }
+    for (int i = 1; i < m; i++)
+    {
+        for (int j = 0; j < i; j++)
+        {
+            _corMatrix(j, i) = _corMatrix(i, j);
+        }
+    }
+    Eigen::VectorXd eigenValueseig;
+    Eigen::MatrixXd eigenVectoreig;
+    int ncv = m;
+    Spectra::DenseSymMatProd<double> op(_corMatrix);
+    Eigen::SelfAdjointEigenSolver<Eigen::MatrixXd> esEg;
+    if (solver == 0)
+    {
+        Spectra::SymEigsSolver<Spectra::DenseSymMatProd<double>> es(op, nmodes, ncv);
+        es.init();
+        es.compute(Spectra::SortRule::LargestAlge);
+        if (es.info() != Spectra::CompInfo::Successful) return 1;
+        eigenVectoreig = es.eigenvectors().real();
+        eigenValueseig = es.eigenvalues().real();
+    }
+    else
+    {
+        esEg.compute(_corMatrix);
+        if (esEg.info() != Eigen::Success) return 1;
+        eigenVectoreig = esEg.eigenvectors().real().rowwise().reverse().leftCols(nmodes);
+        eigenValueseig = esEg.eigenvalues().real().reverse().head(nmodes);
+    }
+    Eigen::VectorXd eigenValueseigLam = eigenValueseig.real().array().cwiseInverse().sqrt();
+    Eigen::MatrixXd modesEig = (SnapMatrix * eigenVectoreig) * eigenValueseigLam.asDiagonal();
+    eigenValueseig = eigenValueseig / eigenValueseig.sum();
+    Eigen::VectorXd cumEigenValues(eigenValueseig);
+    for (int j = 1; j < cumEigenValues.size(); ++j)
+    {
+        cumEigenValues(j) += cumEigenValues(j - 1);
+    }
+    if (G_out) std::memcpy(G_out, _corMatrix.data(), sizeof(double) * m * m);
+    std::memcpy(evals_norm_out, eigenValueseig.data(), sizeof(double) * nmodes);
+    std::memcpy(cum_out, cumEigenValues.data(), sizeof(double) * nmodes);
+    if (evecs_out) std::memcpy(evecs_out, eigenVectoreig.data(), sizeof(double) * m * nmodes);
+    std::memcpy(modes_out, modesEig.data(), sizeof(double) * Nd * nmodes);
     return 0;
 }
 

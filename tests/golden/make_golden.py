@@ -20,6 +20,18 @@ CASES = [
 ]
 
 
+def variant_inputs():
+    """Inputs of the getModesSVD / per-snapshot-volume getModes fixture (pod_variants.npz)."""
+    Nc, dim, m, r = 1203, 3, 14, 4
+    S = synth.snapshots(Nc, dim, m, 2 * r, 105)
+    V = synth.volumes(Nc, 105)
+    Ss = synth.snapshots(Nc, 1, m, 2 * r, 106)
+    rng = np.random.default_rng(106)
+    Vs = np.asfortranarray(V[:, None] * (1.0 + 0.2 * rng.uniform(-1, 1, (Nc, m))))
+    Vs[::53, 2] *= -1.0
+    return Nc, dim, m, r, S, V, Ss, Vs
+
+
 def inputs(Nc, dim, m, r, seed, nbc):
     S = synth.snapshots(Nc, dim, m, 2 * r, seed)
     V = synth.volumes(Nc, seed)
@@ -42,3 +54,11 @@ if __name__ == "__main__":
             stride=stride, modes_bc=(out["modes_bc"] if nbc else np.zeros((0, r))),
             meta=np.array([Nc, dim, m, r, seed, nbc]), solver=solver, norm=norm)
         print("wrote", name, out["evals_norm"][:3])
+
+    Nc, dim, m, r, S, V, Ss, Vs = variant_inputs()
+    a = po.ref_getmodes_svd(S, V, dim, r)
+    b = po.ref_getmodes_volumes(Ss, Vs, r, "eigen")
+    np.savez_compressed(os.path.join(here, "pod_variants.npz"), svd_evals_norm=a["evals_norm"], svd_cum=a["cum"],
+                        svd_modes_sub=a["modes"][::9], vol_G=b["G"], vol_evals_norm=b["evals_norm"], vol_cum=b["cum"],
+                        vol_modes_sub=b["modes"][::3])
+    print("wrote variants", a["evals_norm"][:3], b["evals_norm"][:3])

@@ -280,3 +280,54 @@ def test_weighted_modes_match_oracle(pkg, pod, solver):
     assert rel_max(out["modes_bc"] * s, ref["modes_bc"]) <= 1e-8
     with pytest.raises(pkg.IthacaB200Error):
         pkg.getWeightedModes(pod, S, V, dim, m - 1, solver)
+
+
+def test_svd_modes_match_oracle(pkg, pod):
+    """getModesSVD (ITHACAPOD.C:858-941) through Gram + eigensolve + scaled lift against a direct thin SVD of
+    diag(sqrt V) S (numpy) and, when built, the reference's own JacobiSVD expression."""
+    Nc, dim, m, r = 2503, 3, 24, 6
+    S = synth.snapshots(Nc, dim, m, 2 * r, 77)
+    V = synth.volumes(Nc, 77)
+    out = pkg.getModesSVD(pod, S, V, dim, r)
+    refs = [po.getmodes_svd(S, V, dim, r)] + ([po.ref_getmodes_svd(S, V, dim, r)] if po.ref_available() else [])
+    for ref in refs:
+        assert len(out["evals_norm"]) == len(ref["evals_norm"]) == m
+        # leading singular values; the noise-floor ones (sigma ~ 1e-6 sigma_0) lose half the digits to the squaring
+        assert np.all(np.abs(out["evals_norm"][:r] - ref["evals_norm"][:r]) <= 1e-10 * ref["evals_norm"][:r])
+        assert np.abs(out["evals_norm"] - ref["evals_norm"]).max() <= 1e-9 * ref["evals_norm"][0]
+        assert modes_rel(out["modes"], ref["modes"]) <= 1e-8
+    with pytest.raises(pkg.IthacaB200Error):
+        pkg.getModesSVD(pod, S, V, dim, m + 1)
+
+
+@pytest.mark.parametrize("solver", ["spectra", "eigen"])
+def test_per_snapshot_volume_modes_match_oracle(pkg, pod, solver):
+    """getModes with one volume field per snapshot (moving meshes, ITHACAPOD.C:1392-1541): correlation matrix as one
+    contraction of the row-scaled snapshots, modes = (S Q) lambda^-1/2."""
+    Nc, m, r = 4001, 18, 5
+    S = synth.snapshots(Nc, 1, m, 2 * r, 88)
+    rng = np.random.default_rng(88)
+    V0 = synth.volumes(Nc, 88)
+    Vs = np.asfortranarray(V0[:, None] * (1.0 + 0.2 * rng.uniform(-1, 1, (Nc, m))))
+    Vs[::97, 3] *= -1.0   # the reference takes |V_i V_j|
+    Sbc = np.asfortranarray(rng.standard_normal((17, m)))
+    out = pkg.getModesVolumes(pod, S, Vs, r, solver, Sbc)
+    refs = [po.getmodes_volumes(S, Vs, r, solver)] + ([po.ref_getmodes_volumes(S, Vs, r, solver)] if po.ref_available() else [])
+    for ref in refs:
+        assert rel_max(out["G"], ref["G"]) <= 1e-13
+        assert np.all(np.abs(out["evals_norm"] - ref["evals_norm"]) <= 1e-10 * ref["evals_norm"])
+        assert modes_rel(out["modes"], ref["modes"]) <= 1e-8
+    ref = refs[0]
+    s = np.sign(np.einsum("ij,ij->j", out["modes"], ref["modes"]))
+    assert rel_max(out["modes_bc"] * s, (Sbc @ ref["evecs"]) / np.sqrt(ref["evals"])) <= 1e-8
+
+
+def test_deim_modes_are_getmodes(pkg, pod):
+    """DEIMmodes (ITHACAPOD.C:1739-1937) shares getModes' arithmetic line for line."""
+    Nc, dim, m, r = 1501, 1, 15, 4
+    S = synth.snapshots(Nc, dim, m, 2 * r, 91)
+    V = synth.volumes(Nc, 91)
+    out = pkg.DEIMmodes(pod, S, V, dim, r, "eigen", "Frobenius")
+    ref = po.getmodes(S, V, dim, r, "eigen", "Frobenius")
+    assert np.all(np.abs(out["evals_norm"][:r] - ref["evals_norm"][:r]) <= 1e-10 * ref["evals_norm"][:r])
+    assert modes_rel(out["modes"], ref["modes"]) <= 1e-8
