@@ -325,6 +325,30 @@ int ithaca_b200_mesh_set_owned(ithaca_b200_t* h, int64_t nOwned);
  * [3]=grad(p), [4]=div(U), [5]=contraction, [6]=per-face records of the fused C. */
 int ithaca_b200_proj_timings(ithaca_b200_t* h, double* out, int n);
 
+/* ---- on-disk formats of the reduced operators (host code, no GPU needed) -------------
+ * The reference caches every projected operator under ./ITHACAoutput/Matrices/ and reads it back instead of
+ * recomputing (steadyNS.C:384-467); these write the ABI's output buffers in exactly those formats so that an
+ * unmodified ITHACA-FV (and its python tooling) reads what this library computed. Errors: last_error(NULL).
+ *   save/read_dense_matrix  ITHACAstream::SaveDenseMatrix / ReadDenseMatrix (ITHACAstream.H:722-762): rows, cols as
+ *                           Eigen::Index (int64), then rows*cols column-major doubles. read: A may be NULL (sizes only).
+ *   save/read_dense_tensor  SaveDenseTensor / ReadDenseTensor (ITHACAstream.H:765-809): Eigen::DSizes<Index,3>
+ *                           (3 x int64), then the data with the FIRST index fastest.
+ *   save_npy                cnpy::save of an Eigen matrix / rank-3 tensor (cnpy.C:524-568, header cnpy.H:454-488):
+ *                           NPY 1.0, '<f8', C order; `data` is the Eigen object's storage (first index fastest),
+ *                           ndim = 1, 2 or 3.
+ *   export_matrix/tensor    ITHACAstream::exportMatrix / exportTensor (ITHACAstream.C:54-147, :263-358): the text
+ *                           files <folder>/<name>_mat.py | .m | .txt ("python": setprecision(10) np.array literal,
+ *                           "matlab", "eigen": precision 20, one file <name><i>_mat.txt per slice T(i,:,:) for tensors). */
+enum { IB200_EXPORT_PYTHON = 0, IB200_EXPORT_MATLAB = 1, IB200_EXPORT_EIGEN = 2 };
+int ithaca_b200_save_dense_matrix(const char* path, const double* A, int64_t rows, int64_t cols);
+int ithaca_b200_read_dense_matrix(const char* path, int64_t* rows, int64_t* cols, double* A, int64_t capacity);
+int ithaca_b200_save_dense_tensor(const char* path, const double* T, int64_t d0, int64_t d1, int64_t d2);
+int ithaca_b200_read_dense_tensor(const char* path, int64_t* dims3, double* T, int64_t capacity);
+int ithaca_b200_save_npy(const char* path, const double* data, int ndim, const int64_t* dims);
+int ithaca_b200_export_matrix(const char* folder, const char* name, int type, const double* A, int64_t rows, int64_t cols);
+int ithaca_b200_export_tensor(const char* folder, const char* name, int type, const double* T, int64_t d0, int64_t d1,
+                              int64_t d2);
+
 /* ---- measurement helpers -------------------------------------------------------------------- */
 /* Register-resident DMMA.8x8x4 (mma.sync.m8n8k4.f64) issue-rate microbenchmark on `device`:
  * the measured FP64 tensor peak used as the Gram kernel's roofline denominator. */

@@ -32,6 +32,8 @@ SYMBOLS = [
     "ithaca_b200_partition_create", "ithaca_b200_partition_destroy", "ithaca_b200_partition_sizes",
     "ithaca_b200_partition_addressing", "ithaca_b200_partition_gather", "ithaca_b200_mesh_upload_shard",
     "ithaca_b200_mesh_set_owned", "ithaca_b200_mesh_renumbering",
+    "ithaca_b200_save_dense_matrix", "ithaca_b200_read_dense_matrix", "ithaca_b200_save_dense_tensor",
+    "ithaca_b200_read_dense_tensor", "ithaca_b200_save_npy", "ithaca_b200_export_matrix", "ithaca_b200_export_tensor",
 ]
 
 _lib = None
@@ -101,6 +103,14 @@ def lib():
         L.ithaca_b200_partition_gather.argtypes = [P, I, I, P, P]
         L.ithaca_b200_mesh_upload_shard.argtypes = [P, P] + [P] * 10
         L.ithaca_b200_mesh_set_owned.argtypes = [P, L64]
+        C = ctypes.c_char_p
+        L.ithaca_b200_save_dense_matrix.argtypes = [C, P, L64, L64]
+        L.ithaca_b200_read_dense_matrix.argtypes = [C, ctypes.POINTER(L64), ctypes.POINTER(L64), P, L64]
+        L.ithaca_b200_save_dense_tensor.argtypes = [C, P, L64, L64, L64]
+        L.ithaca_b200_read_dense_tensor.argtypes = [C, P, P, L64]
+        L.ithaca_b200_save_npy.argtypes = [C, P, I, P]
+        L.ithaca_b200_export_matrix.argtypes = [C, C, I, P, L64, L64]
+        L.ithaca_b200_export_tensor.argtypes = [C, C, I, P, L64, L64, L64]
         _lib = L
     return _lib
 
@@ -133,6 +143,77 @@ def dmma_peak(device=0):
     if rc:
         raise IthacaB200Error("dmma_peak failed (no sm_100 device?)")
     return v.value
+
+
+def _io_chk(rc):
+    if rc:
+        raise IthacaB200Error(lib().ithaca_b200_last_error(None).decode())
+
+
+def _eigen_storage(A):
+    """The bytes an Eigen::MatrixXd / Eigen::Tensor<double,3> of this shape holds: first index fastest."""
+    return np.asfortranarray(np.asarray(A, dtype=np.float64))
+
+
+def SaveDenseMatrix(A, folder, name):
+    """ITHACAstream::SaveDenseMatrix (ITHACAstream.H:722-737): folder + name, folder created."""
+    A = _eigen_storage(np.atleast_2d(A))
+    os.makedirs(folder, exist_ok=True)
+    _io_chk(lib().ithaca_b200_save_dense_matrix((folder + name).encode(), A.ctypes.data, A.shape[0], A.shape[1]))
+
+
+def ReadDenseMatrix(folder, name):
+    """ITHACAstream::ReadDenseMatrix (ITHACAstream.H:739-762)."""
+    path = (folder + name).encode()
+    r, c = ctypes.c_int64(), ctypes.c_int64()
+    _io_chk(lib().ithaca_b200_read_dense_matrix(path, ctypes.byref(r), ctypes.byref(c), None, 0))
+    A = np.zeros((r.value, c.value), order="F")
+    _io_chk(lib().ithaca_b200_read_dense_matrix(path, ctypes.byref(r), ctypes.byref(c), A.ctypes.data, A.size))
+    return A
+
+
+def SaveDenseTensor(T, folder, name):
+    """ITHACAstream::SaveDenseTensor (ITHACAstream.H:765-784); like the reference it does not create the folder."""
+    T = _eigen_storage(T)
+    assert T.ndim == 3
+    _io_chk(lib().ithaca_b200_save_dense_tensor((folder + name).encode(), T.ctypes.data, *T.shape))
+
+
+def ReadDenseTensor(folder, name):
+    """ITHACAstream::ReadDenseTensor (ITHACAstream.H:786-809)."""
+    path = (folder + name).encode()
+    d = np.zeros(3, dtype=np.int64)
+    _io_chk(lib().ithaca_b200_read_dense_tensor(path, d.ctypes.data, None, 0))
+    T = np.zeros(tuple(int(x) for x in d), order="F")
+    _io_chk(lib().ithaca_b200_read_dense_tensor(path, d.ctypes.data, T.ctypes.data, T.size))
+    return T
+
+
+def save_npy(A, fname):
+    """cnpy::save of an Eigen vector / matrix / rank-3 tensor (cnpy.C:524-568)."""
+    A = _eigen_storage(A)
+    dims = np.array(A.shape, dtype=np.int64)
+    _io_chk(lib().ithaca_b200_save_npy(fname.encode(), A.ctypes.data, A.ndim, dims.ctypes.data))
+
+
+_EXPORT = {"python": 0, "matlab": 1, "eigen": 2}
+
+
+def exportMatrix(A, name, type, folder):
+    """ITHACAstream::exportMatrix (ITHACAstream.C:54-147)."""
+    if type not in _EXPORT:
+        raise IthacaB200Error('The extension "%s" was not implemented. Check the list of possible extensions.' % type)
+    A = _eigen_storage(np.atleast_2d(A))
+    _io_chk(lib().ithaca_b200_export_matrix(folder.encode(), name.encode(), _EXPORT[type], A.ctypes.data, *A.shape))
+
+
+def exportTensor(T, name, type, folder):
+    """ITHACAstream::exportTensor (ITHACAstream.C:263-358)."""
+    if type not in _EXPORT:
+        raise IthacaB200Error('The extension "%s" was not implemented. Check the list of possible extensions.' % type)
+    T = _eigen_storage(T)
+    assert T.ndim == 3
+    _io_chk(lib().ithaca_b200_export_tensor(folder.encode(), name.encode(), _EXPORT[type], T.ctypes.data, *T.shape))
 
 
 def _ptr(x):
