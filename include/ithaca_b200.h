@@ -176,7 +176,8 @@ int ithaca_b200_pod_block_lift_finish(ithaca_b200_t* h, int r, int norm_kind, do
 /* ---- Galerkin projection: steadyNS::projectSUP term builders ---------------------------------------
  * (src/ITHACA_FOMPROBLEMS/steadyNS/steadyNS.C:556-707 calls :883-1137; inherited by unsteadyNS,
  *  src/ITHACA_FOMPROBLEMS/unsteadyNS/unsteadyNS.H:61). Scheme set: Gauss linear (grad, div, interpolate),
- *  Gauss linear corrected | uncorrected (laplacian). */
+ *  Gauss linear corrected | uncorrected (laplacian); ithaca_b200_mesh_set_schemes adds the cellMDLimited gradient
+ *  and the limited snGrad. */
 
 /* Mesh addressing and geometry exactly as OpenFOAM holds them (32-bit labels):
  *   owner[nInt+nBnd], neighbour[nInt]      mesh.owner(), mesh.neighbour() (faces in OpenFOAM order: internal, then patches)
@@ -192,6 +193,23 @@ int ithaca_b200_mesh_upload(ithaca_b200_t* h, int64_t nCells, int64_t nIntFaces,
                             const int32_t* owner, const int32_t* neighbour, const double* Sf, const double* magSf,
                             const double* weights, const double* nonOrthDeltaCoeffs, const double* bndDeltaCoeffs,
                             const double* nonOrthCorrVec, const double* V, const unsigned char* bndMask);
+
+/* Scheme selection beyond "Gauss linear" for the mesh just uploaded: the set that
+ * tutorials/CFD/04unsteadyNS/system/fvSchemes ships ("gradSchemes default cellMDLimited Gauss linear 0.5",
+ * "laplacianSchemes default Gauss linear limited 1.0", "snGradSchemes default limited 1").
+ *   grad_limit_k  in (0,1]: every fvc::grad on the path -- grad(P_j) of K, D, G, BC3 and the divergent background term,
+ *                 grad(U_j) inside the non-orthogonal correction of fvc::laplacian (B, BC1, BP) and inside curl(U_j) of
+ *                 BC3 -- is the cellMDLimited gradient (OpenFOAM limitedGradSchemes/cellMDLimitedGrad): the Gauss linear
+ *                 cell gradient clipped face by face, in OpenFOAM's face order, so that the value extrapolated to each
+ *                 face centre stays within the min/max of the cell's neighbourhood (widened by 1/k - 1). 0 (or < SMALL,
+ *                 as in OpenFOAM): plain Gauss linear. k > 1 is refused (OpenFOAM: FatalIOError).
+ *   sngrad_psi    in [0,1]: the laplacian's snGrad is "limited psi" (limitedSnGrad): the non-orthogonal correction is scaled
+ *                 per face by min(psi |snGrad_uncorrected| / ((1 - psi) |correction| + SMALL), 1). Negative: "corrected"
+ *                 (or "uncorrected" when mesh_upload got nonOrthCorrVec = NULL). Needs nonOrthCorrVec.
+ *   C[3*nCells], Cf[3*(nInt+nBnd)]   mesh.C() internal field and mesh.Cf() (internal then boundary), in the order of the
+ *                 uploaded mesh (a shard's local order after mesh_upload_shard); only read when grad_limit_k > 0.
+ * mesh_upload / mesh_upload_shard reset both to off. Host or device pointers. */
+int ithaca_b200_mesh_set_schemes(ithaca_b200_t* h, double grad_limit_k, double sngrad_psi, const double* C, const double* Cf);
 
 /* The device-built cell->face CSR, for the bit-exact addressing check: off[nCells+1]; ent[2*nInt+nBnd] = +(f+1) when
  * the cell owns face f, -(f+1) when it is its neighbour, ascending face index per cell (primitiveMesh::cells() order);

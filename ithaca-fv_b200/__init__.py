@@ -32,6 +32,7 @@ SYMBOLS = [
     "ithaca_b200_partition_create", "ithaca_b200_partition_destroy", "ithaca_b200_partition_sizes",
     "ithaca_b200_partition_addressing", "ithaca_b200_partition_gather", "ithaca_b200_mesh_upload_shard",
     "ithaca_b200_mesh_set_owned", "ithaca_b200_mesh_renumbering",
+    "ithaca_b200_mesh_set_schemes",
     "ithaca_b200_save_dense_matrix", "ithaca_b200_read_dense_matrix", "ithaca_b200_save_dense_tensor",
     "ithaca_b200_read_dense_tensor", "ithaca_b200_save_npy", "ithaca_b200_export_matrix", "ithaca_b200_export_tensor",
 ]
@@ -103,6 +104,7 @@ def lib():
         L.ithaca_b200_partition_gather.argtypes = [P, I, I, P, P]
         L.ithaca_b200_mesh_upload_shard.argtypes = [P, P] + [P] * 10
         L.ithaca_b200_mesh_set_owned.argtypes = [P, L64]
+        L.ithaca_b200_mesh_set_schemes.argtypes = [P, D, D, P, P]
         C = ctypes.c_char_p
         L.ithaca_b200_save_dense_matrix.argtypes = [C, P, L64, L64]
         L.ithaca_b200_read_dense_matrix.argtypes = [C, ctypes.POINTER(L64), ctypes.POINTER(L64), P, L64]
@@ -498,6 +500,13 @@ class Projector:
         self.pod._chk(self.L.ithaca_b200_mesh_upload(
             self.h, self.nCells, self.nInt, self.nBnd, _ptr(k["owner"]), _ptr(k["nei"]), _ptr(k["Sf"]), _ptr(k["magSf"]),
             _ptr(k["w"]), _ptr(k["dc"]), _ptr(k["dcB"]), _ptr(k["corr"]), _ptr(k["V"]), _ptr(k["bmask"])))
+
+    def set_schemes(self, grad_limit_k=0.0, sngrad_psi=-1.0, C=None, Cf=None):
+        """fvSchemes beyond 'Gauss linear': gradSchemes 'cellMDLimited Gauss linear k', snGrad 'limited psi'
+        (tutorials/CFD/04unsteadyNS/system/fvSchemes). C, Cf: mesh.C(), mesh.Cf() in the uploaded mesh's order."""
+        c = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.float64)
+        C, Cf = c(C), c(Cf)
+        self.pod._chk(self.L.ithaca_b200_mesh_set_schemes(self.h, float(grad_limit_k), float(sngrad_psi), _ptr(C), _ptr(Cf)))
 
     def set_mesh_shard(self, mesh, part, corrected=True):
         """Upload `part`'s shard of the GLOBAL mesh; set_basis then takes shard fields (part.gather) and project()

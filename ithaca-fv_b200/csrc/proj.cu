@@ -42,6 +42,10 @@ struct MeshDev {
     const double *Sf, *magSf, *w, *dc, *dcB, *corr, *V;
     const unsigned char* bmask;
     const int *off, *ent, *other;
+    // scheme selection beyond "Gauss linear" (ithaca_b200_mesh_set_schemes); limK <= 0 / snPsi < 0: off
+    const int *entL, *otherL;     // the CSR entries of each cell in the CALLER's face order (the limiter is order dependent)
+    const double *Cc, *Cf;        // cell / face centres, internal order
+    double limK, snPsi;
 };
 
 struct ProjState {
@@ -54,6 +58,8 @@ struct ProjState {
     DevBuf Vw, cmask;   // shard: integration weights (V on owned cells, 0 on halo cells) and owned mask, internal order
     long long nOwned = 0;   // == nCells unless mesh_set_owned marked halo cells
     DevBuf fperm;   // original index of the internal face at each new position (int, nInt)
+    DevBuf entL, otherL, Cc, Cf;   // cellMDLimited gradient limiter (mesh_set_schemes)
+    double limK = 0.0, snPsi = -1.0;
     DevBuf stage;   // one field in the caller's order (upload / fvc_eval staging)
     int nU = 0, nP = 0;
     long long ldU = 0, ldUb = 0, ldP = 0, ldPb = 0, ldF = 0;
@@ -97,7 +103,7 @@ void proj_destroy(ithaca_b200* h)
     if (!s) return;
     for (DevBuf* b : {&s->owner, &s->neigh, &s->Sf, &s->magSf, &s->w, &s->dc, &s->dcB, &s->corr, &s->V, &s->bmask,
                       &s->off, &s->ent, &s->other, &s->cnt, &s->blocksum, &s->U, &s->Ub, &s->P, &s->Pb, &s->flux,
-                      &s->owner0, &s->neigh0, &s->off0, &s->ent0, &s->other0, &s->perm, &s->fperm, &s->stage, &s->Vw, &s->cmask, &s->Tcm, &s->Lcm, &s->gradP, &s->bndA, &s->bndB,
+                      &s->owner0, &s->neigh0, &s->off0, &s->ent0, &s->other0, &s->entL, &s->otherL, &s->Cc, &s->Cf, &s->perm, &s->fperm, &s->stage, &s->Vw, &s->cmask, &s->Tcm, &s->Lcm, &s->gradP, &s->bndA, &s->bndB,
                       &s->work, &s->T, &s->out, &s->conv.Ucm, &s->conv.Ubcm, &s->conv.Dcm, &s->conv.Aj, &s->conv.Bk, &s->conv.Dd,
                       &s->conv.ws, &s->conv.chunks})
         if (b->p) cudaFree(b->p);
@@ -115,6 +121,8 @@ static MeshDev mesh_dev(const ProjState* s)
     m.corr = s->corrected ? s->corr.as<double>() : nullptr;
     m.V = s->V.as<double>(); m.bmask = s->bmask.as<unsigned char>();
     m.off = s->off.as<int>(); m.ent = s->ent.as<int>(); m.other = s->other.as<int>();
+    m.entL = s->entL.as<int>(); m.otherL = s->otherL.as<int>(); m.Cc = s->Cc.as<double>(); m.Cf = s->Cf.as<double>();
+    m.limK = s->limK; m.snPsi = s->corrected ? s->snPsi : -1.0;
     return m;
 }
 
@@ -271,6 +279,87 @@ __global__ void unpermute_faces_kernel(const double* __restrict__ in, const int*
 {
     for (long long f = blockIdx.x * (long long)blockDim.x + threadIdx.x; f < nF; f += (long long)gridDim.x * blockDim.x)
         out[(f < nInt) ? fperm[f] : f] = in[f];
+}
+
+// each cell's CSR segment re-sorted by the CALLER's face index (internal face f sat at fperm[f] before the renumbering)
+__global__ void csr_sort_caller_order_kernel(const int* __restrict__ off, long long nCells, const int* __restrict__ fperm, long long nInt,
+                                             int* __restrict__ ent, int* __restrict__ other)
+{
+    const long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (c >= nCells) return;
+    const int a = off[c], b = off[c + 1];
+    auto key = [&](int e) { const int f = abs(e) - 1; return f < nInt ? fperm[f] : f; };
+    for (int i = a + 1; i < b; i++) {
+        const int e = ent[i], o = other[i], k = key(e);
+        int j = i - 1;
+        while (j >= a && key(ent[j]) > k) {
+            ent[j + 1] = ent[j];
+            other[j + 1] = other[j];
+            j--;
+        }
+        ent[j + 1] = e;
+        other[j + 1] = o;
+    }
+}
+// face centres into the internal face order
+__global__ void permute_face_vectors_kernel(const double* __restrict__ in, const int* __restrict__ fperm, long long nInt, long long nF,
+                                            double* __restrict__ out)
+{
+    for (long long f = blockIdx.x * (long long)blockDim.x + threadIdx.x; f < nF; f += (long long)gridDim.x * blockDim.x) {
+        const long long g = (f < nInt) ? fperm[f] : f;
+        out[3 * f] = in[3 * g]; out[3 * f + 1] = in[3 * g + 1]; out[3 * f + 2] = in[3 * g + 2];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// gradSchemes "cellMDLimited Gauss linear k" (tutorials/CFD/04unsteadyNS/system/fvSchemes; OpenFOAM
+// limitedGradSchemes/cellMDLimitedGrad: calcGrad + limitFaceCmpt). One scalar component of one cell: bounds = max/min
+// of the cell's value and its face neighbours' (boundary faces: the patch value) minus the cell value, widened by
+// (1/k - 1)(max - min) for k < 1; then the gradient is clipped face by face along dcf = Cf - C, in the CALLER's face
+// order (OpenFOAM's loop: internal faces ascending, then boundary faces) -- the clipping is order dependent, so the
+// renumbered CSR order of the summation kernels cannot be used here.
+// ------------------------------------------------------------------------------------------------
+template <class NbVal, class BndVal>
+__device__ __forceinline__ void md_limit(const MeshDev& m, long long c, double vc, NbVal nbval, BndVal bndval, double& gx, double& gy,
+                                         double& gz)
+{
+    const int e0 = m.off[c], e1 = m.off[c + 1];
+    double mx = vc, mn = vc;
+    for (int e = e0; e < e1; e++) {
+        const int ot = m.otherL[e];
+        double v;
+        if (ot >= 0) v = nbval(ot);
+        else {
+            const long long b = -(long long)ot - 1;
+            if (!m.bmask[b]) continue;
+            v = bndval(b);
+        }
+        mx = fmax(mx, v);
+        mn = fmin(mn, v);
+    }
+    mx -= vc;
+    mn -= vc;
+    if (m.limK < 1.0) {
+        const double dd = (1.0 / m.limK - 1.0) * (mx - mn);
+        mx += dd;
+        mn -= dd;
+    }
+    const double cx = m.Cc[3 * c], cy = m.Cc[3 * c + 1], cz = m.Cc[3 * c + 2];
+    for (int e = e0; e < e1; e++) {
+        const int ot = m.otherL[e];
+        if (ot < 0 && !m.bmask[-(long long)ot - 1]) continue;
+        const long long f = abs(m.entL[e]) - 1;
+        const double dx = m.Cf[3 * f] - cx, dy = m.Cf[3 * f + 1] - cy, dz = m.Cf[3 * f + 2] - cz;
+        const double ex = dx * gx + dy * gy + dz * gz;
+        double sft;
+        if (ex > mx) sft = mx - ex;
+        else if (ex < mn) sft = mn - ex;
+        else continue;
+        const double msq = dx * dx + dy * dy + dz * dz;
+        gx = gx + dx * sft / msq;
+        gy = gy + dy * sft / msq;
+        gz = gz + dz * sft / msq;
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -452,9 +541,16 @@ grad_scalar_kernel(MeshDev m, const double* __restrict__ P, long long ldP, const
     const double V = m.V[c];
 #pragma unroll
     for (int jj = 0; jj < FB; jj++)
-        if (j0 + jj < np)
-#pragma unroll
-            for (int d = 0; d < 3; d++) out[(size_t)(j0 + jj) * ldo + 3 * c + d] = acc[jj][d] / V;
+        if (j0 + jj < np) {
+            double g0 = acc[jj][0] / V, g1 = acc[jj][1] / V, g2 = acc[jj][2] / V;
+            if (m.limK > 0.0) {
+                const double* p = P + (size_t)(j0 + jj) * ldP;
+                const double* pb = Pb + (size_t)(j0 + jj) * ldPb;
+                md_limit(m, c, pc[jj], [&](int o) { return p[o]; }, [&](long long b) { return pb[b]; }, g0, g1, g2);
+            }
+            double* o = out + (size_t)(j0 + jj) * ldo + 3 * c;
+            o[0] = g0; o[1] = g1; o[2] = g2;
+        }
 }
 
 // Adjoint of `fvc::div` with owner-extrapolated boundary values: int P_i div(A) = sum_c V_c A[c] . t_i[c] for every vector
@@ -552,6 +648,17 @@ grad_vec_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const do
         }
     }
     const double V = m.V[c];
+#pragma unroll
+    for (int i = 0; i < 3; i++)
+#pragma unroll
+        for (int d = 0; d < 3; d++) acc[i][d] /= V;
+    if (m.limK > 0.0) {
+        const double* ub = Ub + (size_t)j * ldUb;
+#pragma unroll
+        for (int d = 0; d < 3; d++)   // component d: its gradient is column d of the tensor
+            md_limit(m, c, uc[d], [&](int o) { return u[3 * (size_t)o + d]; }, [&](long long b) { return ub[3 * b + d]; }, acc[0][d],
+                     acc[1][d], acc[2][d]);
+    }
     // component-major within a field, T[j][3i+d][c] (ldc = ldT/9 cells per component): consecutive cells of a warp
     // read and write consecutive doubles (the 72-byte cell-major records cost 3-4x the L1 sector accesses)
     const long long ldc = ldT / 9;
@@ -559,7 +666,7 @@ grad_vec_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const do
 #pragma unroll
     for (int i = 0; i < 3; i++)
 #pragma unroll
-        for (int d = 0; d < 3; d++) t[(3 * i + d) * ldc] = acc[i][d] / V;
+        for (int d = 0; d < 3; d++) t[(3 * i + d) * ldc] = acc[i][d];
 }
 
 // K7b: out_j = fvc::laplacian(1, U_j) = surfaceIntegrate(|Sf| snGrad(U_j)); snGrad = dc (U[n]-U[o])
@@ -604,10 +711,24 @@ laplacian_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const d
                     }
                 }
             }
+            double snu[3];
 #pragma unroll
             for (int d = 0; d < 3; d++) {
                 const double x = u[3 * (size_t)ot + d];
-                double sn = own ? dc * (x - uc[d]) : dc * (uc[d] - x);
+                snu[d] = own ? dc * (x - uc[d]) : dc * (uc[d] - x);
+            }
+            if (t && m.snPsi >= 0.0) {
+                // snGrad "limited psi" (limitedSnGrad::correction): limiter = min(psi |snGrad_unc| / ((1-psi) |corr| + SMALL), 1);
+                // both magnitudes are the same seen from either side of the face
+                const double a = sqrt(snu[0] * snu[0] + snu[1] * snu[1] + snu[2] * snu[2]);
+                const double cm = sqrt(cr[0] * cr[0] + cr[1] * cr[1] + cr[2] * cr[2]);
+                const double lim = fmin(m.snPsi * a / ((1.0 - m.snPsi) * cm + 1e-15), 1.0);
+#pragma unroll
+                for (int d = 0; d < 3; d++) cr[d] = lim * cr[d];
+            }
+#pragma unroll
+            for (int d = 0; d < 3; d++) {
+                double sn = snu[d];
                 if (t) sn += cr[d];
                 const double v = ms * sn;
                 acc[d] += own ? v : -v;
@@ -806,6 +927,13 @@ bnd_curl_kernel(MeshDev m, const unsigned char* __restrict__ cmask, const double
     for (int i = 0; i < 3; i++)
 #pragma unroll
         for (int d = 0; d < 3; d++) g[i][d] /= V;
+    if (m.limK > 0.0) {
+        const double* ubj = Ub + (size_t)j * ldUb;
+#pragma unroll
+        for (int d = 0; d < 3; d++)
+            md_limit(m, c, uc[d], [&](int o) { return u[3 * (size_t)o + d]; }, [&](long long b) { return ubj[3 * b + d]; }, g[0][d],
+                     g[1][d], g[2][d]);
+    }
     const double ms = m.magSf[f0];
     const double n[3] = {m.Sf[3 * f0] / ms, m.Sf[3 * f0 + 1] / ms, m.Sf[3 * f0 + 2] / ms};
     const double* ub = Ub + (size_t)j * ldUb + 3 * b0;
@@ -864,6 +992,10 @@ bnd_ncross_gradp_kernel(MeshDev m, const unsigned char* __restrict__ cmask, cons
     const double V = m.V[c];
 #pragma unroll
     for (int d = 0; d < 3; d++) g[d] /= V;
+    if (m.limK > 0.0) {
+        const double* pbj = Pb + (size_t)j * ldPb;
+        md_limit(m, c, pc, [&](int o) { return p[o]; }, [&](long long b) { return pbj[b]; }, g[0], g[1], g[2]);
+    }
     const double ms = m.magSf[f0];
     const double n[3] = {m.Sf[3 * f0] / ms, m.Sf[3 * f0 + 1] / ms, m.Sf[3 * f0 + 2] / ms};
     const double sn = m.dcB[b0] * (Pb[(size_t)j * ldPb + b0] - pc);
@@ -1142,7 +1274,7 @@ static int run_laplacians(ithaca_b200* h, ProjState* s, double* out)
         size_t have = s->conv.Ucm.cap + s->conv.Ubcm.cap + s->Tcm.cap + s->Lcm.cap, fr = 0, tot = 0;
         cudaMemGetInfo(&fr, &tot);
         const char* ev = getenv("ITHACA_B200_LAP");
-        if (ev && strcmp(ev, "cm") == 0 && need <= have + fr / 2) {
+        if (ev && strcmp(ev, "cm") == 0 && need <= have + fr / 2 && !(s->limK > 0.0) && s->snPsi < 0.0) {
             int rc;
             if ((rc = ensure(h, s->conv.Ucm, (size_t)s->nCells * 3 * per)) ||
                 (rc = ensure(h, s->conv.Ubcm, (size_t)std::max<long long>(s->nBnd, 1) * 3 * per)) ||
@@ -1306,6 +1438,51 @@ int ithaca_b200_mesh_upload(ithaca_b200_t* h, int64_t nCells, int64_t nIntFaces,
     s->have_mesh = true;
     s->nOwned = nCells;
     s->nU = s->nP = 0;
+    s->limK = 0.0;     // a new mesh starts with the "Gauss linear" / "corrected" scheme set
+    s->snPsi = -1.0;
+    return IB200_OK;
+}
+
+int ithaca_b200_mesh_set_schemes(ithaca_b200_t* h, double grad_limit_k, double sngrad_psi, const double* C, const double* Cf)
+{
+    if (!h) return IB200_ERR_ARG;
+    ProjState* s = h->proj;
+    PROJ_REQUIRE(s && s->have_mesh, "mesh_set_schemes: no mesh uploaded");
+    PROJ_REQUIRE(!(grad_limit_k > 1.0), "mesh_set_schemes: cellMDLimited coefficient k = " + std::to_string(grad_limit_k) + " should be >= 0 and <= 1");
+    PROJ_REQUIRE(!(sngrad_psi > 1.0), "mesh_set_schemes: limited snGrad coefficient = " + std::to_string(sngrad_psi) + " should be >= 0 and <= 1");
+    PROJ_REQUIRE(!(sngrad_psi >= 0.0) || s->corrected, "mesh_set_schemes: limited snGrad needs the nonOrthCorrectionVectors (mesh_upload got NULL)");
+    // OpenFOAM returns the unlimited gradient when k < SMALL (cellMDLimitedGrads.C)
+    const bool lim = grad_limit_k >= 1e-15;
+    PROJ_REQUIRE(!lim || (C && Cf), "mesh_set_schemes: the cellMDLimited gradient needs mesh.C() and mesh.Cf()");
+    cudaSetDevice(h->device);
+    if (lim) {
+        const long long nC = s->nCells, nF = s->nInt + s->nBnd, nnz = 2 * s->nInt + s->nBnd;
+        int rc;
+        DevBuf C0, Cf0;
+        auto drop = [&]() { for (DevBuf* b : {&C0, &Cf0}) if (b->p) { cudaFree(b->p); b->p = nullptr; } };
+        if ((rc = upload(h, C0, C, 3 * nC * sizeof(double))) || (rc = upload(h, Cf0, Cf, 3 * nF * sizeof(double))) ||
+            (rc = ensure(h, s->Cc, 3 * nC * sizeof(double))) || (rc = ensure(h, s->Cf, 3 * std::max<long long>(nF, 1) * sizeof(double))) ||
+            (rc = ensure(h, s->entL, std::max<long long>(nnz, 1) * sizeof(int))) ||
+            (rc = ensure(h, s->otherL, std::max<long long>(nnz, 1) * sizeof(int)))) {
+            drop();
+            return rc;
+        }
+        const int cg = (int)std::min<long long>((nC + 255) / 256, 64LL * h->num_sms);
+        const int fg = (int)std::min<long long>((nF + 255) / 256, 64LL * h->num_sms);
+        permute_cells_kernel<<<std::max(cg, 1), 256, 0, h->stream>>>(C0.as<double>(), s->perm.as<int>(), nC, 3, s->Cc.as<double>());
+        permute_face_vectors_kernel<<<std::max(fg, 1), 256, 0, h->stream>>>(Cf0.as<double>(), s->fperm.as<int>(), s->nInt, nF, s->Cf.as<double>());
+        cudaMemcpyAsync(s->entL.p, s->ent.p, nnz * sizeof(int), cudaMemcpyDeviceToDevice, h->stream);
+        cudaMemcpyAsync(s->otherL.p, s->other.p, nnz * sizeof(int), cudaMemcpyDeviceToDevice, h->stream);
+        csr_sort_caller_order_kernel<<<(unsigned)((nC + 255) / 256), 256, 0, h->stream>>>(s->off.as<int>(), nC, s->fperm.as<int>(), s->nInt,
+                                                                                         s->entL.as<int>(), s->otherL.as<int>());
+        h->launches += 3;
+        cudaError_t e = cudaStreamSynchronize(h->stream);
+        drop();
+        IB_CUDA(h, e);
+        IB_CUDA(h, cudaGetLastError());
+    }
+    s->limK = lim ? grad_limit_k : 0.0;
+    s->snPsi = sngrad_psi >= 0.0 ? sngrad_psi : -1.0;
     return IB200_OK;
 }
 

@@ -15,7 +15,8 @@ P = ctypes.c_void_p
 class _Mesh(ctypes.Structure):
     _fields_ = [("nCells", ctypes.c_longlong), ("nInt", ctypes.c_longlong), ("nBnd", ctypes.c_longlong),
                 ("owner", P), ("neighbour", P), ("Sf", P), ("magSf", P), ("w", P), ("dc", P), ("dcB", P),
-                ("corr", P), ("V", P), ("bmask", P)]
+                ("corr", P), ("V", P), ("bmask", P), ("Cc", P), ("Cf", P), ("gradK", ctypes.c_double),
+                ("snPsi", ctypes.c_double)]
 
 
 def lib():
@@ -34,16 +35,19 @@ def _c(a, dt=np.float64):
 class Oracle:
     """Holds the C mesh struct (and keeps the numpy arrays it points into alive)."""
 
-    def __init__(self, mesh, corrected=True):
+    def __init__(self, mesh, corrected=True, grad_limit_k=0.0, sngrad_psi=-1.0):
+        """grad_limit_k > 0: gradSchemes 'cellMDLimited Gauss linear k'; sngrad_psi >= 0: snGrad 'limited psi'
+        (tutorials/CFD/04unsteadyNS/system/fvSchemes); defaults = the 'Gauss linear' / 'corrected' set."""
         self.mesh = mesh
         self.keep = dict(owner=_c(mesh.owner, np.int32), neighbour=_c(mesh.neighbour, np.int32), Sf=_c(mesh.Sf),
                          magSf=_c(mesh.magSf), w=_c(mesh.w), dc=_c(mesh.dc), dcB=_c(mesh.dcB), corr=_c(mesh.corr),
-                         V=_c(mesh.V), bmask=_c(mesh.bmask, np.uint8))
+                         V=_c(mesh.V), bmask=_c(mesh.bmask, np.uint8), Cc=_c(mesh.Cc), Cf=_c(mesh.Cf))
         k = self.keep
         self.m = _Mesh(mesh.nCells, mesh.nInt, mesh.nBnd, k["owner"].ctypes.data, k["neighbour"].ctypes.data,
                        k["Sf"].ctypes.data, k["magSf"].ctypes.data, k["w"].ctypes.data, k["dc"].ctypes.data,
                        k["dcB"].ctypes.data, k["corr"].ctypes.data if corrected else None, k["V"].ctypes.data,
-                       k["bmask"].ctypes.data)
+                       k["bmask"].ctypes.data, k["Cc"].ctypes.data, k["Cf"].ctypes.data, float(grad_limit_k),
+                       float(sngrad_psi))
         self.L = lib()
 
     def _ref(self):

@@ -44,7 +44,79 @@ typedef struct {
     const double* corr;    /* 3*nInt nonOrthCorrectionVectors, or NULL for "uncorrected" */
     const double* V;       /* nCells */
     const unsigned char* bmask; /* nBnd: 0 = face of an `empty` patch */
+    /* scheme selection beyond "Gauss linear" (tutorials/CFD/04unsteadyNS/system/fvSchemes): */
+    const double* Cc;      /* 3*nCells cell centres mesh.C()  (only read when gradK > 0) */
+    const double* Cf;      /* 3*(nInt+nBnd) face centres mesh.Cf() */
+    double gradK;          /* > 0: gradSchemes "cellMDLimited Gauss linear <gradK>"; <= 0: "Gauss linear" */
+    double snPsi;          /* >= 0: snGrad "limited <snPsi>" (needs corr); < 0: "corrected" / "uncorrected" */
 } fvo_mesh;
+
+/* cellMDLimited gradient limiter (OpenFOAM finiteVolume/gradSchemes/limitedGradSchemes/cellMDLimitedGrad:
+ * cellMDLimitedGrads.C calcGrad + cellMDLimitedGrad.H limitFaceCmpt), applied in place to the Gauss linear cell
+ * gradients g[c][i*dim + d] = d_i vf_d of a dim-component field vf (boundary values vb on non-empty faces):
+ *   max/min of vf over the cell and its face neighbours (boundary faces: the patch value), minus the cell value,
+ *   widened by (1/k - 1)(max - min) when k < 1; then, face by face IN OPENFOAM'S ORDER (internal faces ascending, each
+ *   limiting its owner then its neighbour; then the boundary faces), every component's gradient is clipped along
+ *   dcf = Cf - C so that the extrapolated increment dcf . g stays inside [min, max]. The vector version limits each
+ *   component's gradient (a column of the tensor) with that component's own bounds. */
+static void limit_face_cmpt(double* g, int stride, double maxDelta, double minDelta, const double* dcf)
+{
+    const double ex = dcf[0] * g[0] + dcf[1] * g[stride] + dcf[2] * g[2 * stride];
+    double s;
+    if (ex > maxDelta) s = maxDelta - ex;
+    else if (ex < minDelta) s = minDelta - ex;
+    else return;
+    const double msq = dcf[0] * dcf[0] + dcf[1] * dcf[1] + dcf[2] * dcf[2];
+    for (int i = 0; i < 3; i++) g[i * stride] = g[i * stride] + dcf[i] * s / msq;
+}
+
+static void fvo_limit_grad(const fvo_mesh* m, int dim, const double* vf, const double* vb, double* g)
+{
+    const double k = m->gradK;
+    if (!(k > 0.0)) return;
+    const long long nC = m->nCells;
+    double* mx = (double*)malloc(sizeof(double) * dim * nC);
+    double* mn = (double*)malloc(sizeof(double) * dim * nC);
+    memcpy(mx, vf, sizeof(double) * dim * nC);
+    memcpy(mn, vf, sizeof(double) * dim * nC);
+    for (long long f = 0; f < m->nInt; f++) {
+        const int o = m->owner[f], n = m->neighbour[f];
+        for (int d = 0; d < dim; d++) {
+            const double vo = vf[dim * o + d], vn = vf[dim * n + d];
+            mx[dim * o + d] = fmax(mx[dim * o + d], vn); mn[dim * o + d] = fmin(mn[dim * o + d], vn);
+            mx[dim * n + d] = fmax(mx[dim * n + d], vo); mn[dim * n + d] = fmin(mn[dim * n + d], vo);
+        }
+    }
+    for (long long b = 0; b < m->nBnd; b++) {
+        if (!m->bmask[b]) continue;
+        const int o = m->owner[m->nInt + b];
+        for (int d = 0; d < dim; d++) {
+            mx[dim * o + d] = fmax(mx[dim * o + d], vb[dim * b + d]);
+            mn[dim * o + d] = fmin(mn[dim * o + d], vb[dim * b + d]);
+        }
+    }
+    for (long long i = 0; i < dim * nC; i++) { mx[i] -= vf[i]; mn[i] -= vf[i]; }
+    if (k < 1.0)
+        for (long long i = 0; i < dim * nC; i++) {
+            const double dd = (1.0 / k - 1.0) * (mx[i] - mn[i]);
+            mx[i] += dd;
+            mn[i] -= dd;
+        }
+    for (long long f = 0; f < m->nInt + m->nBnd; f++) {
+        if (f >= m->nInt && !m->bmask[f - m->nInt]) continue;
+        const int o = m->owner[f];
+        double dcf[3];
+        for (int i = 0; i < 3; i++) dcf[i] = m->Cf[3 * f + i] - m->Cc[3 * o + i];
+        for (int d = 0; d < dim; d++) limit_face_cmpt(g + 3 * dim * (long long)o + d, dim, mx[dim * o + d], mn[dim * o + d], dcf);
+        if (f < m->nInt) {
+            const int n = m->neighbour[f];
+            for (int i = 0; i < 3; i++) dcf[i] = m->Cf[3 * f + i] - m->Cc[3 * n + i];
+            for (int d = 0; d < dim; d++) limit_face_cmpt(g + 3 * dim * (long long)n + d, dim, mx[dim * n + d], mn[dim * n + d], dcf);
+        }
+    }
+    free(mx);
+    free(mn);
+}
 
 /* ---- operators ------------------------------------------------------------------------------------- */
 
@@ -125,6 +197,7 @@ void fvo_grad_scalar(const fvo_mesh* m, const double* p, const double* pb, doubl
     }
     for (long long i = 0; i < m->nCells; i++)
         for (int c = 0; c < 3; c++) out[3 * i + c] /= m->V[i];
+    fvo_limit_grad(m, 1, p, pb, out);
 }
 
 /* T = fvc::grad(U), Gauss linear: T[cell][i][j] = sum_f Sf_i U_f,j / V (outer product Sf * U_f). out: 9*nCells. */
@@ -151,6 +224,7 @@ void fvo_grad_vec(const fvo_mesh* m, const double* U, const double* Ub, double* 
     }
     for (long long c = 0; c < m->nCells; c++)
         for (int k = 0; k < 9; k++) out[9 * c + k] /= m->V[c];
+    fvo_limit_grad(m, 3, U, Ub, out);
 }
 
 /* out = fvc::laplacian(dimensionedScalar(1), U), Gauss linear corrected (m->corr != NULL) or uncorrected.
@@ -166,14 +240,23 @@ void fvo_laplacian_vec(const fvo_mesh* m, const double* U, const double* Ub, dou
     for (long long f = 0; f < m->nInt; f++) {
         const int o = m->owner[f], n = m->neighbour[f];
         const double w = m->w[f];
+        double snu[3], cr[3] = {0.0, 0.0, 0.0}, lim = 1.0;
         for (int j = 0; j < 3; j++) {
-            double sn = m->dc[f] * (U[3 * n + j] - U[3 * o + j]);
-            if (T) {
-                double cr = 0.0; /* nonOrthCorrectionVectors & linearInterpolate(grad(U.component(j))) */
+            snu[j] = m->dc[f] * (U[3 * n + j] - U[3 * o + j]);
+            if (T) /* nonOrthCorrectionVectors & linearInterpolate(grad(U)) (correctedSnGrad<vector>::correction) */
                 for (int i = 0; i < 3; i++)
-                    cr += m->corr[3 * f + i] * (w * T[9 * o + 3 * i + j] + (1.0 - w) * T[9 * n + 3 * i + j]);
-                sn += cr;
-            }
+                    cr[j] += m->corr[3 * f + i] * (w * T[9 * o + 3 * i + j] + (1.0 - w) * T[9 * n + 3 * i + j]);
+        }
+        if (T && m->snPsi >= 0.0) {
+            /* snGradSchemes/limitedSnGrad/limitedSnGrad.C correction(): limiter * corr,
+             * limiter = min(psi |snGrad_uncorrected| / ((1 - psi) |corr| + SMALL), 1), |.| the vector magnitude */
+            const double a = sqrt(snu[0] * snu[0] + snu[1] * snu[1] + snu[2] * snu[2]);
+            const double c = sqrt(cr[0] * cr[0] + cr[1] * cr[1] + cr[2] * cr[2]);
+            lim = fmin(m->snPsi * a / ((1.0 - m->snPsi) * c + 1e-15), 1.0);
+        }
+        for (int j = 0; j < 3; j++) {
+            double sn = snu[j];
+            if (T) sn += (m->snPsi >= 0.0) ? lim * cr[j] : cr[j];
             const double v = m->magSf[f] * sn;
             out[3 * o + j] += v;
             out[3 * n + j] -= v;

@@ -223,3 +223,65 @@ def test_cell_major_and_field_major_laplacians_agree_bitwise(pkg, pod, monkeypat
         b, Bb = pr.fvc("laplacian", 4), pr.project("B")
         assert np.array_equal(a, b) and np.array_equal(Ba, Bb)
     monkeypatch.delenv("ITHACA_B200_LAP", raising=False)
+
+
+# ---- the scheme set of tutorials/CFD/04unsteadyNS/system/fvSchemes ----------------------------
+@pytest.fixture(scope="module", params=[("tutorial04", 1.0, 1.0), ("tutorial04", 0.5, 1.0), ("cyl", 1.0, 0.5), ("box", 0.7, -1.0)])
+def scheme_case(request, pkg, pod):
+    name, k, psi = request.param
+    mesh = meshes()[name]()
+    U, Ub, P, Pb = fvc.synthetic_basis(mesh, 6, 3, seed=21)
+    rng = np.random.default_rng(5)   # rough modes: the gradient limiter is active in most cells for k = 1
+    U = [u + 0.2 * rng.standard_normal(u.shape) for u in U]
+    P = [p + 0.2 * rng.standard_normal(p.shape) for p in P]
+    pr = pkg.Projector(pod)
+    pr.set_mesh(mesh, corrected=True)
+    pr.set_schemes(grad_limit_k=k, sngrad_psi=psi, C=mesh.Cc, Cf=mesh.Cf)
+    pr.set_basis("U", U, Ub)
+    pr.set_basis("P", P, Pb)
+    return mesh, fvc.Oracle(mesh, corrected=True, grad_limit_k=k, sngrad_psi=psi), fvc.Oracle(mesh, corrected=True), pr, (U, Ub, P, Pb), k
+
+
+def test_limited_schemes_fields_match_oracle(scheme_case):
+    mesh, orc, plain, pr, (U, Ub, P, Pb), k = scheme_case
+    g = orc.grad(P[1], Pb[1])
+    assert rel(pr.fvc("grad_p", 1), g) <= 1e-12
+    if k == 1.0:
+        assert rel(g, plain.grad(P[1], Pb[1])) > 1e-3      # the limiter really acts on these modes
+    assert rel(pr.fvc("laplacian", 3), orc.laplacian(U[3], Ub[3])) <= 1e-11
+
+
+def test_limited_schemes_operators_match_oracle(scheme_case):
+    mesh, orc, plain, pr, (U, Ub, P, Pb), k = scheme_case
+    assert rel(pr.project("K"), orc.pressure_gradient_term(U, P, Pb)) <= TOL
+    assert rel(pr.project("B"), orc.diffusive_term(U, Ub)) <= TOL
+    D = pr.project("D")
+    assert rel(D, orc.laplacian_pressure(P, Pb)) <= TOL and np.array_equal(D, D.T)
+    assert rel(pr.project("G"), orc.div_momentum(U, Ub, P, Pb)) <= TOL
+    assert rel(pr.project("BC3"), orc.pressure_bc3(U, Ub, P, Pb)) <= TOL
+    assert rel(pr.project("BC1"), orc.pressure_bc1(U, Ub, Pb)) <= TOL
+    assert rel(pr.project("BP"), orc.diffusive_term_flux_method(U, Ub, P)) <= TOL
+    vls, vlsb = U[1] + 0.5 * U[2], Ub[1] + 0.5 * Ub[2]
+    assert rel(pr.project_background(vls, vlsb, divergent=True), orc.convective_background(U, Ub, vls, vlsb, P, Pb)) <= TOL
+    # operators without a gradient or snGrad in them are untouched by the scheme selection
+    assert rel(pr.project("P"), plain.divergence_term(U, Ub, P)) <= TOL
+    if k == 1.0:
+        assert rel(pr.project("K"), plain.pressure_gradient_term(U, P, Pb)) > 1e-6
+
+
+def test_set_schemes_argument_checks(pkg, pod):
+    mesh = meshes()["box"]()
+    pr = pkg.Projector(pod)
+    pr.set_mesh(mesh, corrected=False)
+    with pytest.raises(pkg.IthacaB200Error, match="should be >= 0 and <= 1"):
+        pr.set_schemes(grad_limit_k=1.5, C=mesh.Cc, Cf=mesh.Cf)
+    with pytest.raises(pkg.IthacaB200Error, match="nonOrthCorrectionVectors"):
+        pr.set_schemes(sngrad_psi=1.0)
+    with pytest.raises(pkg.IthacaB200Error, match="needs mesh.C"):
+        pr.set_schemes(grad_limit_k=0.5)
+    # k below SMALL is the unlimited gradient (cellMDLimitedGrads.C), and a new mesh resets the selection
+    U, Ub, P, Pb = fvc.synthetic_basis(mesh, 2, 2, seed=1)
+    pr.set_schemes(grad_limit_k=1e-16, C=mesh.Cc, Cf=mesh.Cf)
+    pr.set_basis("U", U, Ub)
+    pr.set_basis("P", P, Pb)
+    assert rel(pr.fvc("grad_p", 0), fvc.Oracle(mesh, corrected=False).grad(P[0], Pb[0])) <= 1e-13
