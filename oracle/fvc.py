@@ -41,8 +41,9 @@ class Oracle:
         self.mesh = mesh
         self.keep = dict(owner=_c(mesh.owner, np.int32), neighbour=_c(mesh.neighbour, np.int32), Sf=_c(mesh.Sf),
                          magSf=_c(mesh.magSf), w=_c(mesh.w), dc=_c(mesh.dc), dcB=_c(mesh.dcB), corr=_c(mesh.corr),
-                         V=_c(mesh.V), bmask=_c(mesh.bmask, np.uint8), Cc=_c(mesh.Cc), Cf=_c(mesh.Cf))
+                         V=_c(mesh.V), bmask=_c(mesh.bmask, np.uint8), Cc=_c(getattr(mesh, "Cc", np.zeros(3))), Cf=_c(getattr(mesh, "Cf", np.zeros(3))))
         k = self.keep
+        assert not grad_limit_k > 0 or (k["Cc"].size == 3 * mesh.nCells and k["Cf"].size == 3 * (mesh.nInt + mesh.nBnd))
         self.m = _Mesh(mesh.nCells, mesh.nInt, mesh.nBnd, k["owner"].ctypes.data, k["neighbour"].ctypes.data,
                        k["Sf"].ctypes.data, k["magSf"].ctypes.data, k["w"].ctypes.data, k["dc"].ctypes.data,
                        k["dcB"].ctypes.data, k["corr"].ctypes.data if corrected else None, k["V"].ctypes.data,

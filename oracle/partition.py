@@ -121,6 +121,9 @@ class ShardMesh:
         self.bmask = np.concatenate([np.asarray(mesh.bmask, dtype=np.uint8)[gb - mesh.nInt], np.zeros(nCut, dtype=np.uint8)])
         self.V = np.asarray(mesh.V, dtype=np.float64)[cpa].copy()
         self.nOwned = int(part["nOwned"])
+        if hasattr(mesh, "Cc"):   # centres for the cellMDLimited gradient (mesh_set_schemes), shard order
+            self.Cc = np.asarray(mesh.Cc, dtype=np.float64)[cpa].copy()
+            self.Cf = np.asarray(mesh.Cf, dtype=np.float64)[g].copy()
         self._cpa, self._gb, self._nCut, self._nInt_g = cpa, gb, nCut, mesh.nInt
 
     def cell_field(self, f, dim):
