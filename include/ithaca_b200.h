@@ -170,6 +170,12 @@ int ithaca_b200_pod_block_begin(ithaca_b200_t* h, int m_total, int dim, int64_t 
 int ithaca_b200_pod_block_upload(ithaca_b200_t* h, int slot, const double* const* snap_ptrs, int nb, int first);
 int ithaca_b200_pod_block_gram(ithaca_b200_t* h, int slotI, int slotJ, int norm_kind);
 int ithaca_b200_pod_block_gram_finish(ithaca_b200_t* h, double* G_out);
+/* Checkpoint / resume of the blocked correlation matrix (PODTemplate::buildCovMatrix saves it after every block pair and
+ * restarts from the newest complete file, src/ITHACA_CORE/ITHACAPOD/PODTemplate.C:419-577, findTempFile :265-341):
+ *   block_gram_get(G_out)   the matrix accumulated so far, summed over ranks, WITHOUT finishing (m x m col-major)
+ *   block_gram_set(G)       after block_begin: continue from a saved matrix (every rank passes the same G) */
+int ithaca_b200_pod_block_gram_get(ithaca_b200_t* h, double* G_out);
+int ithaca_b200_pod_block_gram_set(ithaca_b200_t* h, const double* G);
 int ithaca_b200_pod_block_lift(ithaca_b200_t* h, int slot, int r);
 int ithaca_b200_pod_block_lift_finish(ithaca_b200_t* h, int r, int norm_kind, double* const* mode_ptrs, double* normfact_out);
 

@@ -26,7 +26,7 @@ SYMBOLS = [
     "ithaca_b200_pod_set_modes", "ithaca_b200_pod_project", "ithaca_b200_pod_modes_mass", "ithaca_b200_pod_get_coeffs",
     "ithaca_b200_pod_reconstruct", "ithaca_b200_pod_lift_scaled", "ithaca_b200_pod_gram_volumes",
     "ithaca_b200_pod_block_begin", "ithaca_b200_pod_block_upload", "ithaca_b200_pod_block_gram",
-    "ithaca_b200_pod_block_gram_finish", "ithaca_b200_pod_block_lift", "ithaca_b200_pod_block_lift_finish",
+    "ithaca_b200_pod_block_gram_finish", "ithaca_b200_pod_block_gram_get", "ithaca_b200_pod_block_gram_set", "ithaca_b200_pod_block_lift", "ithaca_b200_pod_block_lift_finish",
     "ithaca_b200_mesh_upload", "ithaca_b200_mesh_addressing", "ithaca_b200_basis_upload", "ithaca_b200_project",
     "ithaca_b200_fvc_eval", "ithaca_b200_proj_timings", "ithaca_b200_project_background", "ithaca_b200_project_bc_velocity",
     "ithaca_b200_partition_create", "ithaca_b200_partition_destroy", "ithaca_b200_partition_sizes",
@@ -82,6 +82,8 @@ def lib():
         L.ithaca_b200_pod_block_upload.argtypes = [P, I, P, I, I]
         L.ithaca_b200_pod_block_gram.argtypes = [P, I, I, I]
         L.ithaca_b200_pod_block_gram_finish.argtypes = [P, P]
+        L.ithaca_b200_pod_block_gram_get.argtypes = [P, P]
+        L.ithaca_b200_pod_block_gram_set.argtypes = [P, P]
         L.ithaca_b200_pod_block_lift.argtypes = [P, I, I]
         L.ithaca_b200_pod_block_lift_finish.argtypes = [P, I, I, P, P]
         L.ithaca_b200_pod_project.argtypes = [P, I, I, P]
@@ -683,6 +685,107 @@ def getModesMemoryEfficient(pod, block_source, m, V, dim, nmodes=0, solver="spec
     pod.r = nmodes
     evn, cum = postprocess_eigenvalues(ev_all, nmodes, solver)
     return dict(G=G, evals_all=ev_all, evals_norm=evn, cum=cum, evecs=Q, normfact=nf, modes=Phi)
+
+
+COV_UNREAL = 999999.999999   # PODTemplate::buildCovMatrix marks entries not computed yet with this value (PODTemplate.C:422)
+
+
+def buildCovMatrix(pod, block_source, m, V, dim, nBlocks, folder, name, norm="L2", keep_temp=3, on_checkpoint=None):
+    """PODTemplate::buildCovMatrix (src/ITHACA_CORE/ITHACAPOD/PODTemplate.C:419-616) on the device: the m x m correlation
+    matrix of a snapshot set streamed in nBlocks blocks of q = m // nBlocks snapshots (+ one remainder block), with the
+    reference's checkpoint / resume protocol:
+      * after every square block pair (i, j < i) the matrix is written to  folder/name_temp_<i>_<j>.npy  (cnpy layout,
+        entries not computed yet = 999999.999999, lower triangle only; nameTempCovMatrix :341-352), the file `keep_temp`
+        steps back is removed;
+      * a run that finds such files restarts from the OLDEST one (findTempFile :265-341) at the next block pair;
+      * the finished matrix (lower part mirrored, :537) is written to  folder/name.npy  and read back by later runs.
+    block_source(first, nb) -> nb snapshot buffers. on_checkpoint(i, j) is called after each temp file is written.
+    The matrix stays installed on the device as the Gram of pod.eig (block_gram_finish). Returns the m x m matrix."""
+    import glob
+    import re
+    if norm not in ("L2", "Frobenius"):
+        raise IthacaB200Error("The PODnorm can be only L2 or Frobenius")
+    nk = 0 if norm == "L2" else 1
+    L, h = pod.L, pod.h
+    nCells = V.shape[0]
+    os.makedirs(folder, exist_ok=True)
+    final = os.path.join(folder, name + ".npy")
+    pod.set_volumes(V)
+    pod._chk(L.ithaca_b200_pod_block_begin(h, m, dim, nCells))
+    pod.m, pod.dim = m, dim
+    if os.path.exists(final):      # "Reading the covariance matrix" branch (:553-558)
+        G = np.asfortranarray(np.load(final))
+        if G.shape != (m, m):
+            raise IthacaB200Error("buildCovMatrix: %s holds a %s matrix, expected %d x %d" % (final, G.shape, m, m))
+        pod._chk(L.ithaca_b200_pod_block_gram_set(h, G.ctypes.data))
+        pod._chk(L.ithaca_b200_pod_block_gram_finish(h, None))
+        return G
+    q, r = m // nBlocks, m % nBlocks
+    if q == 0:
+        raise IthacaB200Error("buildCovMatrix: more blocks than snapshots")
+    blocks = [(b * q, q) for b in range(nBlocks)] + ([(nBlocks * q, r)] if r else [])
+    done = np.zeros((m, m), dtype=bool)          # lower-triangle entries computed so far
+    # restart point
+    temps = []
+    for f in glob.glob(os.path.join(folder, name + "_temp_*_*.npy")):
+        mt = re.match(re.escape(name) + r"_temp_(\d+)_(\d+)\.npy$", os.path.basename(f))
+        if mt:
+            temps.append((int(mt.group(1)), int(mt.group(2)), f))
+    etI, etJ = 0, 0
+    if temps:
+        ti, tj, tf = min(temps)
+        C = np.load(tf)
+        if C.shape != (m, m):
+            raise IthacaB200Error("buildCovMatrix: temp file %s has the wrong size" % tf)
+        done = np.tril(C != COV_UNREAL)
+        Gl = np.where(done, C, 0.0)
+        G0 = np.asfortranarray(Gl + np.tril(Gl, -1).T)      # the device keeps both halves of every computed block
+        pod._chk(L.ithaca_b200_pod_block_gram_set(h, G0.ctypes.data))
+        etI, etJ = (ti + 1, 0) if tj == ti - 1 else (ti, tj + 1)    # PODTemplate.C:452-466
+
+    def up(slot, b):
+        first, nb = blocks[b]
+        bufs = block_source(first, nb)
+        arr = (ctypes.c_void_p * nb)(*[_ptr(x) for x in bufs])
+        pod._chk(L.ithaca_b200_pod_block_upload(h, slot, arr, nb, first))
+        return bufs
+
+    def mark(bi, bj):
+        (i0, ni), (j0, nj) = blocks[bi], blocks[bj]
+        done[i0:i0 + ni, j0:j0 + nj] = True
+
+    saved = [(ti, tj) for ti, tj, _ in sorted(temps)]
+    G = np.zeros((m, m), order="F")
+    for bi in range(etI, len(blocks)):
+        # the remainder block restarts its row from j = 0 as the reference does (:509-529)
+        j_start = etJ if (bi == etI and bi < nBlocks) else 0
+        keep = up(0, bi)
+        pod._chk(L.ithaca_b200_pod_block_gram(h, 0, 0, nk))      # addCovMatrixTriCoeff
+        mark(bi, bi)
+        for bj in range(j_start, bi):
+            keep2 = up(1, bj)
+            pod._chk(L.ithaca_b200_pod_block_gram(h, 0, 1, nk))  # addCovMatrixSquareCoeff
+            mark(bi, bj)
+            pod._chk(L.ithaca_b200_pod_block_gram_get(h, G.ctypes.data))
+            save_npy(np.where(np.tril(done), G, COV_UNREAL), os.path.join(folder, "%s_temp_%d_%d.npy" % (name, bi, bj)))
+            saved.append((bi, bj))
+            while len(saved) > keep_temp + 1:                     # deletePreviousTempCovMatrix_N
+                oi, oj = saved.pop(0)
+                old = os.path.join(folder, "%s_temp_%d_%d.npy" % (name, oi, oj))
+                if os.path.exists(old):
+                    os.remove(old)
+            if on_checkpoint is not None:
+                on_checkpoint(bi, bj)
+    pod._chk(L.ithaca_b200_pod_block_gram_finish(h, G.ctypes.data))
+    if not np.tril(done).sum() == m * (m + 1) // 2:
+        raise IthacaB200Error("!!! OUPS !!! Unreal value [%s] found in triangular part of %s" % (COV_UNREAL, name))
+    G = np.asfortranarray(np.tril(G) + np.tril(G, -1).T)          # covMatrix.selfadjointView<Eigen::Lower>()
+    save_npy(G, final)
+    for oi, oj in saved:
+        old = os.path.join(folder, "%s_temp_%d_%d.npy" % (name, oi, oj))
+        if os.path.exists(old):
+            os.remove(old)
+    return G
 
 
 def check_nmodes(m, nmodes, solver):

@@ -787,6 +787,42 @@ int ithaca_b200_pod_block_gram_finish(ithaca_b200_t* h, double* G_out)
     return IB200_OK;
 }
 
+// Checkpoint support of the blocked correlation matrix (PODTemplate::buildCovMatrix saves the matrix after every block
+// pair, PODTemplate.C:487-505, and restarts from the file, :265-341).
+int ithaca_b200_pod_block_gram_get(ithaca_b200_t* h, double* G_out)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->block_mode || !G_out) { set_error(h, "pod_block_gram_get: call pod_block_begin first"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    const size_t n = (size_t)h->m * h->m;
+    double* src = h->dG;
+    if (h->nranks > 1 && h->nccl_comm) {
+        // the resident matrix holds this rank's partial sums until pod_block_gram_finish: reduce a copy
+        int rc = ensure(h, &h->dPhiTmp, &h->dPhiTmp_cap, n * sizeof(double));
+        if (rc) return rc;
+        IB_CUDA(h, cudaMemcpyAsync(h->dPhiTmp, h->dG, n * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+        if ((rc = allreduce_sum(h, h->dPhiTmp, n))) return rc;
+        src = h->dPhiTmp;
+    }
+    IB_CUDA(h, cudaMemcpyAsync(G_out, src, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_block_gram_set(ithaca_b200_t* h, const double* G)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->block_mode || !G) { set_error(h, "pod_block_gram_set: call pod_block_begin first"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    const size_t n = (size_t)h->m * h->m;
+    // G is the all-reduced matrix: rank 0 carries it, the other ranks restart their partial sums from zero
+    if (h->rank == 0) IB_CUDA(h, cudaMemcpyAsync(h->dG, G, n * sizeof(double), cudaMemcpyDefault, h->stream));
+    else IB_CUDA(h, cudaMemsetAsync(h->dG, 0, n * sizeof(double), h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->have_gram = h->have_eig = false;
+    return IB200_OK;
+}
+
 int ithaca_b200_pod_block_lift(ithaca_b200_t* h, int slot, int r)
 {
     if (!h) return IB200_ERR_ARG;

@@ -603,6 +603,7 @@ div_adjoint_kernel(MeshDev m, const double* __restrict__ P, long long ldP, int n
 }
 
 // K7a: T_j = fvc::grad(U_j), Gauss linear: T[c][i][d] = sum_f +-Sf_i * Uf_d / V. One field per block.
+template <bool SCH>   // SCH: a scheme of mesh_set_schemes is active (kept out of the default instantiation)
 __global__ void __launch_bounds__(PROJ_T)
 grad_vec_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const double* __restrict__ Ub, long long ldUb,
                 int j0, int nb, double* __restrict__ T, long long ldT)
@@ -652,7 +653,7 @@ grad_vec_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const do
     for (int i = 0; i < 3; i++)
 #pragma unroll
         for (int d = 0; d < 3; d++) acc[i][d] /= V;
-    if (m.limK > 0.0) {
+    if (SCH && m.limK > 0.0) {
         const double* ub = Ub + (size_t)j * ldUb;
 #pragma unroll
         for (int d = 0; d < 3; d++)   // component d: its gradient is column d of the tensor
@@ -671,6 +672,7 @@ grad_vec_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const do
 
 // K7b: out_j = fvc::laplacian(1, U_j) = surfaceIntegrate(|Sf| snGrad(U_j)); snGrad = dc (U[n]-U[o])
 // (+ corr . (w T[o] + (1-w) T[n]) when corrected); boundary |Sf| dcB (Ub - U[c]). Grid as in grad_vec_kernel.
+template <bool SCH>
 __global__ void __launch_bounds__(PROJ_T)
 laplacian_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const double* __restrict__ Ub, long long ldUb,
                  int j0, int nb, const double* __restrict__ T, long long ldT, double* __restrict__ out, long long ldo)
@@ -711,27 +713,32 @@ laplacian_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const d
                     }
                 }
             }
-            double snu[3];
-#pragma unroll
-            for (int d = 0; d < 3; d++) {
-                const double x = u[3 * (size_t)ot + d];
-                snu[d] = own ? dc * (x - uc[d]) : dc * (uc[d] - x);
-            }
-            if (t && m.snPsi >= 0.0) {
+            if (SCH && t && m.snPsi >= 0.0) {
                 // snGrad "limited psi" (limitedSnGrad::correction): limiter = min(psi |snGrad_unc| / ((1-psi) |corr| + SMALL), 1);
                 // both magnitudes are the same seen from either side of the face
+                double snu[3];
+#pragma unroll
+                for (int d = 0; d < 3; d++) {
+                    const double x = u[3 * (size_t)ot + d];
+                    snu[d] = own ? dc * (x - uc[d]) : dc * (uc[d] - x);
+                }
                 const double a = sqrt(snu[0] * snu[0] + snu[1] * snu[1] + snu[2] * snu[2]);
                 const double cm = sqrt(cr[0] * cr[0] + cr[1] * cr[1] + cr[2] * cr[2]);
                 const double lim = fmin(m.snPsi * a / ((1.0 - m.snPsi) * cm + 1e-15), 1.0);
 #pragma unroll
-                for (int d = 0; d < 3; d++) cr[d] = lim * cr[d];
-            }
+                for (int d = 0; d < 3; d++) {
+                    const double v = ms * (snu[d] + lim * cr[d]);
+                    acc[d] += own ? v : -v;
+                }
+            } else {
 #pragma unroll
-            for (int d = 0; d < 3; d++) {
-                double sn = snu[d];
-                if (t) sn += cr[d];
-                const double v = ms * sn;
-                acc[d] += own ? v : -v;
+                for (int d = 0; d < 3; d++) {
+                    const double x = u[3 * (size_t)ot + d];
+                    double sn = own ? dc * (x - uc[d]) : dc * (uc[d] - x);
+                    if (t) sn += cr[d];
+                    const double v = ms * sn;
+                    acc[d] += own ? v : -v;
+                }
             }
         } else {
             const long long b = -(long long)ot - 1;
@@ -1308,16 +1315,25 @@ static int run_laplacians(ithaca_b200* h, ProjState* s, double* out)
         int rc = ensure(h, s->T, (size_t)batch * ldT * sizeof(double));
         if (rc) return rc;
     }
+    const bool sch = s->limK > 0.0 || (s->corrected && s->snPsi >= 0.0);
     StageTimer t(h->stream, &s->ms[2]);
     for (int j0 = 0; j0 < s->nU; j0 += batch) {
         const int nb = std::min(batch, s->nU - j0);
         if (s->corrected) {
-            grad_vec_kernel<<<gx(s->nCells) * nb, PROJ_T, 0, h->stream>>>(m, s->U.as<double>(), s->ldU, s->Ub.as<double>(),
-                                                                           s->ldUb, j0, nb, s->T.as<double>(), ldT);
+            if (sch)
+                grad_vec_kernel<true><<<gx(s->nCells) * nb, PROJ_T, 0, h->stream>>>(m, s->U.as<double>(), s->ldU, s->Ub.as<double>(),
+                                                                                     s->ldUb, j0, nb, s->T.as<double>(), ldT);
+            else
+                grad_vec_kernel<false><<<gx(s->nCells) * nb, PROJ_T, 0, h->stream>>>(m, s->U.as<double>(), s->ldU, s->Ub.as<double>(),
+                                                                                      s->ldUb, j0, nb, s->T.as<double>(), ldT);
             h->launches += 1;
         }
-        laplacian_kernel<<<gx(s->nCells) * nb, PROJ_T, 0, h->stream>>>(m, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb,
-                                                                        j0, nb, s->corrected ? s->T.as<double>() : nullptr, ldT, out, s->ldU);
+        if (sch)
+            laplacian_kernel<true><<<gx(s->nCells) * nb, PROJ_T, 0, h->stream>>>(m, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb, j0, nb,
+                                                                                  s->corrected ? s->T.as<double>() : nullptr, ldT, out, s->ldU);
+        else
+            laplacian_kernel<false><<<gx(s->nCells) * nb, PROJ_T, 0, h->stream>>>(m, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb, j0, nb,
+                                                                                   s->corrected ? s->T.as<double>() : nullptr, ldT, out, s->ldU);
         h->launches += 1;
     }
     t.stop();

@@ -331,3 +331,50 @@ def test_deim_modes_are_getmodes(pkg, pod):
     ref = po.getmodes(S, V, dim, r, "eigen", "Frobenius")
     assert np.all(np.abs(out["evals_norm"][:r] - ref["evals_norm"][:r]) <= 1e-10 * ref["evals_norm"][:r])
     assert modes_rel(out["modes"], ref["modes"]) <= 1e-8
+
+
+def test_blocked_cov_matrix_checkpoint_and_resume(pkg, pod, tmp_path):
+    """PODTemplate::buildCovMatrix's checkpoint / resume protocol (PODTemplate.C:419-616): an interrupted run leaves
+    covMatrix<field>_temp_<i>_<j>.npy files, the next run restarts from the oldest of them at the following block pair and
+    ends with the same matrix; the finished covMatrix<field>.npy is read back by later runs without touching the snapshots."""
+    Nc, dim, m, nBlocks = 2003, 3, 23, 4          # q = 5, remainder block of 3
+    S = synth.snapshots(Nc, dim, m, 8, 17)
+    V = synth.volumes(Nc, 17)
+    folder, name = str(tmp_path / "CovMatrices") + "/", "covMatrixU"
+    ref = po.gram(S, V, dim)
+    reads = []
+
+    def source(first, nb):
+        reads.append((first, nb))
+        return [np.ascontiguousarray(S[:, j]) for j in range(first, first + nb)]
+
+    class Crash(Exception):
+        pass
+
+    def crash_at(i, j):
+        if (i, j) == (3, 1):
+            raise Crash()
+
+    with pytest.raises(Crash):
+        pkg.buildCovMatrix(pod, source, m, V, dim, nBlocks, folder, name, on_checkpoint=crash_at)
+    left = sorted(os.listdir(folder))
+    # pairs saved: (1,0) (2,0) (2,1) (3,0) (3,1); the last keep_temp + 1 = 4 files stay
+    assert left == [name + "_temp_%d_%d.npy" % ij for ij in [(2, 0), (2, 1), (3, 0), (3, 1)]]
+    T = np.load(folder + name + "_temp_2_0.npy")
+    assert T.shape == (m, m) and T[0, 1] == pkg.COV_UNREAL and T[12, 14] == pkg.COV_UNREAL      # upper half / block (2,2)'s upper
+    assert T[12, 3] != pkg.COV_UNREAL and T[12, 7] == pkg.COV_UNREAL and T[17, 0] == pkg.COV_UNREAL  # (2,0) done, (2,1), (3,0) not
+    assert abs(T[12, 3] - ref[12, 3]) <= 1e-13 * np.abs(ref).max()
+    reads.clear()
+    G = pkg.buildCovMatrix(pod, source, m, V, dim, nBlocks, folder, name)
+    # restart from the oldest file (2,0): the next pair is (2,1); blocks 0 and 1 are never read as the row block again
+    assert reads[0] == (10, 5) and reads[1] == (5, 5)
+    assert rel_max(G, ref) <= 1e-13 and np.array_equal(G, G.T)
+    assert sorted(os.listdir(folder)) == [name + ".npy"]
+    assert np.array_equal(np.load(folder + name + ".npy"), G)
+    # the matrix is installed as the Gram of the eigensolve
+    ev, Q = pod.eig(5)
+    ref_ev = np.linalg.eigvalsh(ref)[::-1]
+    assert np.all(np.abs(ev[:5] - ref_ev[:5]) <= 1e-10 * ref_ev[0])
+    reads.clear()
+    G2 = pkg.buildCovMatrix(pod, source, m, V, dim, nBlocks, folder, name)
+    assert reads == [] and np.array_equal(G2, G)
