@@ -277,7 +277,8 @@ int ithaca_b200_project_background(ithaca_b200_t* h, int kind, const double* vls
  * steadyNS.C:1515-1582; inletIndex(k,0) = patch, inletIndex(k,1) = component):
  *   vec_out[i]    = sum over the patch faces of U_i.boundaryField()[patch].component(comp)              (N)
  *   mat_out(i,j)  = sum over the patch faces of U_i...component(comp) * U_j...component(comp)           (N x N)
- * for ALL N velocity fields (the reference skips the lift fields: BCsize = NUmodes + NSUPmodes; take the trailing block).
+ * for ALL N velocity fields (the reference fills BCsize = NUmodes + NSUPmodes entries indexed L_U_SUPmodes[0 .. BCsize): as
+ * coded that is the LEADING block, lift fields included; host/steadyNS_b200.H takes exactly that block).
  * The patch is the boundary-face range [patch_start, patch_start + patch_size) (patch.start() - nInternalFaces). */
 int ithaca_b200_project_bc_velocity(ithaca_b200_t* h, int64_t patch_start, int64_t patch_size, int comp, double* vec_out,
                                     double* mat_out);
