@@ -39,7 +39,7 @@ def write_input(path, mesh, lift, U, sup, P, NU, NP, NSUP, ppe=False, penalty=Fa
         f.write(c(mesh.owner, np.int32) + c(mesh.neighbour, np.int32) + c(mesh.Sf) + c(mesh.magSf) + c(mesh.w) + c(mesh.dc)
                 + c(mesh.dcB) + c(mesh.corr) + c(mesh.V) + c(mesh.bmask, np.uint8) + c(mesh.Cc) + c(mesh.Cf))
         f.write(c([s.start for _, _, s in patches], np.int64) + c([s.stop - s.start for _, _, s in patches], np.int64))
-        f.write(c(np.array(inlet, dtype=np.int64).reshape(-1)))
+        f.write(c(np.array(inlet, dtype=np.int64).reshape(-1), np.int64))
         for fi, fb in list(lift) + list(U) + list(sup) + list(P):
             f.write(c(fi) + c(fb))
 
