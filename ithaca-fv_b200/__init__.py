@@ -598,6 +598,43 @@ def getWeightedModes(pod, snapshots, V, dim, nmodes=0, solver="spectra", Sbc=Non
     return dict(G=G, evals=ev, evals_norm=evn, cum=np.cumsum(evn), evecs=Q, factors=factors, modes=Phi, modes_bc=Pbc)
 
 
+def corMatrix(pod, snapshots, V, dim):
+    """ITHACAPOD::corMatrix (ITHACAPOD.C:955-1008): matrix(i, j) = fvc::domainIntegrate(snapshots[i] (&) snapshots[j]),
+    the volume-weighted correlation matrix, lower triangle mirrored: one Gram launch."""
+    pod.set_volumes(V)
+    pod.upload(snapshots, dim)
+    return pod.gram()
+
+
+def getNestedSnapshotMatrix(pod, snapshots, V, dim, Npar, NnestedOut, solver="spectra"):
+    """ITHACAPOD::getNestedSnapshotMatrix (ITHACAPOD.C:41-82): the snapshot set holds Npar parameter groups of
+    Nt = m / Npar consecutive time snapshots; every group is compressed by getWeightedModes to NnestedOut modes and the
+    groups' modes are appended in order (the nested-POD snapshot matrix). snapshots: (Nd, m) array."""
+    m = snapshots.shape[1]
+    Nt = m // Npar
+    out = []
+    for i in range(Npar):
+        grp = np.asfortranarray(snapshots[:, Nt * i:Nt * (i + 1)])
+        out.append(getWeightedModes(pod, grp, V, dim, NnestedOut, solver)["modes"])
+    return np.asfortranarray(np.concatenate(out, axis=1))
+
+
+def getMeanMemoryEfficient(pod, block_source, m, V, dim, block=64):
+    """ITHACAPOD::getMeanMemoryEfficient (ITHACAPOD.C:660-697): mean of a snapshot set streamed block by block
+    (block_source(first, nb) -> nb buffers); each block contributes S_block (1/m) through the reconstruct kernel."""
+    L, h = pod.L, pod.h
+    nCells = V.shape[0]
+    pod.set_volumes(V)
+    pod._chk(L.ithaca_b200_pod_block_begin(h, m, dim, nCells))
+    pod.m, pod.dim = m, dim
+    mean = np.zeros(nCells * dim)
+    for first in range(0, m, block):
+        nb = min(block, m - first)
+        pod.set_modes(block_source(first, nb))
+        mean += pod.reconstruct(np.full((nb, 1), 1.0 / m))[:, 0]
+    return mean
+
+
 def getModesSVD(pod, snapshots, V, dim, nmodes):
     """ITHACAPOD::getModesSVD (ITHACAPOD.C:858-941) without forming the N_d x m SVD: the left singular vectors of
     diag(sqrt V) S are diag(sqrt V) S q_i / sigma_i with (sigma_i^2, q_i) the eigenpairs of the Gram matrix, so

@@ -378,3 +378,21 @@ def test_blocked_cov_matrix_checkpoint_and_resume(pkg, pod, tmp_path):
     reads.clear()
     G2 = pkg.buildCovMatrix(pod, source, m, V, dim, nBlocks, folder, name)
     assert reads == [] and np.array_equal(G2, G)
+
+
+def test_nested_snapshot_matrix_cormatrix_and_streamed_mean(pkg, pod):
+    """getNestedSnapshotMatrix (ITHACAPOD.C:41-82), corMatrix (:955-1008) and getMeanMemoryEfficient (:660-697): host loops of
+    the reference over kernels that are already on the path."""
+    Nc, dim, Npar, Nt, nout = 1501, 3, 3, 12, 4
+    m = Npar * Nt
+    S = synth.snapshots(Nc, dim, m, 10, 33)
+    V = synth.volumes(Nc, 33)
+    out = pkg.getNestedSnapshotMatrix(pod, S, V, dim, Npar, nout, "eigen")
+    assert out.shape == (Nc * dim, Npar * nout)
+    for i in range(Npar):
+        ref = po.getweightedmodes(np.asfortranarray(S[:, Nt * i:Nt * (i + 1)]), V, dim, nout, "eigen", None)
+        assert modes_rel(out[:, nout * i:nout * (i + 1)], ref["modes"]) <= 1e-8
+    assert rel_max(pkg.corMatrix(pod, S, V, dim), po.gram(S, V, dim)) <= 1e-13
+    mean = pkg.getMeanMemoryEfficient(pod, lambda first, nb: [np.ascontiguousarray(S[:, j]) for j in range(first, first + nb)],
+                                      m, V, dim, block=7)
+    assert np.abs(mean - S.mean(axis=1)).max() <= 1e-13 * np.abs(S).max()
