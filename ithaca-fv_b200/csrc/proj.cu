@@ -603,8 +603,14 @@ div_adjoint_kernel(MeshDev m, const double* __restrict__ P, long long ldP, int n
 }
 
 // K7a: T_j = fvc::grad(U_j), Gauss linear: T[c][i][d] = sum_f +-Sf_i * Uf_d / V. One field per block.
+#ifndef GRADV_MINB
+#define GRADV_MINB 1
+#endif
+#ifndef LAP_MINB
+#define LAP_MINB 1
+#endif
 template <bool SCH>   // SCH: a scheme of mesh_set_schemes is active (kept out of the default instantiation)
-__global__ void __launch_bounds__(PROJ_T)
+__global__ void __launch_bounds__(PROJ_T, GRADV_MINB)
 grad_vec_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const double* __restrict__ Ub, long long ldUb,
                 int j0, int nb, double* __restrict__ T, long long ldT)
 {
@@ -673,7 +679,7 @@ grad_vec_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const do
 // K7b: out_j = fvc::laplacian(1, U_j) = surfaceIntegrate(|Sf| snGrad(U_j)); snGrad = dc (U[n]-U[o])
 // (+ corr . (w T[o] + (1-w) T[n]) when corrected); boundary |Sf| dcB (Ub - U[c]). Grid as in grad_vec_kernel.
 template <bool SCH>
-__global__ void __launch_bounds__(PROJ_T)
+__global__ void __launch_bounds__(PROJ_T, LAP_MINB)
 laplacian_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const double* __restrict__ Ub, long long ldUb,
                  int j0, int nb, const double* __restrict__ T, long long ldT, double* __restrict__ out, long long ldo)
 {
