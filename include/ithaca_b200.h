@@ -213,9 +213,22 @@ int ithaca_b200_mesh_upload(ithaca_b200_t* h, int64_t nCells, int64_t nIntFaces,
  *                 per face by min(psi |snGrad_uncorrected| / ((1 - psi) |correction| + SMALL), 1). Negative: "corrected"
  *                 (or "uncorrected" when mesh_upload got nonOrthCorrVec = NULL). Needs nonOrthCorrVec.
  *   C[3*nCells], Cf[3*(nInt+nBnd)]   mesh.C() internal field and mesh.Cf() (internal then boundary), in the order of the
- *                 uploaded mesh (a shard's local order after mesh_upload_shard); only read when grad_limit_k > 0.
+ *                 uploaded mesh (a shard's local order after mesh_upload_shard); needed when grad_limit_k > 0 and for
+ *                 ithaca_b200_mesh_set_convection(LINEAR_UPWIND); stored whenever both are given.
  * mesh_upload / mesh_upload_shard reset both to off. Host or device pointers. */
 int ithaca_b200_mesh_set_schemes(ithaca_b200_t* h, double grad_limit_k, double sngrad_psi, const double* C, const double* Cf);
+
+/* Interpolation scheme of the convection operators fvc::div(phi, U_k) ("divSchemes  div(phi,U)  Gauss <scheme>"; the flux
+ * phi itself is always linearInterpolate(U_j) & Sf, steadyNS.C:1019-1021). Boundary faces take the patch value in every scheme.
+ *   IB200_CONV_LINEAR         "Gauss linear" (the shipped tutorials; default after mesh_upload)
+ *   IB200_CONV_UPWIND         "Gauss upwind": the owner's value when phi >= 0, else the neighbour's (upwind::weights = pos0(phi))
+ *   IB200_CONV_LINEAR_UPWIND  "Gauss linearUpwind grad(U)": upwind value + (Cf - C_upwind) . grad(U_k)[upwind]
+ *                             (linearUpwind::correction; grad(U_k) by the gradient scheme of mesh_set_schemes, which must
+ *                             have been given C and Cf)
+ * With a non-linear scheme C and G are formed through materialised div(phi_j, U_k) fields (the fused face-based contraction
+ * is the linear face value); BC2 and the background terms follow the scheme; Cf is refused. */
+enum { IB200_CONV_LINEAR = 0, IB200_CONV_UPWIND = 1, IB200_CONV_LINEAR_UPWIND = 2 };
+int ithaca_b200_mesh_set_convection(ithaca_b200_t* h, int scheme);
 
 /* The device-built cell->face CSR, for the bit-exact addressing check: off[nCells+1]; ent[2*nInt+nBnd] = +(f+1) when
  * the cell owns face f, -(f+1) when it is its neighbour, ascending face index per cell (primitiveMesh::cells() order);

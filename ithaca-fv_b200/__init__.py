@@ -32,7 +32,7 @@ SYMBOLS = [
     "ithaca_b200_partition_create", "ithaca_b200_partition_destroy", "ithaca_b200_partition_sizes",
     "ithaca_b200_partition_addressing", "ithaca_b200_partition_gather", "ithaca_b200_mesh_upload_shard",
     "ithaca_b200_mesh_set_owned", "ithaca_b200_mesh_renumbering",
-    "ithaca_b200_mesh_set_schemes",
+    "ithaca_b200_mesh_set_schemes", "ithaca_b200_mesh_set_convection",
     "ithaca_b200_save_dense_matrix", "ithaca_b200_read_dense_matrix", "ithaca_b200_save_dense_tensor",
     "ithaca_b200_read_dense_tensor", "ithaca_b200_save_npy", "ithaca_b200_export_matrix", "ithaca_b200_export_tensor",
 ]
@@ -107,6 +107,7 @@ def lib():
         L.ithaca_b200_mesh_upload_shard.argtypes = [P, P] + [P] * 10
         L.ithaca_b200_mesh_set_owned.argtypes = [P, L64]
         L.ithaca_b200_mesh_set_schemes.argtypes = [P, D, D, P, P]
+        L.ithaca_b200_mesh_set_convection.argtypes = [P, I]
         C = ctypes.c_char_p
         L.ithaca_b200_save_dense_matrix.argtypes = [C, P, L64, L64]
         L.ithaca_b200_read_dense_matrix.argtypes = [C, ctypes.POINTER(L64), ctypes.POINTER(L64), P, L64]
@@ -509,6 +510,12 @@ class Projector:
         c = lambda a: None if a is None else np.ascontiguousarray(a, dtype=np.float64)
         C, Cf = c(C), c(Cf)
         self.pod._chk(self.L.ithaca_b200_mesh_set_schemes(self.h, float(grad_limit_k), float(sngrad_psi), _ptr(C), _ptr(Cf)))
+
+    def set_convection(self, scheme="linear"):
+        """divSchemes 'Gauss linear | upwind | linearUpwind grad(U)' of fvc::div(phi, U_k)."""
+        if scheme not in ("linear", "upwind", "linearUpwind"):
+            raise IthacaB200Error("unknown convection scheme " + str(scheme))
+        self.pod._chk(self.L.ithaca_b200_mesh_set_convection(self.h, {"linear": 0, "upwind": 1, "linearUpwind": 2}[scheme]))
 
     def set_mesh_shard(self, mesh, part, corrected=True):
         """Upload `part`'s shard of the GLOBAL mesh; set_basis then takes shard fields (part.gather) and project()

@@ -46,6 +46,7 @@ struct MeshDev {
     const int *entL, *otherL;     // the CSR entries of each cell in the CALLER's face order (the limiter is order dependent)
     const double *Cc, *Cf;        // cell / face centres, internal order
     double limK, snPsi;
+    int conv;                     // convection interpolation of fvc::div(phi, U): 0 linear, 1 upwind, 2 linearUpwind grad(U)
 };
 
 struct ProjState {
@@ -60,6 +61,9 @@ struct ProjState {
     DevBuf fperm;   // original index of the internal face at each new position (int, nInt)
     DevBuf entL, otherL, Cc, Cf;   // cellMDLimited gradient limiter (mesh_set_schemes)
     double limK = 0.0, snPsi = -1.0;
+    int convScheme = 0;
+    bool have_centres = false, have_Tall = false;
+    DevBuf Tall;   // grad(U_k) of all basis fields (linearUpwind), component-major per field like T
     DevBuf stage;   // one field in the caller's order (upload / fvc_eval staging)
     int nU = 0, nP = 0;
     long long ldU = 0, ldUb = 0, ldP = 0, ldPb = 0, ldF = 0;
@@ -103,7 +107,7 @@ void proj_destroy(ithaca_b200* h)
     if (!s) return;
     for (DevBuf* b : {&s->owner, &s->neigh, &s->Sf, &s->magSf, &s->w, &s->dc, &s->dcB, &s->corr, &s->V, &s->bmask,
                       &s->off, &s->ent, &s->other, &s->cnt, &s->blocksum, &s->U, &s->Ub, &s->P, &s->Pb, &s->flux,
-                      &s->owner0, &s->neigh0, &s->off0, &s->ent0, &s->other0, &s->entL, &s->otherL, &s->Cc, &s->Cf, &s->perm, &s->fperm, &s->stage, &s->Vw, &s->cmask, &s->Tcm, &s->Lcm, &s->gradP, &s->bndA, &s->bndB,
+                      &s->owner0, &s->neigh0, &s->off0, &s->ent0, &s->other0, &s->entL, &s->otherL, &s->Cc, &s->Cf, &s->Tall, &s->perm, &s->fperm, &s->stage, &s->Vw, &s->cmask, &s->Tcm, &s->Lcm, &s->gradP, &s->bndA, &s->bndB,
                       &s->work, &s->T, &s->out, &s->conv.Ucm, &s->conv.Ubcm, &s->conv.Dcm, &s->conv.Aj, &s->conv.Bk, &s->conv.Dd,
                       &s->conv.ws, &s->conv.chunks})
         if (b->p) cudaFree(b->p);
@@ -123,6 +127,7 @@ static MeshDev mesh_dev(const ProjState* s)
     m.off = s->off.as<int>(); m.ent = s->ent.as<int>(); m.other = s->other.as<int>();
     m.entL = s->entL.as<int>(); m.otherL = s->otherL.as<int>(); m.Cc = s->Cc.as<double>(); m.Cf = s->Cf.as<double>();
     m.limK = s->limK; m.snPsi = s->corrected ? s->snPsi : -1.0;
+    m.conv = s->convScheme;
     return m;
 }
 
@@ -411,10 +416,31 @@ face_flux_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const d
 // K6: out_k = fvc::div(phi, U_k) = surfaceIntegrate(phi * linearInterpolate(U_k)), FB fields k per thread,
 // one thread per cell walking the cell's CSR segment (OpenFOAM's summation order, then / V).
 // ------------------------------------------------------------------------------------------------
+// CONV selects the interpolation of U_k onto the internal faces (divSchemes "Gauss <scheme>"; boundary faces always take
+// the patch value): 0 linear; 1 upwind (owner value when phi >= 0, upwind::weights = pos0(faceFlux)); 2 linearUpwind
+// grad(U): upwind value + (Cf - C_upwind) . grad(U_k)[upwind] (linearUpwind::correction), grad from Tall.
+template <int CONV>
+__device__ __forceinline__ double conv_face_value(const MeshDev& m, long long f, bool own, double ph, double w, double w1, double vc, double vn,
+                                                  long long c, long long ot, const double* __restrict__ tk, long long ldc, int d)
+{
+    if (CONV == 0) return own ? (w * vc + w1 * vn) : (w * vn + w1 * vc);
+    const bool up_is_c = (ph >= 0.0) == own;
+    double v = up_is_c ? vc : vn;
+    if (CONV == 2) {
+        const long long u = up_is_c ? c : ot;
+        const double dx = m.Cf[3 * f] - m.Cc[3 * u], dy = m.Cf[3 * f + 1] - m.Cc[3 * u + 1], dz = m.Cf[3 * f + 2] - m.Cc[3 * u + 2];
+        v += dx * tk[(size_t)d * ldc + u] + dy * tk[(size_t)(3 + d) * ldc + u] + dz * tk[(size_t)(6 + d) * ldc + u];
+    }
+    return v;
+}
+
+template <int CONV>
 __global__ void __launch_bounds__(PROJ_T)
 div_phi_kernel(MeshDev m, const double* __restrict__ phi, const double* __restrict__ U, long long ldU,
-               const double* __restrict__ Ub, long long ldUb, int nk, double* __restrict__ out, long long ldo)
+               const double* __restrict__ Ub, long long ldUb, int nk, double* __restrict__ out, long long ldo,
+               const double* __restrict__ Tall, long long ldT)
 {
+    const long long ldc = ldT / 9;
     const long long c = blockIdx.x * (long long)PROJ_T + threadIdx.x;
     if (c >= m.nCells) return;
     const int k0 = blockIdx.y * FB;
@@ -437,10 +463,11 @@ div_phi_kernel(MeshDev m, const double* __restrict__ phi, const double* __restri
             for (int kk = 0; kk < FB; kk++) {
                 const int k = min(k0 + kk, nk - 1);
                 const double* un = U + (size_t)k * ldU + 3 * (size_t)ot;
+                const double* tk = CONV == 2 ? Tall + (size_t)k * ldT : nullptr;
 #pragma unroll
                 for (int d = 0; d < 3; d++) {
                     const double x = un[d];
-                    const double uf = own ? (w * uc[kk][d] + w1 * x) : (w * x + w1 * uc[kk][d]);
+                    const double uf = conv_face_value<CONV>(m, f, own, ph, w, w1, uc[kk][d], x, c, ot, tk, ldc, d);
                     const double v = ph * uf;
                     acc[kk][d] += own ? v : -v;
                 }
@@ -812,11 +839,13 @@ bnd_owner_dot_sf_kernel(MeshDev m, const unsigned char* __restrict__ cmask, cons
 // Db[k][b] = fvc::div(phi, U_k)[owner(b)] . Sf_b for the boundary faces b (BC2 = Pb^T Db per flux field): the div(phi_j, U_k)
 // value of the owner cell is recomputed from the cell's CSR segment with div_phi_kernel's own arithmetic (same order, same
 // rounding), so only the N_b boundary-owner cells are visited instead of materialising N^2 whole div fields.
+template <int CONV>
 __global__ void __launch_bounds__(PROJ_T)
 bnd_div_phi_dot_sf_kernel(MeshDev m, const unsigned char* __restrict__ cmask, const double* __restrict__ phi,
                           const double* __restrict__ U, long long ldU, const double* __restrict__ Ub, long long ldUb, int nk,
-                          double* __restrict__ out, long long ldo)
+                          double* __restrict__ out, long long ldo, const double* __restrict__ Tall, long long ldT)
 {
+    const long long ldc = ldT / 9;
     const long long bf = blockIdx.x * (long long)PROJ_T + threadIdx.x;
     if (bf >= m.nBnd) return;
     const int k0 = blockIdx.y * FB;
@@ -847,10 +876,11 @@ bnd_div_phi_dot_sf_kernel(MeshDev m, const unsigned char* __restrict__ cmask, co
             for (int kk = 0; kk < FB; kk++) {
                 const int k = min(k0 + kk, nk - 1);
                 const double* un = U + (size_t)k * ldU + 3 * (size_t)ot;
+                const double* tk = CONV == 2 ? Tall + (size_t)k * ldT : nullptr;
 #pragma unroll
                 for (int d = 0; d < 3; d++) {
                     const double x = un[d];
-                    const double uf = own ? (w * uc[kk][d] + w1 * x) : (w * x + w1 * uc[kk][d]);
+                    const double uf = conv_face_value<CONV>(m, f, own, ph, w, w1, uc[kk][d], x, c, ot, tk, ldc, d);
                     const double v = ph * uf;
                     acc[kk][d] += own ? v : -v;
                 }
@@ -1272,6 +1302,37 @@ static int need_flux(ithaca_b200* h, ProjState* s)
     return IB200_OK;
 }
 
+// grad(U_k) of ALL basis fields for the linearUpwind correction (limited when the cellMDLimited gradient is selected, as the
+// scheme's "grad(U)" argument names the case's gradient scheme)
+static int need_gradU_all(ithaca_b200* h, ProjState* s)
+{
+    if (s->convScheme != 2 || s->have_Tall) return IB200_OK;
+    const long long ldT = 9 * pad16(s->nCells);
+    int rc = ensure(h, s->Tall, (size_t)s->nU * ldT * sizeof(double));
+    if (rc) return rc;
+    const MeshDev m = mesh_dev(s);
+    if (s->limK > 0.0)
+        grad_vec_kernel<true><<<gx(s->nCells) * s->nU, PROJ_T, 0, h->stream>>>(m, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb, 0, s->nU,
+                                                                                s->Tall.as<double>(), ldT);
+    else
+        grad_vec_kernel<false><<<gx(s->nCells) * s->nU, PROJ_T, 0, h->stream>>>(m, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb, 0, s->nU,
+                                                                                 s->Tall.as<double>(), ldT);
+    h->launches += 1;
+    IB_CUDA(h, cudaGetLastError());
+    s->have_Tall = true;
+    return IB200_OK;
+}
+// one launch of K (div_phi_kernel or its boundary-owner twin) with the convection scheme of the mesh
+#define LAUNCH_DIV_PHI(K, GRID, ...)                                                                                              \
+    do {                                                                                                                          \
+        int rc_ldp_ = need_gradU_all(h, s);                                                                                       \
+        if (rc_ldp_) return rc_ldp_;                                                                                              \
+        const long long ldT_ldp_ = 9 * pad16(s->nCells);                                                                          \
+        if (s->convScheme == 2) K<2><<<GRID, PROJ_T, 0, h->stream>>>(__VA_ARGS__, s->Tall.as<double>(), ldT_ldp_);                      \
+        else if (s->convScheme == 1) K<1><<<GRID, PROJ_T, 0, h->stream>>>(__VA_ARGS__, nullptr, 0);                                     \
+        else K<0><<<GRID, PROJ_T, 0, h->stream>>>(__VA_ARGS__, nullptr, 0);                                                       \
+    } while (0)
+
 // laplacian(1, U_j) for j in [0, nU) into `out` (columns of ldU doubles)
 static int run_laplacians(ithaca_b200* h, ProjState* s, double* out)
 {
@@ -1462,6 +1523,21 @@ int ithaca_b200_mesh_upload(ithaca_b200_t* h, int64_t nCells, int64_t nIntFaces,
     s->nU = s->nP = 0;
     s->limK = 0.0;     // a new mesh starts with the "Gauss linear" / "corrected" scheme set
     s->snPsi = -1.0;
+    s->convScheme = 0;
+    s->have_centres = s->have_Tall = false;
+    return IB200_OK;
+}
+
+int ithaca_b200_mesh_set_convection(ithaca_b200_t* h, int scheme)
+{
+    if (!h) return IB200_ERR_ARG;
+    ProjState* s = h->proj;
+    PROJ_REQUIRE(s && s->have_mesh, "mesh_set_convection: no mesh uploaded");
+    PROJ_REQUIRE(scheme >= IB200_CONV_LINEAR && scheme <= IB200_CONV_LINEAR_UPWIND, "mesh_set_convection: unknown interpolation scheme");
+    PROJ_REQUIRE(scheme != IB200_CONV_LINEAR_UPWIND || s->have_centres,
+                 "mesh_set_convection: linearUpwind needs mesh.C() and mesh.Cf() (pass them to mesh_set_schemes first)");
+    s->convScheme = scheme;
+    s->have_Tall = false;
     return IB200_OK;
 }
 
@@ -1477,7 +1553,8 @@ int ithaca_b200_mesh_set_schemes(ithaca_b200_t* h, double grad_limit_k, double s
     const bool lim = grad_limit_k >= 1e-15;
     PROJ_REQUIRE(!lim || (C && Cf), "mesh_set_schemes: the cellMDLimited gradient needs mesh.C() and mesh.Cf()");
     cudaSetDevice(h->device);
-    if (lim) {
+    s->have_Tall = false;
+    if (C && Cf) {
         const long long nC = s->nCells, nF = s->nInt + s->nBnd, nnz = 2 * s->nInt + s->nBnd;
         int rc;
         DevBuf C0, Cf0;
@@ -1502,6 +1579,7 @@ int ithaca_b200_mesh_set_schemes(ithaca_b200_t* h, double grad_limit_k, double s
         drop();
         IB_CUDA(h, e);
         IB_CUDA(h, cudaGetLastError());
+        s->have_centres = true;
     }
     s->limK = lim ? grad_limit_k : 0.0;
     s->snPsi = sngrad_psi >= 0.0 ? sngrad_psi : -1.0;
@@ -1586,7 +1664,7 @@ int ithaca_b200_basis_upload(ithaca_b200_t* h, int which, const double* const* i
                                        cudaMemcpyDefault, h->stream));
     }
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
-    if (which == 0) { s->nU = n; s->ldU = ld; s->ldUb = ldb; s->ldF = pad16(s->nInt + s->nBnd); s->have_flux = false; }
+    if (which == 0) { s->nU = n; s->ldU = ld; s->ldUb = ldb; s->ldF = pad16(s->nInt + s->nBnd); s->have_flux = false; s->have_Tall = false; }
     else { s->nP = n; s->ldP = ld; s->ldPb = ldb; }
     return IB200_OK;
 }
@@ -1619,7 +1697,7 @@ int ithaca_b200_fvc_eval(ithaca_b200_t* h, int op, int j, int k, double* out)
         PROJ_REQUIRE(j >= 0 && j < s->nU && k >= 0 && k < s->nU, "fvc_eval: field index out of range");
         if ((rc = need_flux(h, s))) return rc;
         if ((rc = ensure(h, s->work, (size_t)s->nU * s->ldU * sizeof(double)))) return rc;
-        div_phi_kernel<<<dim3(gx(s->nCells), gy(s->nU)), PROJ_T, 0, h->stream>>>(
+        LAUNCH_DIV_PHI(div_phi_kernel, dim3(gx(s->nCells), gy(s->nU)), 
             m, s->flux.as<double>() + (size_t)j * s->ldF, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb, s->nU,
             s->work.as<double>(), s->ldU);
         h->launches += 1;
@@ -1750,7 +1828,9 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
         if (rc) return rc;
         break;
     }
-    case IB200_OP_C: {  // convective_term_tens (== _cache), steadyNS.C:997-1083, fused face-based contraction (conv.cu)
+    case IB200_OP_C:    // convective_term_tens (== _cache), steadyNS.C:997-1083, fused face-based contraction (conv.cu)
+        if (s->convScheme != 0) goto materialised_C;   // the fused form is the LINEAR face value; other schemes take the div fields
+    {
         nout = (size_t)N * N * N;
         if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
         ConvMesh cm;
@@ -1761,6 +1841,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
         if (rc) return rc;
         break;
     }
+    materialised_C:
     case IB200_OP_C_MATERIALISED: {  // same tensor through materialised div(phi_j, U_k) fields + cell-based contraction
         nout = (size_t)N * N * N;
         if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
@@ -1773,7 +1854,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
             {
                 StageTimer t(h->stream, &s->ms[1]);
                 for (int jj = 0; jj < nj; jj++) {
-                    div_phi_kernel<<<dim3(gx(s->nCells), gy(N)), PROJ_T, 0, h->stream>>>(
+                    LAUNCH_DIV_PHI(div_phi_kernel, dim3(gx(s->nCells), gy(N)), 
                         m, s->flux.as<double>() + (size_t)(j0 + jj) * s->ldF, U, s->ldU, s->Ub.as<double>(), s->ldUb, N,
                         s->work.as<double>() + (size_t)jj * N * s->ldU, s->ldU);
                     h->launches += 1;
@@ -1821,7 +1902,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
         // fused face-based form (conv.cu), as for C: G(i,j,k) = sum_f flux_j(f) (Uf_k(f) . (g_i[own] - g_i[nei])), g_i = grad(P_i);
         // ITHACA_B200_G=mat keeps the materialised div(phi_j, U_k) fields (cross-check)
         const char* gev = getenv("ITHACA_B200_G");
-        if (Np <= N && !(gev && strcmp(gev, "mat") == 0)) {
+        if (Np <= N && !(gev && strcmp(gev, "mat") == 0) && s->convScheme == 0) {
             ConvMesh cm;
             cm.nInt = s->nInt; cm.nBnd = s->nBnd; cm.owner = m.owner; cm.neigh = m.neigh; cm.Sf = m.Sf; cm.w = m.w; cm.bmask = m.bmask;
             cm.cmask = shard ? s->cmask.as<unsigned char>() : nullptr;
@@ -1839,7 +1920,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
             {
                 StageTimer t(h->stream, &s->ms[1]);
                 for (int jj = 0; jj < nj; jj++) {
-                    div_phi_kernel<<<dim3(gx(s->nCells), gy(N)), PROJ_T, 0, h->stream>>>(
+                    LAUNCH_DIV_PHI(div_phi_kernel, dim3(gx(s->nCells), gy(N)), 
                         m, s->flux.as<double>() + (size_t)(j0 + jj) * s->ldF, U, s->ldU, s->Ub.as<double>(), s->ldUb, N,
                         s->work.as<double>() + (size_t)jj * N * s->ldU, s->ldU);
                     h->launches += 1;
@@ -1938,7 +2019,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
                 {
                     StageTimer t(h->stream, &s->ms[1]);
                     for (int jj = 0; jj < nj; jj++) {
-                        bnd_div_phi_dot_sf_kernel<<<dim3(gx(s->nBnd), gy(N)), PROJ_T, 0, h->stream>>>(
+                        LAUNCH_DIV_PHI(bnd_div_phi_dot_sf_kernel, dim3(gx(s->nBnd), gy(N)), 
                             m, shard ? s->cmask.as<unsigned char>() : nullptr, s->flux.as<double>() + (size_t)(j0 + jj) * s->ldF, U, s->ldU,
                             s->Ub.as<double>(), s->ldUb, N, s->bndA.as<double>() + (size_t)jj * N * ldB, ldB);
                         h->launches += 1;
@@ -1959,6 +2040,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
     case IB200_OP_CF: {  // convective_term_flux_tens, steadyNS.C:1704-1746: Np x N x N, int P_i div(div(flux(U_j), U_k)), i fastest
         // both through the adjoint of the outer div (div_adjoint_kernel): int P_i div(A) = int t_i . A, so BP is one
         // contraction against the laplacian fields and Cf is the fused face-based contraction of G with t_i as test fields
+        PROJ_REQUIRE(op == IB200_OP_BP || s->convScheme == 0, "project(Cf): only built for the linear convection scheme (the fused contraction)");
         nout = op == IB200_OP_BP ? (size_t)Np * N : (size_t)Np * N * N;
         if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
         if ((rc = ensure(h, s->gradP, (size_t)Np * s->ldU * sizeof(double)))) return rc;
@@ -1995,7 +2077,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
         for (int j0 = 0; j0 < N; j0 += jb) {
             const int nj = std::min(jb, N - j0);
             for (int jj = 0; jj < nj; jj++) {
-                div_phi_kernel<<<dim3(gx(s->nCells), gy(N)), PROJ_T, 0, h->stream>>>(
+                LAUNCH_DIV_PHI(div_phi_kernel, dim3(gx(s->nCells), gy(N)), 
                     m, s->flux.as<double>() + (size_t)(j0 + jj) * s->ldF, U, s->ldU, s->Ub.as<double>(), s->ldUb, N,
                     s->work.as<double>() + (size_t)jj * N * s->ldU, s->ldU);
                 h->launches += 1;
@@ -2094,7 +2176,7 @@ int ithaca_b200_project_background(ithaca_b200_t* h, int kind, const double* vls
     }
     {
         StageTimer t(h->stream, &s->ms[1]);
-        div_phi_kernel<<<dim3(gx(s->nCells), gy(N)), PROJ_T, 0, h->stream>>>(m, phi, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb, N,
+        LAUNCH_DIV_PHI(div_phi_kernel, dim3(gx(s->nCells), gy(N)), m, phi, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb, N,
                                                                              s->work.as<double>(), s->ldU);
         t.stop();
     }

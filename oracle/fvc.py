@@ -16,7 +16,7 @@ class _Mesh(ctypes.Structure):
     _fields_ = [("nCells", ctypes.c_longlong), ("nInt", ctypes.c_longlong), ("nBnd", ctypes.c_longlong),
                 ("owner", P), ("neighbour", P), ("Sf", P), ("magSf", P), ("w", P), ("dc", P), ("dcB", P),
                 ("corr", P), ("V", P), ("bmask", P), ("Cc", P), ("Cf", P), ("gradK", ctypes.c_double),
-                ("snPsi", ctypes.c_double)]
+                ("snPsi", ctypes.c_double), ("convScheme", ctypes.c_int)]
 
 
 def lib():
@@ -35,7 +35,7 @@ def _c(a, dt=np.float64):
 class Oracle:
     """Holds the C mesh struct (and keeps the numpy arrays it points into alive)."""
 
-    def __init__(self, mesh, corrected=True, grad_limit_k=0.0, sngrad_psi=-1.0):
+    def __init__(self, mesh, corrected=True, grad_limit_k=0.0, sngrad_psi=-1.0, convection="linear"):
         """grad_limit_k > 0: gradSchemes 'cellMDLimited Gauss linear k'; sngrad_psi >= 0: snGrad 'limited psi'
         (tutorials/CFD/04unsteadyNS/system/fvSchemes); defaults = the 'Gauss linear' / 'corrected' set."""
         self.mesh = mesh
@@ -43,12 +43,12 @@ class Oracle:
                          magSf=_c(mesh.magSf), w=_c(mesh.w), dc=_c(mesh.dc), dcB=_c(mesh.dcB), corr=_c(mesh.corr),
                          V=_c(mesh.V), bmask=_c(mesh.bmask, np.uint8), Cc=_c(getattr(mesh, "Cc", np.zeros(3))), Cf=_c(getattr(mesh, "Cf", np.zeros(3))))
         k = self.keep
-        assert not grad_limit_k > 0 or (k["Cc"].size == 3 * mesh.nCells and k["Cf"].size == 3 * (mesh.nInt + mesh.nBnd))
+        assert not (grad_limit_k > 0 or convection == "linearUpwind") or (k["Cc"].size == 3 * mesh.nCells and k["Cf"].size == 3 * (mesh.nInt + mesh.nBnd))
         self.m = _Mesh(mesh.nCells, mesh.nInt, mesh.nBnd, k["owner"].ctypes.data, k["neighbour"].ctypes.data,
                        k["Sf"].ctypes.data, k["magSf"].ctypes.data, k["w"].ctypes.data, k["dc"].ctypes.data,
                        k["dcB"].ctypes.data, k["corr"].ctypes.data if corrected else None, k["V"].ctypes.data,
                        k["bmask"].ctypes.data, k["Cc"].ctypes.data, k["Cf"].ctypes.data, float(grad_limit_k),
-                       float(sngrad_psi))
+                       float(sngrad_psi), {"linear": 0, "upwind": 1, "linearUpwind": 2}[convection])
         self.L = lib()
 
     def _ref(self):

@@ -49,7 +49,10 @@ typedef struct {
     const double* Cf;      /* 3*(nInt+nBnd) face centres mesh.Cf() */
     double gradK;          /* > 0: gradSchemes "cellMDLimited Gauss linear <gradK>"; <= 0: "Gauss linear" */
     double snPsi;          /* >= 0: snGrad "limited <snPsi>" (needs corr); < 0: "corrected" / "uncorrected" */
+    int convScheme;        /* divSchemes "Gauss <scheme>" of fvc::div(phi, U): 0 linear, 1 upwind, 2 linearUpwind grad(U) */
 } fvo_mesh;
+
+void fvo_grad_vec(const fvo_mesh* m, const double* U, const double* Ub, double* out);
 
 /* cellMDLimited gradient limiter (OpenFOAM finiteVolume/gradSchemes/limitedGradSchemes/cellMDLimitedGrad:
  * cellMDLimitedGrads.C calcGrad + cellMDLimitedGrad.H limitFaceCmpt), applied in place to the Gauss linear cell
@@ -142,16 +145,36 @@ void fvo_flux(const fvo_mesh* m, const double* U, const double* Ub, double* phi)
 /* out = fvc::div(phi, U) with Gauss linear: surfaceIntegrate(phi * linearInterpolate(U)). out: 3*nCells. */
 void fvo_div_phi_vec(const fvo_mesh* m, const double* phi, const double* U, const double* Ub, double* out)
 {
+    /* face value of U by the convection scheme (OpenFOAM interpolation/surfaceInterpolation):
+     *   linear        schemes/linear/linear.H            w U[own] + (1 - w) U[nei]
+     *   upwind        limitedSchemes/upwind/upwind.H     weights = pos0(faceFlux): U[own] when phi >= 0, else U[nei]
+     *   linearUpwind  schemes/linearUpwind/linearUpwind.C  upwind + correction, correction = (Cf - C[up]) & grad(U)[up]
+     *                 (faceFlux > 0 ? owner : neighbour; at phi == 0 the product phi * U_f vanishes anyway), grad(U) by the
+     *                 gradient scheme the dictionary entry names ("linearUpwind grad(U)") */
+    double* T = NULL;
+    if (m->convScheme == 2) {
+        T = (double*)malloc(sizeof(double) * 9 * m->nCells);
+        fvo_grad_vec(m, U, Ub, T);
+    }
     memset(out, 0, sizeof(double) * 3 * m->nCells);
     for (long long f = 0; f < m->nInt; f++) {
         const int o = m->owner[f], n = m->neighbour[f];
         const double w = m->w[f];
+        const int up = phi[f] >= 0.0 ? o : n;
         for (int c = 0; c < 3; c++) {
-            const double v = phi[f] * (w * U[3 * o + c] + (1.0 - w) * U[3 * n + c]);
+            double uf;
+            if (m->convScheme == 0) uf = w * U[3 * o + c] + (1.0 - w) * U[3 * n + c];
+            else {
+                uf = U[3 * up + c];
+                if (T)
+                    for (int i = 0; i < 3; i++) uf += (m->Cf[3 * f + i] - m->Cc[3 * up + i]) * T[9 * up + 3 * i + c];
+            }
+            const double v = phi[f] * uf;
             out[3 * o + c] += v;
             out[3 * n + c] -= v;
         }
     }
+    free(T);
     for (long long b = 0; b < m->nBnd; b++) {
         if (!m->bmask[b]) continue;
         const int o = m->owner[m->nInt + b];

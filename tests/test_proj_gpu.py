@@ -314,3 +314,48 @@ def test_sharded_projection_with_limited_schemes(pkg, pod):
         part.close()
     for k in acc:
         assert rel(acc[k], ref[k]) <= TOL, k
+
+
+@pytest.mark.parametrize("name,scheme,k", [("tutorial04", "upwind", 0.0), ("cyl", "linearUpwind", 0.0), ("box", "linearUpwind", 1.0)])
+def test_upwind_and_linear_upwind_convection_match_oracle(pkg, pod, name, scheme, k):
+    """divSchemes 'Gauss upwind' / 'Gauss linearUpwind grad(U)' (SURVEY 8(f) rank 4): the div field, C and G (formed through
+    materialised div fields: the fused contraction is the linear face value), BC2 and the background terms follow the scheme;
+    linearUpwind takes its gradient from the selected gradient scheme (k = 1: cellMDLimited)."""
+    mesh = meshes()[name]()
+    U, Ub, P, Pb = fvc.synthetic_basis(mesh, 6, 3, seed=23)
+    rng = np.random.default_rng(6)
+    U = [u + 0.1 * rng.standard_normal(u.shape) for u in U]
+    pr = pkg.Projector(pod)
+    pr.set_mesh(mesh, corrected=True)
+    pr.set_schemes(grad_limit_k=k, C=mesh.Cc, Cf=mesh.Cf)
+    pr.set_convection(scheme)
+    pr.set_basis("U", U, Ub)
+    pr.set_basis("P", P, Pb)
+    orc = fvc.Oracle(mesh, corrected=True, grad_limit_k=k, convection=scheme)
+    lin = fvc.Oracle(mesh, corrected=True, grad_limit_k=k)
+    phi = orc.flux(U[2], Ub[2])
+    d = orc.div_phi(phi, U[4], Ub[4])
+    assert rel(pr.fvc("div_phi", 2, 4), d) <= 1e-12
+    assert rel(d, lin.div_phi(phi, U[4], Ub[4])) > 1e-3
+    Cr = orc.convective_term_tens(U, Ub, cache=True)
+    assert rel(pr.project("C"), Cr) <= TOL and rel(pr.project("Cmat"), Cr) <= TOL
+    assert rel(Cr, lin.convective_term_tens(U, Ub, cache=True)) > 1e-4
+    assert rel(pr.project("G"), orc.div_momentum(U, Ub, P, Pb)) <= TOL
+    assert rel(pr.project("BC2"), orc.pressure_bc2(U, Ub, Pb)) <= TOL
+    vls, vlsb = U[1] + 0.5 * U[2], Ub[1] + 0.5 * Ub[2]
+    assert rel(pr.project_background(vls, vlsb), orc.convective_background(U, Ub, vls, vlsb)) <= TOL
+    with pytest.raises(pkg.IthacaB200Error, match="linear convection scheme"):
+        pr.project("Cf")
+    # operators without a convection term are untouched; back to linear restores the fused path
+    assert rel(pr.project("B"), lin.diffusive_term(U, Ub)) <= TOL
+    pr.set_convection("linear")
+    assert rel(pr.project("C"), lin.convective_term_tens(U, Ub, cache=True)) <= TOL
+
+
+def test_linear_upwind_needs_centres(pkg, pod):
+    mesh = meshes()["box"]()
+    pr = pkg.Projector(pod)
+    pr.set_mesh(mesh, corrected=True)
+    with pytest.raises(pkg.IthacaB200Error, match="needs mesh.C"):
+        pr.set_convection("linearUpwind")
+    pr.set_convection("upwind")
