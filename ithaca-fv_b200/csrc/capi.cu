@@ -210,7 +210,7 @@ int ithaca_b200_destroy(ithaca_b200_t* h)
     if (h->nccl_comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->nccl_comm);
     for (void* p : {(void*)h->dV, (void*)h->dS, (void*)h->dG, (void*)h->dWs, (void*)h->dQ, (void*)h->dW,
                     (void*)h->dEvals, (void*)h->dQr, (void*)h->dPhi, (void*)h->dNormPart, (void*)h->dNorm,
-                    h->dJobs, (void*)h->dFlags, h->wexp[0].p, h->wexp[1].p, (void*)h->dS2, (void*)h->dPhiTmp, h->volT.p})
+                    h->dJobs, (void*)h->dFlags, h->wexp[0].p, h->wexp[1].p, (void*)h->dS2, (void*)h->dPhiTmp, h->volT.p, h->eigTmp.p})
         if (p) cudaFree(p);
     for (int i = 0; i < T_COUNT; i++) {
         cudaEventDestroy(h->timers[i].a);

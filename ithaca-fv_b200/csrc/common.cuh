@@ -225,6 +225,7 @@ struct ithaca_b200 {
     unsigned long long vol_gen = 1;  // bumped whenever a volume vector on the device may have changed
     int wexp_next = 0;
     int* dFlags = nullptr;
+    ib200::DevBuf eigTmp; // eigensolve: m unsorted eigenvalues + 2 bounds
     ib200::DevBuf volT;   // pod_gram_volumes: the snapshot matrix scaled row-wise by sqrt|V_j|
 
     // ---- projection state (proj.cu) ----

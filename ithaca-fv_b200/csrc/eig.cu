@@ -49,29 +49,68 @@ __global__ void eig_init_kernel(const double* __restrict__ G, double* __restrict
     }
 }
 
-// max diagonal entry and Gershgorin bound max_i (sum_{j != i} |G_ij| - G_ii): out[0], out[1]. One block.
-__global__ void eig_bounds_kernel(const double* __restrict__ G, int m, double* __restrict__ out)
+// max diagonal entry and Gershgorin bound max_i (sum_{j != i} |G_ij| - G_ii): out[0], out[1]. One block; one warp per
+// column (G is symmetric: column i is row i), lanes over the contiguous rows.
+__global__ void __launch_bounds__(1024) eig_bounds_kernel(const double* __restrict__ G, int m, double* __restrict__ out)
 {
     __shared__ double sd[32], sg[32];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
     double dmax = -1e300, gmax = -1e300;
-    for (int i = threadIdx.x; i < m; i += blockDim.x) {
+    for (int i = w; i < m; i += nw) {
+        const double* col = G + (size_t)i * m;
         double s = 0.0;
-        for (int j = 0; j < m; j++) if (j != i) s += fabs(G[(size_t)i + (size_t)j * m]);
-        const double d = G[(size_t)i + (size_t)i * m];
+        for (int j = lane; j < m; j += 32) if (j != i) s += fabs(col[j]);
+        s = warp_sum(s);
+        const double d = col[i];
         dmax = fmax(dmax, fabs(d));
         gmax = fmax(gmax, s - d);
     }
-    for (int o = 16; o > 0; o >>= 1) {
-        dmax = fmax(dmax, __shfl_xor_sync(0xffffffffu, dmax, o));
-        gmax = fmax(gmax, __shfl_xor_sync(0xffffffffu, gmax, o));
-    }
-    if ((threadIdx.x & 31) == 0) { sd[threadIdx.x >> 5] = dmax; sg[threadIdx.x >> 5] = gmax; }
+    if (lane == 0) { sd[w] = dmax; sg[w] = gmax; }
     __syncthreads();
     if (threadIdx.x == 0) {
-        for (int w = 1; w < (int)(blockDim.x >> 5); w++) { sd[0] = fmax(sd[0], sd[w]); sg[0] = fmax(sg[0], sg[w]); }
+        for (int k = 1; k < nw; k++) { sd[0] = fmax(sd[0], sd[k]); sg[0] = fmax(sg[0], sg[k]); }
         out[0] = sd[0];
         out[1] = sg[0];
     }
+}
+
+// ---- small matrices: init + Cholesky in ONE single-CTA launch ------------------------------------------------------
+// X = chol(lower(scale G) + sigma I) (lower factor, strict upper triangle = 0), right-looking, unblocked, on the packed lower
+// triangle in shared memory: replaces eig_init_kernel + the 3 m / CH_B launches of the blocked factorisation.
+// Measured (scripts/eig_bench.py, whole eigensolve): m = 100 1.265 ms against 1.284 ms blocked; m = 200 2.73 ms against 2.66 ms
+// (three block-wide barriers per column cost more than the blocked path's launch gaps), so it serves m <= CHS_MAX = 128.
+// flag[0] = 1 on a non-positive (or NaN) pivot (X is then unspecified; the caller retries with a shift).
+constexpr int CHS_MAX = 128;
+__global__ void __launch_bounds__(1024) chol_small_kernel(const double* __restrict__ G, double* __restrict__ X, int m, double sigma,
+                                                          double scale, int* __restrict__ flag)
+{
+    extern __shared__ double A[];   // column j at off(j) = j m - j (j - 1) / 2, rows j..m-1
+    __shared__ int bad;
+    const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, w = tid >> 5, nw = nt >> 5;
+    auto off = [m](int j) { return j * m - (j * (j - 1)) / 2 - j; };   // A[off(j) + i] = element (i, j), i >= j
+    if (tid == 0) bad = 0;
+    for (int j = w; j < m; j += nw)
+        for (int i = j + lane; i < m; i += 32) A[off(j) + i] = scale * G[(size_t)i + (size_t)j * m] + (i == j ? sigma : 0.0);
+    __syncthreads();
+    for (int k = 0; k < m; k++) {
+        const double d = A[off(k) + k];
+        if (!(d > 0.0)) { if (tid == 0) bad = 1; break; }   // uniform: every thread reads the same d
+        const double r = sqrt(d), rinv = 1.0 / r;
+        __syncthreads();                                     // everyone has read d before it is overwritten
+        for (int i = k + tid; i < m; i += nt) A[off(k) + i] = (i == k) ? r : A[off(k) + i] * rinv;
+        __syncthreads();
+        const double* ck = A + off(k);
+        for (int j = k + 1 + w; j < m; j += nw) {
+            const double ljk = ck[j];
+            double* cj = A + off(j);
+            for (int i = j + lane; i < m; i += 32) cj[i] -= ck[i] * ljk;
+        }
+        __syncthreads();
+    }
+    __syncthreads();
+    if (bad) { if (tid == 0) flag[0] = 1; return; }
+    for (int j = w; j < m; j += nw)
+        for (int i = lane; i < m; i += 32) X[(size_t)i + (size_t)j * m] = (i >= j) ? A[off(j) + i] : 0.0;
 }
 
 // ---- blocked right-looking Cholesky, panel width CH_B ------------------------------------------------------------
@@ -486,11 +525,14 @@ int eig_launch(ithaca_b200* h, int* sweeps)
 {
     const int m = h->m;
     const double eps = 2.220446049250313e-16;
-    double* lam_tmp = nullptr;   // m eigenvalues + 2 bounds
-    IB_CUDA(h, cudaMalloc(&lam_tmp, (size_t)(m + 2) * sizeof(double)));
-    auto fail = [&](int rc) { cudaFree(lam_tmp); return rc; };
+    {
+        int rc = dev_ensure(h, h->eigTmp, (size_t)(m + 2) * sizeof(double));   // m eigenvalues + 2 bounds, kept across calls
+        if (rc) return rc;
+    }
+    double* lam_tmp = h->eigTmp.as<double>();
+    auto fail = [&](int rc) { return rc; };
     int* flags = h->dFlags;       // [0..40] sweep counters, [48] Cholesky flag
-    eig_bounds_kernel<<<1, 256, 0, h->stream>>>(h->dG, m, lam_tmp + m);
+    eig_bounds_kernel<<<1, 1024, 0, h->stream>>>(h->dG, m, lam_tmp + m);
     double bounds[2] = {0.0, 0.0};
     if (cudaMemcpyAsync(bounds, lam_tmp + m, 2 * sizeof(double), cudaMemcpyDeviceToHost, h->stream) != cudaSuccess ||
         cudaStreamSynchronize(h->stream) != cudaSuccess) {
@@ -511,6 +553,20 @@ int eig_launch(ithaca_b200* h, int* sweeps)
     for (int attempt = 0; attempt < 3 && !ok; attempt++) {
         sigma = shifts[attempt];
         if (attempt > 0 && !(sigma > shifts[attempt - 1])) continue;
+        const char* evc = getenv("ITHACA_B200_CHOL");   // "blocked" keeps the multi-launch factorisation (A/B measurements)
+        if (m <= CHS_MAX && !(evc && strcmp(evc, "blocked") == 0)) {
+            const size_t csm = (size_t)m * (m + 1) / 2 * sizeof(double);
+            IB_CUDA(h, cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csm));
+            IB_CUDA(h, cudaMemsetAsync(flags + 48, 0, sizeof(int), h->stream));
+            chol_small_kernel<<<1, 1024, csm, h->stream>>>(h->dG, h->dW, m, sigma, scale, flags + 48);
+            h->launches += 1;
+            IB_CUDA(h, cudaGetLastError());
+            int f = 0;
+            IB_CUDA(h, cudaMemcpyAsync(&f, flags + 48, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+            IB_CUDA(h, cudaStreamSynchronize(h->stream));
+            ok = (f == 0);
+            continue;
+        }
         eig_init_kernel<<<ig, ib, 0, h->stream>>>(h->dG, h->dW, m, sigma, scale);
         h->launches += 1;
         int rc = cholesky(h, h->dW, m, flags + 48, &ok);
@@ -576,7 +632,6 @@ int eig_launch(ithaca_b200* h, int* sweeps)
     int hflags[EIG_MAX_SWEEPS + 1];
     IB_CUDA(h, cudaMemcpyAsync(hflags, flags, sizeof(hflags), cudaMemcpyDeviceToHost, h->stream));
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
-    cudaFree(lam_tmp);
     const int done = hflags[EIG_MAX_SWEEPS];
     if (sweeps) *sweeps = done;
     if (done >= EIG_MAX_SWEEPS && hflags[EIG_MAX_SWEEPS - 1] != 0) {

@@ -24,12 +24,12 @@ def main():
     for m in ms:
         G = gram_like(m)
         w_ref = np.linalg.eigvalsh(G)[::-1]
-        variants = [("reg", {}), ("block", {"ITHACA_B200_EIG": "block"})]
+        variants = [("reg", {}), ("reg_chol_blocked", {"ITHACA_B200_CHOL": "blocked"}), ("block", {"ITHACA_B200_EIG": "block"})]
         if m <= 1024:
             for b in (4, 8, 12):
                 variants.append(("reg_b%d" % b, {"ITHACA_B200_EIG_B": str(b)}))
         for name, env in variants:
-            for k in ("ITHACA_B200_EIG", "ITHACA_B200_EIG_B"):
+            for k in ("ITHACA_B200_EIG", "ITHACA_B200_EIG_B", "ITHACA_B200_CHOL"):
                 os.environ.pop(k, None)
             os.environ.update(env)
             pod.set_gram(G)

@@ -396,3 +396,25 @@ def test_nested_snapshot_matrix_cormatrix_and_streamed_mean(pkg, pod):
     mean = pkg.getMeanMemoryEfficient(pod, lambda first, nb: [np.ascontiguousarray(S[:, j]) for j in range(first, first + nb)],
                                       m, V, dim, block=7)
     assert np.abs(mean - S.mean(axis=1)).max() <= 1e-13 * np.abs(S).max()
+
+
+@pytest.mark.parametrize("m", [5, 57, 128, 129])
+def test_small_matrix_cholesky_matches_the_blocked_one(pkg, pod, m, monkeypatch):
+    """m <= 128: init + Cholesky run as ONE single-CTA launch in shared memory (chol_small_kernel); ITHACA_B200_CHOL=blocked
+    keeps the multi-launch blocked factorisation. Same eigenpairs either way (129 takes the blocked path regardless)."""
+    rng = np.random.default_rng(100 + m)
+    A = rng.standard_normal((m + 3, m))
+    G = A.T @ A
+    w = np.linalg.eigvalsh(G)[::-1]
+    out = {}
+    for mode in ("small", "blocked"):
+        if mode == "blocked":
+            monkeypatch.setenv("ITHACA_B200_CHOL", "blocked")
+        else:
+            monkeypatch.delenv("ITHACA_B200_CHOL", raising=False)
+        pod.set_gram(G)
+        ev, Q = pod.eig(m)
+        assert np.abs(ev - w).max() <= 1e-12 * w[0]
+        assert np.abs(G @ Q - Q * ev).max() <= 1e-12 * w[0]
+        out[mode] = ev
+    assert np.abs(out["small"] - out["blocked"]).max() <= 1e-13 * w[0]
