@@ -630,14 +630,21 @@ div_adjoint_kernel(MeshDev m, const double* __restrict__ P, long long ldP, int n
 }
 
 // K7a: T_j = fvc::grad(U_j), Gauss linear: T[c][i][d] = sum_f +-Sf_i * Uf_d / V. One field per block.
-#ifndef GRADV_MINB
-#define GRADV_MINB 1
+// Occupancy experiments: -DGRADV_MINB=n / -DLAP_MINB=n force n CTAs per SM. The default leaves the register count to ptxas
+// (62 / 80 registers, 4 / 3 CTAs per SM): NOT the same as a minimum of 1, which lets ptxas take 78 / 108 registers and costs
+// 2 ms of the 15.4 ms laplacian stage at C4.
+#ifdef GRADV_MINB
+#define GRADV_BOUNDS __launch_bounds__(PROJ_T, GRADV_MINB)
+#else
+#define GRADV_BOUNDS __launch_bounds__(PROJ_T)
 #endif
-#ifndef LAP_MINB
-#define LAP_MINB 1
+#ifdef LAP_MINB
+#define LAP_BOUNDS __launch_bounds__(PROJ_T, LAP_MINB)
+#else
+#define LAP_BOUNDS __launch_bounds__(PROJ_T)
 #endif
 template <bool SCH>   // SCH: a scheme of mesh_set_schemes is active (kept out of the default instantiation)
-__global__ void __launch_bounds__(PROJ_T, GRADV_MINB)
+__global__ void GRADV_BOUNDS
 grad_vec_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const double* __restrict__ Ub, long long ldUb,
                 int j0, int nb, double* __restrict__ T, long long ldT)
 {
@@ -706,7 +713,7 @@ grad_vec_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const do
 // K7b: out_j = fvc::laplacian(1, U_j) = surfaceIntegrate(|Sf| snGrad(U_j)); snGrad = dc (U[n]-U[o])
 // (+ corr . (w T[o] + (1-w) T[n]) when corrected); boundary |Sf| dcB (Ub - U[c]). Grid as in grad_vec_kernel.
 template <bool SCH>
-__global__ void __launch_bounds__(PROJ_T, LAP_MINB)
+__global__ void LAP_BOUNDS
 laplacian_kernel(MeshDev m, const double* __restrict__ U, long long ldU, const double* __restrict__ Ub, long long ldUb,
                  int j0, int nb, const double* __restrict__ T, long long ldT, double* __restrict__ out, long long ldo)
 {
