@@ -225,8 +225,10 @@ int ithaca_b200_mesh_set_schemes(ithaca_b200_t* h, double grad_limit_k, double s
  *   IB200_CONV_LINEAR_UPWIND  "Gauss linearUpwind grad(U)": upwind value + (Cf - C_upwind) . grad(U_k)[upwind]
  *                             (linearUpwind::correction; grad(U_k) by the gradient scheme of mesh_set_schemes, which must
  *                             have been given C and Cf)
- * With a non-linear scheme C and G are formed through materialised div(phi_j, U_k) fields (the fused face-based contraction
- * is the linear face value); BC2 and the background terms follow the scheme; Cf is refused. */
+ * upwind keeps the fused face-based contraction of C, G and Cf: the face value depends on the sign of phi_j only, so every
+ * internal face becomes two rank-one records (max(phi_j,0) with the owner's U_k, min(phi_j,0) with the neighbour's).
+ * linearUpwind forms C and G through materialised div(phi_j, U_k) fields and refuses Cf. BC2 and the background terms follow
+ * the scheme in both. */
 enum { IB200_CONV_LINEAR = 0, IB200_CONV_UPWIND = 1, IB200_CONV_LINEAR_UPWIND = 2 };
 int ithaca_b200_mesh_set_convection(ithaca_b200_t* h, int scheme);
 

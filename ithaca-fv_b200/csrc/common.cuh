@@ -114,6 +114,8 @@ struct ConvMesh {
     const double *Sf, *w;
     const unsigned char* bmask;
     const unsigned char* cmask;   // per cell: 1 owned, 0 halo (null = all owned); scales U_i in d_i = U_i[own] - U_i[nei]
+    int upwind = 0;               // 1: "Gauss upwind" face value. Every internal face becomes TWO rank-one records,
+                                  // (max(a,0), U_k[own], d) at f and (min(a,0), U_k[nei], d) at nInt + nBnd + f
 };
 struct ConvBufs {
     DevBuf Ucm, Ubcm, Dcm, Aj, Bk, Dd, ws, chunks;

@@ -1836,13 +1836,14 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
         break;
     }
     case IB200_OP_C:    // convective_term_tens (== _cache), steadyNS.C:997-1083, fused face-based contraction (conv.cu)
-        if (s->convScheme != 0) goto materialised_C;   // the fused form is the LINEAR face value; other schemes take the div fields
+        if (s->convScheme == 2) goto materialised_C;   // linearUpwind: the face value needs grad(U_k) of the upwind cell -> div fields
     {
         nout = (size_t)N * N * N;
         if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
         ConvMesh cm;
         cm.nInt = s->nInt; cm.nBnd = s->nBnd; cm.owner = m.owner; cm.neigh = m.neigh; cm.Sf = m.Sf; cm.w = m.w; cm.bmask = m.bmask;
         cm.cmask = shard ? s->cmask.as<unsigned char>() : nullptr;
+        cm.upwind = s->convScheme == 1 ? 1 : 0;
         rc = conv_fused_launch(h, &s->conv, cm, s->nCells, U, s->ldU, s->Ub.as<double>(), s->ldUb, N, s->out.as<double>(), &s->ms[6],
                                &s->ms[5]);
         if (rc) return rc;
@@ -1909,10 +1910,11 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
         // fused face-based form (conv.cu), as for C: G(i,j,k) = sum_f flux_j(f) (Uf_k(f) . (g_i[own] - g_i[nei])), g_i = grad(P_i);
         // ITHACA_B200_G=mat keeps the materialised div(phi_j, U_k) fields (cross-check)
         const char* gev = getenv("ITHACA_B200_G");
-        if (Np <= N && !(gev && strcmp(gev, "mat") == 0) && s->convScheme == 0) {
+        if (Np <= N && !(gev && strcmp(gev, "mat") == 0) && s->convScheme != 2) {
             ConvMesh cm;
             cm.nInt = s->nInt; cm.nBnd = s->nBnd; cm.owner = m.owner; cm.neigh = m.neigh; cm.Sf = m.Sf; cm.w = m.w; cm.bmask = m.bmask;
             cm.cmask = shard ? s->cmask.as<unsigned char>() : nullptr;
+        cm.upwind = s->convScheme == 1 ? 1 : 0;
             rc = conv_fused_launch(h, &s->conv, cm, s->nCells, U, s->ldU, s->Ub.as<double>(), s->ldUb, N, s->out.as<double>(), &s->ms[6],
                                    &s->ms[5], s->gradP.as<double>(), s->ldU, Np);   // writes G(i,j,k) at i + Np*(j + N*k)
             if (rc) return rc;
@@ -2047,7 +2049,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
     case IB200_OP_CF: {  // convective_term_flux_tens, steadyNS.C:1704-1746: Np x N x N, int P_i div(div(flux(U_j), U_k)), i fastest
         // both through the adjoint of the outer div (div_adjoint_kernel): int P_i div(A) = int t_i . A, so BP is one
         // contraction against the laplacian fields and Cf is the fused face-based contraction of G with t_i as test fields
-        PROJ_REQUIRE(op == IB200_OP_BP || s->convScheme == 0, "project(Cf): only built for the linear convection scheme (the fused contraction)");
+        PROJ_REQUIRE(op == IB200_OP_BP || s->convScheme != 2, "project(Cf): not built for the linearUpwind convection scheme (fused contraction only)");
         nout = op == IB200_OP_BP ? (size_t)Np * N : (size_t)Np * N * N;
         if ((rc = ensure(h, s->out, nout * sizeof(double)))) return rc;
         if ((rc = ensure(h, s->gradP, (size_t)Np * s->ldU * sizeof(double)))) return rc;
@@ -2072,6 +2074,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
             ConvMesh cm;
             cm.nInt = s->nInt; cm.nBnd = s->nBnd; cm.owner = m.owner; cm.neigh = m.neigh; cm.Sf = m.Sf; cm.w = m.w; cm.bmask = m.bmask;
             cm.cmask = shard ? s->cmask.as<unsigned char>() : nullptr;
+        cm.upwind = s->convScheme == 1 ? 1 : 0;
             rc = conv_fused_launch(h, &s->conv, cm, s->nCells, U, s->ldU, s->Ub.as<double>(), s->ldUb, N, s->out.as<double>(), &s->ms[6],
                                    &s->ms[5], s->gradP.as<double>(), s->ldU, Np);   // writes Cf(i,j,k) at i + Np*(j + N*k)
             if (rc) return rc;
