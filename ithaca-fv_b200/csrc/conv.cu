@@ -52,6 +52,7 @@ conv_transpose_kernel(const double* __restrict__ in, long long ld, long long row
 // ---- per-face records for all N modes ---------------------------------------------------------------------------
 // Aj[f][NP], Bk[f][N][4] (component padded to 4: 32 B per mode, TMA-box friendly), Dd[f][3][NP]. One block = 4 faces,
 // lanes over the mode index (coalesced 8*NP-byte rows of the cell-major basis).
+template <bool UPW>   // UPW: "Gauss upwind" face value, two records per internal face (ConvMesh::upwind)
 __global__ void __launch_bounds__(256)
 conv_face_prep_kernel(ConvMesh m, const double* __restrict__ Ucm, const double* __restrict__ Ubcm, const double* __restrict__ Dcm,
                       int N, int NP, double* __restrict__ Aj, double* __restrict__ Bk, double* __restrict__ Dd)
@@ -76,26 +77,38 @@ conv_face_prep_kernel(ConvMesh m, const double* __restrict__ Ucm, const double* 
             const double b0 = w * o0 + w1 * n0, b1 = w * o1 + w1 * n1, b2 = w * o2 + w1 * n2;
             double a = 0.0;
             a += b0 * s0; a += b1 * s1; a += b2 * s2;   // the flux is linearInterpolate(U_j) & Sf in every scheme
-            double d0, d1, d2;
-            if (Dcm) {
-                const double* qo = Dcm + (size_t)o * 3 * NP;
-                const double* qn = Dcm + (size_t)nn * 3 * NP;
-                d0 = mo * qo[j] - mn * qn[j]; d1 = mo * qo[NP + j] - mn * qn[NP + j];
-                d2 = mo * qo[2 * NP + j] - mn * qn[2 * NP + j];
-            } else {
-                d0 = mo * o0 - mn * n0; d1 = mo * o1 - mn * n1; d2 = mo * o2 - mn * n2;
-            }
-            double* d = Dd + (size_t)f * 3 * NP;
-            d[j] = d0; d[NP + j] = d1; d[2 * NP + j] = d2;
-            if (!m.upwind) {
+            if (!UPW) {
                 Aj[(size_t)f * NP + j] = a;
-                if (j < N) *reinterpret_cast<double4*>(Bk + ((size_t)f * N + j) * 4) = make_double4(b0, b1, b2, 0.0);
+                double* d = Dd + (size_t)f * 3 * NP;
+                if (Dcm) {
+                    const double* qo = Dcm + (size_t)o * 3 * NP;
+                    const double* qn = Dcm + (size_t)nn * 3 * NP;
+                    d[j] = mo * qo[j] - mn * qn[j]; d[NP + j] = mo * qo[NP + j] - mn * qn[NP + j];
+                    d[2 * NP + j] = mo * qo[2 * NP + j] - mn * qn[2 * NP + j];
+                } else {
+                    d[j] = mo * o0 - mn * n0; d[NP + j] = mo * o1 - mn * n1; d[2 * NP + j] = mo * o2 - mn * n2;
+                }
+                if (j < N) {
+                    double4* b = reinterpret_cast<double4*>(Bk + ((size_t)f * N + j) * 4);
+                    *b = make_double4(b0, b1, b2, 0.0);
+                }
             } else {
                 // upwind: phi_j >= 0 carries the owner's U_k, phi_j < 0 the neighbour's -> two records of the same face
+                double d0, d1, d2;
+                if (Dcm) {
+                    const double* qo = Dcm + (size_t)o * 3 * NP;
+                    const double* qn = Dcm + (size_t)nn * 3 * NP;
+                    d0 = mo * qo[j] - mn * qn[j]; d1 = mo * qo[NP + j] - mn * qn[NP + j];
+                    d2 = mo * qo[2 * NP + j] - mn * qn[2 * NP + j];
+                } else {
+                    d0 = mo * o0 - mn * n0; d1 = mo * o1 - mn * n1; d2 = mo * o2 - mn * n2;
+                }
                 const long long f2 = nF + f;
                 Aj[(size_t)f * NP + j] = a >= 0.0 ? a : 0.0;
                 Aj[(size_t)f2 * NP + j] = a >= 0.0 ? 0.0 : a;
+                double* d = Dd + (size_t)f * 3 * NP;
                 double* dd = Dd + (size_t)f2 * 3 * NP;
+                d[j] = d0; d[NP + j] = d1; d[2 * NP + j] = d2;
                 dd[j] = d0; dd[NP + j] = d1; dd[2 * NP + j] = d2;
                 if (j < N) {
                     *reinterpret_cast<double4*>(Bk + ((size_t)f * N + j) * 4) = make_double4(o0, o1, o2, 0.0);
@@ -317,9 +330,14 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
         conv_transpose_kernel<<<(unsigned)((3 * m.nBnd + 95) / 96), 256, 0, h->stream>>>(Ub, ldUb, 3 * m.nBnd, N, NP, cb->Ubcm.as<double>());
     if (Dfm)   // Ni test fields, zero-padded to N by the transpose
         conv_transpose_kernel<<<(unsigned)((3 * nCells + 95) / 96), 256, 0, h->stream>>>(Dfm, ldD, 3 * nCells, Ni, NP, cb->Dcm.as<double>());
-    conv_face_prep_kernel<<<(unsigned)((nFaces + 3) / 4), dim3(64, 4), 0, h->stream>>>(m, cb->Ucm.as<double>(), cb->Ubcm.as<double>(),
-                                                                                   Dfm ? cb->Dcm.as<double>() : nullptr, N, NP,
-                                                                                   cb->Aj.as<double>(), cb->Bk.as<double>(), cb->Dd.as<double>());
+    if (m.upwind)
+        conv_face_prep_kernel<true><<<(unsigned)((nFaces + 3) / 4), dim3(64, 4), 0, h->stream>>>(
+            m, cb->Ucm.as<double>(), cb->Ubcm.as<double>(), Dfm ? cb->Dcm.as<double>() : nullptr, N, NP, cb->Aj.as<double>(),
+            cb->Bk.as<double>(), cb->Dd.as<double>());
+    else
+        conv_face_prep_kernel<false><<<(unsigned)((nFaces + 3) / 4), dim3(64, 4), 0, h->stream>>>(
+            m, cb->Ucm.as<double>(), cb->Ubcm.as<double>(), Dfm ? cb->Dcm.as<double>() : nullptr, N, NP, cb->Aj.as<double>(),
+            cb->Bk.as<double>(), cb->Dd.as<double>());
     IB_CUDA(h, cudaGetLastError());
     cudaEventRecord(e1, h->stream);
 

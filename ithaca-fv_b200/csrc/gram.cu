@@ -262,8 +262,17 @@ __global__ void gram_reduce_kernel(const double* __restrict__ ws, const GramJob*
         if (!((jb.mask[w] >> ((r >> 3) * GRAM_WF + (c >> 3))) & 1u)) continue;
         const int i = jb.boxrow[jb.ta[w]] + r, j = jb.boxrow[jb.tb[w]] + c;
         if (i >= Ma || j >= Nb || (symmetric && j > i)) continue;
-        double s = 0.0;
-        for (int k = 0; k < nsplit; k++) s += base[((size_t)k * GRAM_WARPS + w) * GRAM_TILE + e];
+        // fixed summation order (reproducible run to run): four interleaved partial sums over the slabs keep four loads in
+        // flight per thread instead of one dependent add chain
+        const size_t sstr = (size_t)GRAM_WARPS * GRAM_TILE;
+        const double* p = base + (size_t)w * GRAM_TILE + e;
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+        int k = 0;
+        for (; k + 4 <= nsplit; k += 4) {
+            s0 += p[(size_t)k * sstr]; s1 += p[(size_t)(k + 1) * sstr]; s2 += p[(size_t)(k + 2) * sstr]; s3 += p[(size_t)(k + 3) * sstr];
+        }
+        for (; k < nsplit; k++) s0 += p[(size_t)k * sstr];
+        const double s = (s0 + s1) + (s2 + s3);
         out[(size_t)i * rs + (size_t)(j / cinner) * cso + (size_t)(j % cinner) * csi] = s;
         if (symmetric) out[(size_t)j * rs + (size_t)(i / cinner) * cso + (size_t)(i % cinner) * csi] = s;
     }
@@ -668,7 +677,7 @@ int atvb_launch(ithaca_b200* h, const double* A, long long lda, int Ma, const do
     IB_CUDA(h, cudaGetLastError());
     IB_CUDA(h, cudaEventRecord(tk.b, h->stream));
     tk.used = true;
-    gram_reduce_kernel<<<dim3(GRAM_WARPS * GRAM_TILE / 256 / 4, njobs), 256, 0, h->stream>>>(
+    gram_reduce_kernel<<<dim3((GRAM_WARPS * GRAM_TILE + 255) / 256, njobs), 256, 0, h->stream>>>(
         h->dWs, (const GramJob*)dj, Ma, Nb, symmetric, out, rs, cinner, cso, csi);
     IB_CUDA(h, cudaGetLastError());
     h->launches += 2;
