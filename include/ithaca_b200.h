@@ -179,6 +179,36 @@ int ithaca_b200_pod_block_gram_set(ithaca_b200_t* h, const double* G);
 int ithaca_b200_pod_block_lift(ithaca_b200_t* h, int slot, int r);
 int ithaca_b200_pod_block_lift_finish(ithaca_b200_t* h, int r, int norm_kind, double* const* mode_ptrs, double* normfact_out);
 
+/* ---- row-streamed POD: a rank's cell shard larger than HBM (C3 on 1 or 2 GPUs: 480 GB / 240 GB per rank) ------------
+ * The reference's own parallel decomposition is over CELLS: every rank forms the Gram of its rows and the partial matrices are
+ * summed (ITHACAcoeffsMass.C:85-115, ITHACAPOD.C:146-149); the lift and the norms are row-local (ITHACAPOD.C:194-243). The same
+ * identity with more cell chunks than GPUs: the shard is cut into chunks of consecutive cells that pass through two device
+ * slots; each snapshot row crosses PCIe twice (once per pass) instead of once per block pair as in the snapshot-blocked path
+ * above, and the m-snapshot contraction keeps its full-size schedule. The r modes of the whole shard stay resident (r << m).
+ *   stream_begin(m, dim, nCellsShard)
+ *   pass 1, per chunk:  stream_upload(slot, cell0, n, V_chunk, ptrs)  or  stream_slot(...) + an in-place producer
+ *                       stream_gram_add(slot)                 G_partial += S_c^T diag(V_c) S_c
+ *   stream_gram_finish(G_out)                                 all-reduce over ranks; installs the Gram of pod_eig
+ *   pod_eig(...)
+ *   pass 2, per chunk:  fill a slot again (a chunk still resident from pass 1 needs no refill), stream_lift_add(slot, r, norm)
+ *   stream_lift_finish(r, mode_ptrs, normfact_out)            norms all-reduced, modes scaled and downloaded: as pod_lift
+ * stream_upload, gram_add and lift_add only ENQUEUE (copies on a copy stream, kernels on ithaca_b200_stream): with the two
+ * slots the upload of chunk k+1 overlaps the contraction of chunk k. The *_finish calls synchronise and report errors.
+ *   stream_upload: V_chunk = n volumes, snap_ptrs[j] -> the chunk's n*dim values of snapshot j (host or device; host memory
+ *                  must stay valid until the next *_finish; pinned memory makes the copies asynchronous).
+ *   stream_slot:   returns the slot's device addresses for a producer that writes the chunk in place (S_out: m columns of
+ *                  *ld_out doubles, V_out: n doubles). Blocks the host until the slot's previous consumers are done. The
+ *                  producer's writes must be complete, or issued on ithaca_b200_stream(h), before gram_add / lift_add. */
+int ithaca_b200_pod_stream_begin(ithaca_b200_t* h, int m, int dim, int64_t nCellsShard);
+int ithaca_b200_pod_stream_upload(ithaca_b200_t* h, int slot, int64_t cell0, int64_t nCellsChunk, const double* V_chunk,
+                                  const double* const* snap_ptrs);
+int ithaca_b200_pod_stream_slot(ithaca_b200_t* h, int slot, int64_t cell0, int64_t nCellsChunk, double** S_out, int64_t* ld_out,
+                                double** V_out);
+int ithaca_b200_pod_stream_gram_add(ithaca_b200_t* h, int slot);
+int ithaca_b200_pod_stream_gram_finish(ithaca_b200_t* h, double* G_out);
+int ithaca_b200_pod_stream_lift_add(ithaca_b200_t* h, int slot, int r, int norm_kind);
+int ithaca_b200_pod_stream_lift_finish(ithaca_b200_t* h, int r, double* const* mode_ptrs, double* normfact_out);
+
 /* ---- Galerkin projection: steadyNS::projectSUP term builders ---------------------------------------
  * (src/ITHACA_FOMPROBLEMS/steadyNS/steadyNS.C:556-707 calls :883-1137; inherited by unsteadyNS,
  *  src/ITHACA_FOMPROBLEMS/unsteadyNS/unsteadyNS.H:61). Scheme set: Gauss linear (grad, div, interpolate),
@@ -393,6 +423,17 @@ int ithaca_b200_export_tensor(const char* folder, const char* name, int type, co
 /* Register-resident DMMA.8x8x4 (mma.sync.m8n8k4.f64) issue-rate microbenchmark on `device`:
  * the measured FP64 tensor peak used as the Gram kernel's roofline denominator. */
 int ithaca_b200_dmma_peak(int device, double* tflops_out);
+
+/* The synthetic snapshot set of the benchmark configurations, written in place on the device (kernels on
+ * ithaca_b200_stream(h)) from a counter-based generator, so that any row range is reproduced identically by any rank in any
+ * chunking and the 480 GB / 800 GB sets of C3 / C5 never have to exist anywhere:
+ *   S(i, j) = sum_{k<R} u_k(x_i) coef(j, k) / (k + 1) + eps * w(i, j),  x_i = (i + 1/2) / NdGlobal,  u_k(x) = sin((k + 1) pi x),
+ *   w = zero-mean unit-variance variate from Philox4x32-10(key = seed, counter = (global row i, snapshot j)).
+ * S: device, rows [row0, row0 + nRows) of the m snapshots, column j at S + j*ld. coef: device, m x R col-major (R <= 256).
+ *   V(c) = exp(0.5 w(c)) e^(-1/8) / nCellsGlobal  (sums to ~1 over the global mesh). */
+int ithaca_b200_synth_snapshots(ithaca_b200_t* h, double* S, int64_t ld, int64_t row0, int64_t nRows, int64_t NdGlobal, int m,
+                                const double* coef, int R, double eps, uint64_t seed);
+int ithaca_b200_synth_volumes(ithaca_b200_t* h, double* V, int64_t cell0, int64_t nCells, int64_t nCellsGlobal, uint64_t seed);
 
 #ifdef __cplusplus
 }

@@ -27,6 +27,9 @@ SYMBOLS = [
     "ithaca_b200_pod_reconstruct", "ithaca_b200_pod_lift_scaled", "ithaca_b200_pod_gram_volumes",
     "ithaca_b200_pod_block_begin", "ithaca_b200_pod_block_upload", "ithaca_b200_pod_block_gram",
     "ithaca_b200_pod_block_gram_finish", "ithaca_b200_pod_block_gram_get", "ithaca_b200_pod_block_gram_set", "ithaca_b200_pod_block_lift", "ithaca_b200_pod_block_lift_finish",
+    "ithaca_b200_pod_stream_begin", "ithaca_b200_pod_stream_upload", "ithaca_b200_pod_stream_slot", "ithaca_b200_pod_stream_gram_add",
+    "ithaca_b200_pod_stream_gram_finish", "ithaca_b200_pod_stream_lift_add", "ithaca_b200_pod_stream_lift_finish",
+    "ithaca_b200_synth_snapshots", "ithaca_b200_synth_volumes",
     "ithaca_b200_mesh_upload", "ithaca_b200_mesh_addressing", "ithaca_b200_basis_upload", "ithaca_b200_project",
     "ithaca_b200_fvc_eval", "ithaca_b200_proj_timings", "ithaca_b200_project_background", "ithaca_b200_project_bc_velocity",
     "ithaca_b200_partition_create", "ithaca_b200_partition_destroy", "ithaca_b200_partition_sizes",
@@ -86,6 +89,15 @@ def lib():
         L.ithaca_b200_pod_block_gram_set.argtypes = [P, P]
         L.ithaca_b200_pod_block_lift.argtypes = [P, I, I]
         L.ithaca_b200_pod_block_lift_finish.argtypes = [P, I, I, P, P]
+        L.ithaca_b200_pod_stream_begin.argtypes = [P, I, I, L64]
+        L.ithaca_b200_pod_stream_upload.argtypes = [P, I, L64, L64, P, P]
+        L.ithaca_b200_pod_stream_slot.argtypes = [P, I, L64, L64, ctypes.POINTER(P), ctypes.POINTER(L64), ctypes.POINTER(P)]
+        L.ithaca_b200_pod_stream_gram_add.argtypes = [P, I]
+        L.ithaca_b200_pod_stream_gram_finish.argtypes = [P, P]
+        L.ithaca_b200_pod_stream_lift_add.argtypes = [P, I, I, I]
+        L.ithaca_b200_pod_stream_lift_finish.argtypes = [P, I, P, P]
+        L.ithaca_b200_synth_snapshots.argtypes = [P, P, L64, L64, L64, L64, I, P, I, D, ctypes.c_uint64]
+        L.ithaca_b200_synth_volumes.argtypes = [P, P, L64, L64, L64, ctypes.c_uint64]
         L.ithaca_b200_pod_project.argtypes = [P, I, I, P]
         L.ithaca_b200_pod_modes_mass.argtypes = [P, I, P]
         L.ithaca_b200_pod_get_coeffs.argtypes = [P, I, P]
@@ -410,6 +422,52 @@ class Pod:
         self.r = r
         return Phi
 
+    # ---- row-streamed POD (a shard larger than HBM passes through two chunk slots) ----
+    def stream_begin(self, m, dim, nCellsShard):
+        self._chk(self.L.ithaca_b200_pod_stream_begin(self.h, m, dim, nCellsShard))
+        self.m, self.dim, self.nCells = m, dim, nCellsShard
+
+    def stream_upload(self, slot, cell0, ncells, V_chunk, snap_ptrs):
+        """snap_ptrs: m addresses of the chunk's first value in each snapshot (host pinned, host pageable or device)."""
+        arr = (ctypes.c_void_p * self.m)(*snap_ptrs)
+        self._chk(self.L.ithaca_b200_pod_stream_upload(self.h, slot, cell0, ncells, _ptr(V_chunk), arr))
+
+    def stream_slot(self, slot, cell0, ncells):
+        """Device addresses (S, ld, V) of a slot for an in-place producer."""
+        S, V, ld = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_int64()
+        self._chk(self.L.ithaca_b200_pod_stream_slot(self.h, slot, cell0, ncells, ctypes.byref(S), ctypes.byref(ld), ctypes.byref(V)))
+        return S.value, ld.value, V.value
+
+    def stream_gram_add(self, slot):
+        self._chk(self.L.ithaca_b200_pod_stream_gram_add(self.h, slot))
+
+    def stream_gram_finish(self, want=True):
+        G = np.zeros((self.m, self.m), order="F") if want else None
+        self._chk(self.L.ithaca_b200_pod_stream_gram_finish(self.h, _ptr(G)))
+        return G
+
+    def stream_lift_add(self, slot, r, norm="L2"):
+        self._chk(self.L.ithaca_b200_pod_stream_lift_add(self.h, slot, r, 0 if norm == "L2" else 1))
+
+    def stream_lift_finish(self, r, out=None, want=True):
+        nf = np.zeros(r)
+        Phi = arr = None
+        if out is not None:
+            arr = (ctypes.c_void_p * r)(*[_ptr(o) for o in out])
+        elif want:
+            Phi = np.zeros((self.nCells * self.dim, r), order="F")
+            arr = (ctypes.c_void_p * r)(*[Phi.ctypes.data + i * Phi.strides[1] for i in range(r)])
+        self._chk(self.L.ithaca_b200_pod_stream_lift_finish(self.h, r, arr, nf.ctypes.data))
+        self.r = r
+        return Phi, nf
+
+    # ---- synthetic benchmark data written in place on the device (measurement helper) ----
+    def synth_snapshots(self, S_ptr, ld, row0, nrows, Nd_global, m, coef_ptr, R, eps, seed):
+        self._chk(self.L.ithaca_b200_synth_snapshots(self.h, S_ptr, ld, row0, nrows, Nd_global, m, coef_ptr, R, eps, seed))
+
+    def synth_volumes(self, V_ptr, cell0, ncells, ncells_global, seed):
+        self._chk(self.L.ithaca_b200_synth_volumes(self.h, V_ptr, cell0, ncells, ncells_global, seed))
+
     def lift_patch(self, Sbc, r):
         Sbc = np.asfortranarray(Sbc, dtype=np.float64)
         out = np.zeros((Sbc.shape[0], r), order="F")
@@ -686,7 +744,7 @@ def DEIMmodes(pod, snapshots, V, dim, nmodes=0, solver="spectra", norm="L2", Sbc
     return getModes(pod, snapshots, V, dim, nmodes, solver, norm, Sbc)
 
 
-def getModesMemoryEfficient(pod, block_source, m, V, dim, nmodes=0, solver="spectra", norm="L2", block=64, want_modes=True):
+def getModesMemoryEfficient(pod, block_source, m, V, dim, nmodes=0, solver="spectra", norm="L2", block=64, want_modes=True, Sbc=None):
     """Snapshot-blocked POD (ITHACAPOD::getModesMemoryEfficient, ITHACAPOD.C:344-628) through the C ABI.
     block_source(first, nb) -> list of nb snapshot buffers (numpy arrays or torch tensors, nCells*dim doubles each):
     the caller streams them from disk / host / a generator; two blocks are resident on the device at a time."""
@@ -727,8 +785,60 @@ def getModesMemoryEfficient(pod, block_source, m, V, dim, nmodes=0, solver="spec
         arr = (ctypes.c_void_p * nmodes)(*[Phi.ctypes.data + i * Phi.strides[1] for i in range(nmodes)])
     pod._chk(L.ithaca_b200_pod_block_lift_finish(h, nmodes, nk, arr, nf.ctypes.data))
     pod.r = nmodes
+    Pbc = pod.lift_patch(Sbc, nmodes) if Sbc is not None else None   # modesEigBC = SnapMatrixBC * eigvec / normFactor (ITHACAPOD.C:573-578)
     evn, cum = postprocess_eigenvalues(ev_all, nmodes, solver)
-    return dict(G=G, evals_all=ev_all, evals_norm=evn, cum=cum, evecs=Q, normfact=nf, modes=Phi)
+    return dict(G=G, evals_all=ev_all, evals_norm=evn, cum=cum, evecs=Q, normfact=nf, modes=Phi, modes_bc=Pbc)
+
+
+def getModesStreamed(pod, snapshots, V, dim, nmodes=0, solver="spectra", norm="L2", chunk_cells=None, Sbc=None, want_modes=True):
+    """getModes for a cell shard larger than HBM, through the row-streamed calls (pod_stream_*): the shard is cut into chunks of
+    `chunk_cells` consecutive cells; pass 1 sums the chunk Grams (the reference's per-rank Gram + reduce, ITHACAcoeffsMass.C:85-115,
+    with more chunks than GPUs), pass 2 lifts chunk by chunk (ITHACAPOD.C:194-243 is row-local). snapshots: Fortran (Nd, m) host
+    array or a list of m host buffers (numpy / pinned torch); the upload of chunk k+1 overlaps the work on chunk k. The chunks
+    still resident after pass 1 are lifted first, without a second upload."""
+    if norm not in ("L2", "Frobenius"):
+        raise IthacaB200Error("The PODnorm can be only L2 or Frobenius")
+    if isinstance(snapshots, np.ndarray) and snapshots.ndim == 2:
+        assert snapshots.flags.f_contiguous and snapshots.dtype == np.float64
+        base = [snapshots.ctypes.data + j * snapshots.strides[1] for j in range(snapshots.shape[1])]
+    else:
+        base = [_ptr(x) for x in snapshots]
+    m = len(base)
+    nmodes = check_nmodes(m, nmodes, solver)
+    Vp = _ptr(V)
+    nCells = int(V.shape[0])
+    if not chunk_cells:
+        chunk_cells = nCells
+    chunks = [(c0, min(chunk_cells, nCells - c0)) for c0 in range(0, nCells, chunk_cells)]
+    pod.stream_begin(m, dim, nCells)
+
+    def up(slot, k):
+        c0, nc = chunks[k]
+        pod.stream_upload(slot, c0, nc, Vp + 8 * c0, [b + 8 * c0 * dim for b in base])
+
+    up(0, 0)
+    for k in range(len(chunks)):
+        if k + 1 < len(chunks):
+            up((k + 1) & 1, k + 1)
+        pod.stream_gram_add(k & 1)
+    G = pod.stream_gram_finish()
+    ev_all, Q = pod.eig(nmodes)
+    n = len(chunks)
+    slot_of = {n - 1: (n - 1) & 1}              # the last two chunks of pass 1 are still in the slots: lift them first
+    if n > 1:
+        slot_of[n - 2] = (n - 2) & 1
+    order = sorted(slot_of, reverse=True) + list(range(n - 3, -1, -1))
+    pending = order[len(slot_of):]
+    for k in order:
+        pod.stream_lift_add(slot_of[k], nmodes, norm)
+        if pending:                              # the slot just consumed takes the next chunk while the other one is lifted
+            kn = pending.pop(0)
+            up(slot_of[k], kn)
+            slot_of[kn] = slot_of[k]
+    Phi, nf = pod.stream_lift_finish(nmodes, want=want_modes)
+    Pbc = pod.lift_patch(Sbc, nmodes) if Sbc is not None else None
+    evn, cum = postprocess_eigenvalues(ev_all, nmodes, solver)
+    return dict(G=G, evals_all=ev_all, evals_norm=evn, cum=cum, evecs=Q, normfact=nf, modes=Phi, modes_bc=Pbc)
 
 
 COV_UNREAL = 999999.999999   # PODTemplate::buildCovMatrix marks entries not computed yet with this value (PODTemplate.C:422)

@@ -216,6 +216,13 @@ int ithaca_b200_destroy(ithaca_b200_t* h)
         cudaEventDestroy(h->timers[i].a);
         cudaEventDestroy(h->timers[i].b);
     }
+    for (auto& sl : h->slot) {
+        if (sl.V) cudaFree(sl.V);
+        if (sl.ready) cudaEventDestroy(sl.ready);
+        if (sl.freed) cudaEventDestroy(sl.freed);
+    }
+    if (h->dGacc) cudaFree(h->dGacc);
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     cudaStreamDestroy(h->stream);
     delete h;
     return IB200_OK;
@@ -320,6 +327,8 @@ int ithaca_b200_pod_upload(ithaca_b200_t* h, const double* const* snap_ptrs, int
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
     h->m = m; h->dim = dim; h->Nd = Nd; h->ld = ld;
     h->block_mode = false;
+    h->stream_mode = false;
+    h->slot[0].ncells = h->slot[1].ncells = 0;
     h->have_gram = h->have_eig = h->have_lift = h->have_modes = false;
     return IB200_OK;
 }
@@ -327,7 +336,7 @@ int ithaca_b200_pod_upload(ithaca_b200_t* h, const double* const* snap_ptrs, int
 int ithaca_b200_pod_gram(ithaca_b200_t* h, double* G_out)
 {
     if (!h) return IB200_ERR_ARG;
-    if (!h->dS || h->m <= 0 || !h->dV) { set_error(h, "pod_gram: upload snapshots and volumes first"); return IB200_ERR_ARG; }
+    if (!h->dS || h->m <= 0 || !h->dV || h->stream_mode) { set_error(h, "pod_gram: upload snapshots and volumes first"); return IB200_ERR_ARG; }
     cudaSetDevice(h->device);
     int rc = ensure_mats(h, h->m);
     if (rc) return rc;
@@ -361,7 +370,7 @@ scale_by_sqrt_abs_kernel(const double* __restrict__ S, double* __restrict__ T, l
 int ithaca_b200_pod_gram_volumes(ithaca_b200_t* h, const double* const* vol_ptrs, double* G_out)
 {
     if (!h) return IB200_ERR_ARG;
-    if (!h->dS || h->m <= 0 || h->block_mode) { set_error(h, "pod_gram_volumes: upload snapshots first"); return IB200_ERR_ARG; }
+    if (!h->dS || h->m <= 0 || h->block_mode || h->stream_mode) { set_error(h, "pod_gram_volumes: upload snapshots first"); return IB200_ERR_ARG; }
     if (!vol_ptrs) { set_error(h, "pod_gram_volumes: null volume list"); return IB200_ERR_ARG; }
     cudaSetDevice(h->device);
     int rc = ensure_mats(h, h->m);
@@ -455,7 +464,7 @@ int ithaca_b200_pod_postprocess_eigenvalues(const double* evals_all, int m, int 
 int ithaca_b200_pod_lift(ithaca_b200_t* h, int r, int norm_kind, double* const* mode_ptrs, double* normfact_out)
 {
     if (!h) return IB200_ERR_ARG;
-    if (!h->have_eig || h->Nd <= 0) { set_error(h, "pod_lift: call pod_upload, pod_gram and pod_eig first"); return IB200_ERR_ARG; }
+    if (!h->have_eig || h->Nd <= 0 || h->block_mode || h->stream_mode) { set_error(h, "pod_lift: call pod_upload, pod_gram and pod_eig first"); return IB200_ERR_ARG; }
     if (r <= 0 || r > h->m) { set_error(h, "pod_lift: The number of requested modes cannot be bigger than the number of Snapshots"); return IB200_ERR_ARG; }
     if (norm_kind != 0 && norm_kind != 1) { set_error(h, "pod_lift: The PODnorm can be only L2 or Frobenius"); return IB200_ERR_ARG; }
     cudaSetDevice(h->device);
@@ -480,11 +489,11 @@ int ithaca_b200_pod_lift(ithaca_b200_t* h, int r, int norm_kind, double* const* 
 int ithaca_b200_pod_lift_scaled(ithaca_b200_t* h, int r, const double* factors, double* const* mode_ptrs)
 {
     if (!h) return IB200_ERR_ARG;
-    if (!h->have_eig || h->Nd <= 0 || h->block_mode) { set_error(h, "pod_lift_scaled: call pod_upload, pod_gram and pod_eig first"); return IB200_ERR_ARG; }
-    if (r <= 0 || r > h->m || r > 104 || !factors) { set_error(h, "pod_lift_scaled: bad argument"); return IB200_ERR_ARG; }
+    if (!h->have_eig || h->Nd <= 0 || h->block_mode || h->stream_mode) { set_error(h, "pod_lift_scaled: call pod_upload, pod_gram and pod_eig first"); return IB200_ERR_ARG; }
+    if (r <= 0 || r > h->m || !factors) { set_error(h, "pod_lift_scaled: bad argument"); return IB200_ERR_ARG; }
     cudaSetDevice(h->device);
     double* dF = nullptr;
-    IB_CUDA(h, cudaMalloc(&dF, 104 * sizeof(double)));
+    IB_CUDA(h, cudaMalloc(&dF, (size_t)r * sizeof(double)));
     cudaError_t e = cudaMemcpyAsync(dF, factors, (size_t)r * sizeof(double), cudaMemcpyDefault, h->stream);
     int rc = e == cudaSuccess ? lift_scaled_launch(h, r, dF) : IB200_ERR_CUDA;
     if (!rc && mode_ptrs)
@@ -712,6 +721,8 @@ int ithaca_b200_pod_block_begin(ithaca_b200_t* h, int m_total, int dim, int64_t 
     int rc = ensure_mats(h, m_total);
     if (rc) return rc;
     h->m = m_total; h->dim = dim; h->Nd = nCells * dim; h->ld = (h->Nd + 15) / 16 * 16;
+    h->stream_mode = false;
+    h->slot[0].ncells = h->slot[1].ncells = 0;
     IB_CUDA(h, cudaMemsetAsync(h->dG, 0, (size_t)m_total * m_total * sizeof(double), h->stream));
     h->blk_n[0] = h->blk_n[1] = 0;
     h->blk_lifted = 0;
@@ -862,7 +873,219 @@ int ithaca_b200_pod_block_lift_finish(ithaca_b200_t* h, int r, int norm_kind, do
     tstop(h, T_DOWNLOAD);
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
     h->have_modes = true;
+    h->have_lift = true;   // pod_lift_patch: eigenvectors, norm factors and r are those of this lift (ITHACAPOD.C:573-578)
     h->blk_lifted = 0;
+    return IB200_OK;
+}
+
+// ---- row-streamed POD: a rank's cell shard larger than HBM passes through two chunk slots -----------------------------
+// The reference's own decomposition over cells (ITHACAcoeffsMass.C:85-115: every rank forms the Gram of its rows, the partial
+// matrices are summed) applied with more cell chunks than GPUs: G = sum over chunks of S_c^T V_c S_c, then modes rows = S_c Q_r.
+
+__global__ void stream_acc_kernel(double* __restrict__ acc, const double* __restrict__ x, size_t n, int assign)
+{
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        acc[i] = assign ? x[i] : acc[i] + x[i];
+}
+
+static int stream_slot_prepare(ithaca_b200* h, int slot, int64_t cell0, int64_t nc, bool host_waits)
+{
+    ithaca_b200::StreamSlot& sl = h->slot[slot];
+    const int64_t Nd = nc * h->dim, ld = (Nd + 15) / 16 * 16;
+    // the previous occupant's consumers (gram_add / lift_add on the compute stream) must be done before the slot is rewritten
+    if (sl.freed_pending) {
+        if (host_waits) IB_CUDA(h, cudaEventSynchronize(sl.freed));
+        else IB_CUDA(h, cudaStreamWaitEvent(h->copy_stream, sl.freed, 0));
+    }
+    double** buf = slot == 0 ? &h->dS : &h->dS2;
+    size_t* cap = slot == 0 ? &h->dS_cap : &h->dS2_cap;
+    if ((size_t)ld * h->m * sizeof(double) > *cap || nc > sl.V_cap) {
+        // growing a slot frees memory the device may still read: drain both streams first (only at the first chunks)
+        IB_CUDA(h, cudaStreamSynchronize(h->stream));
+        IB_CUDA(h, cudaStreamSynchronize(h->copy_stream));
+        int rc = ensure(h, buf, cap, (size_t)ld * h->m * sizeof(double));
+        if (rc) return rc;
+        if (nc > sl.V_cap) {
+            if (sl.V) cudaFree(sl.V);
+            sl.V = nullptr; sl.V_cap = 0;
+            IB_CUDA(h, cudaMalloc(&sl.V, (size_t)nc * sizeof(double)));
+            sl.V_cap = nc;
+        }
+    }
+    sl.cell0 = cell0; sl.ncells = nc; sl.ld = ld;
+    sl.ready_pending = false;
+    h->vol_gen++;   // the weights of this slot changed: the contraction rebuilds its repeated copy
+    return IB200_OK;
+}
+
+static int stream_args(ithaca_b200* h, const char* who, int slot, int64_t cell0, int64_t nc)
+{
+    if (!h->stream_mode) { set_error(h, std::string(who) + ": call pod_stream_begin first"); return IB200_ERR_ARG; }
+    if ((slot != 0 && slot != 1) || cell0 < 0 || nc <= 0 || cell0 + nc > h->strm_cells) { set_error(h, std::string(who) + ": bad argument"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_stream_begin(ithaca_b200_t* h, int m, int dim, int64_t nCellsTotal)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (m <= 0 || dim <= 0 || nCellsTotal <= 0) { set_error(h, "pod_stream_begin: bad argument"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    int rc = ensure_mats(h, m);
+    if (rc) return rc;
+    if (!h->copy_stream) IB_CUDA(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+    for (auto& sl : h->slot) {
+        if (!sl.ready) IB_CUDA(h, cudaEventCreateWithFlags(&sl.ready, cudaEventDisableTiming));
+        if (!sl.freed) IB_CUDA(h, cudaEventCreateWithFlags(&sl.freed, cudaEventDisableTiming));
+        sl.ncells = 0; sl.ready_pending = sl.freed_pending = false;
+    }
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->copy_stream));
+    if (m > h->gacc_cap) {
+        if (h->dGacc) cudaFree(h->dGacc);
+        h->dGacc = nullptr; h->gacc_cap = 0;
+        IB_CUDA(h, cudaMalloc(&h->dGacc, (size_t)m * m * sizeof(double)));
+        h->gacc_cap = m;
+    }
+    h->m = m; h->dim = dim;
+    h->strm_cells = nCellsTotal; h->strm_Nd = nCellsTotal * dim; h->strm_ld = (h->strm_Nd + 15) / 16 * 16;
+    h->Nd = 0; h->ld = 0; h->nCells = 0;          // no resident snapshot matrix in this mode
+    h->strm_gram_chunks = h->strm_lift_chunks = 0;
+    h->stream_mode = true; h->block_mode = false;
+    h->have_gram = h->have_eig = h->have_lift = h->have_modes = false;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_stream_slot(ithaca_b200_t* h, int slot, int64_t cell0, int64_t nCellsChunk, double** S_out, int64_t* ld_out,
+                                double** V_out)
+{
+    if (!h) return IB200_ERR_ARG;
+    int rc = stream_args(h, "pod_stream_slot", slot, cell0, nCellsChunk);
+    if (rc) return rc;
+    if ((rc = stream_slot_prepare(h, slot, cell0, nCellsChunk, true))) return rc;
+    if (S_out) *S_out = slot == 0 ? h->dS : h->dS2;
+    if (ld_out) *ld_out = h->slot[slot].ld;
+    if (V_out) *V_out = h->slot[slot].V;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_stream_upload(ithaca_b200_t* h, int slot, int64_t cell0, int64_t nCellsChunk, const double* V_chunk,
+                                  const double* const* snap_ptrs)
+{
+    if (!h) return IB200_ERR_ARG;
+    int rc = stream_args(h, "pod_stream_upload", slot, cell0, nCellsChunk);
+    if (rc) return rc;
+    if (!V_chunk || !snap_ptrs) { set_error(h, "pod_stream_upload: null pointer"); return IB200_ERR_ARG; }
+    if ((rc = stream_slot_prepare(h, slot, cell0, nCellsChunk, false))) return rc;
+    ithaca_b200::StreamSlot& sl = h->slot[slot];
+    double* S = slot == 0 ? h->dS : h->dS2;
+    const size_t bytes = (size_t)nCellsChunk * h->dim * sizeof(double);
+    IB_CUDA(h, cudaMemcpyAsync(sl.V, V_chunk, (size_t)nCellsChunk * sizeof(double), cudaMemcpyDefault, h->copy_stream));
+    for (int j = 0; j < h->m; j++) {
+        if (!snap_ptrs[j]) { set_error(h, "pod_stream_upload: null snapshot pointer"); return IB200_ERR_ARG; }
+        IB_CUDA(h, cudaMemcpyAsync(S + (size_t)j * sl.ld, snap_ptrs[j], bytes, cudaMemcpyDefault, h->copy_stream));
+    }
+    IB_CUDA(h, cudaEventRecord(sl.ready, h->copy_stream));
+    sl.ready_pending = true;
+    return IB200_OK;
+}
+
+// the compute stream picks up a slot: wait for its copies, remember that a consumer is in flight
+static int stream_consume_begin(ithaca_b200* h, int slot)
+{
+    ithaca_b200::StreamSlot& sl = h->slot[slot];
+    if (sl.ready_pending) IB_CUDA(h, cudaStreamWaitEvent(h->stream, sl.ready, 0));
+    return IB200_OK;
+}
+static int stream_consume_end(ithaca_b200* h, int slot)
+{
+    ithaca_b200::StreamSlot& sl = h->slot[slot];
+    IB_CUDA(h, cudaEventRecord(sl.freed, h->stream));
+    sl.freed_pending = true;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_stream_gram_add(ithaca_b200_t* h, int slot)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->stream_mode || (slot != 0 && slot != 1) || h->slot[slot].ncells <= 0) { set_error(h, "pod_stream_gram_add: fill the slot first"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    const ithaca_b200::StreamSlot& sl = h->slot[slot];
+    const double* S = slot == 0 ? h->dS : h->dS2;
+    int rc = stream_consume_begin(h, slot);
+    if (rc) return rc;
+    tstart(h, T_GRAM);
+    rc = atvb_launch(h, S, sl.ld, h->m, S, sl.ld, h->m, sl.ncells * h->dim, sl.V, h->dim, 1, h->dG, 1, 0x7fffffff, 0, h->m);
+    if (rc) return rc;
+    const size_t n = (size_t)h->m * h->m;
+    stream_acc_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 1024), 256, 0, h->stream>>>(h->dGacc, h->dG, n, h->strm_gram_chunks == 0);
+    h->launches += 1;
+    tstop(h, T_GRAM);
+    IB_CUDA(h, cudaGetLastError());
+    h->strm_gram_chunks++;
+    h->have_gram = h->have_eig = false;
+    return stream_consume_end(h, slot);
+}
+
+int ithaca_b200_pod_stream_gram_finish(ithaca_b200_t* h, double* G_out)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->stream_mode || h->strm_gram_chunks <= 0) { set_error(h, "pod_stream_gram_finish: no chunk was added"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    const size_t n = (size_t)h->m * h->m;
+    tstart(h, T_ALLREDUCE);
+    IB_CUDA(h, cudaMemcpyAsync(h->dG, h->dGacc, n * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+    int rc = allreduce_sum(h, h->dG, n);
+    tstop(h, T_ALLREDUCE);
+    if (rc) return rc;
+    if (G_out) IB_CUDA(h, cudaMemcpyAsync(G_out, h->dG, n * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->have_gram = true;
+    h->have_eig = h->have_lift = false;
+    h->strm_gram_chunks = 0;
+    h->strm_lift_chunks = 0;
+    return IB200_OK;
+}
+
+int ithaca_b200_pod_stream_lift_add(ithaca_b200_t* h, int slot, int r, int norm_kind)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->stream_mode || !h->have_eig || (slot != 0 && slot != 1) || h->slot[slot].ncells <= 0) {
+        set_error(h, "pod_stream_lift_add: needs pod_stream_gram_finish, pod_eig and a filled slot");
+        return IB200_ERR_ARG;
+    }
+    if (r <= 0 || r > h->m) { set_error(h, "pod_stream_lift_add: The number of requested modes cannot be bigger than the number of Snapshots"); return IB200_ERR_ARG; }
+    if (norm_kind != 0 && norm_kind != 1) { set_error(h, "pod_stream_lift_add: The PODnorm can be only L2 or Frobenius"); return IB200_ERR_ARG; }
+    if (h->strm_lift_chunks > 0 && r != h->r) { set_error(h, "pod_stream_lift_add: r differs from the previous chunk"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    const ithaca_b200::StreamSlot& sl = h->slot[slot];
+    int rc = stream_consume_begin(h, slot);
+    if (rc) return rc;
+    rc = lift_stream_add(h, slot == 0 ? h->dS : h->dS2, sl.ld, sl.ncells * h->dim, sl.V, r, norm_kind, sl.cell0 * h->dim, h->strm_ld,
+                         h->strm_lift_chunks == 0);
+    if (rc) return rc;
+    h->strm_lift_chunks++;
+    return stream_consume_end(h, slot);
+}
+
+int ithaca_b200_pod_stream_lift_finish(ithaca_b200_t* h, int r, double* const* mode_ptrs, double* normfact_out)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!h->stream_mode || h->strm_lift_chunks <= 0 || r != h->r) { set_error(h, "pod_stream_lift_finish: call pod_stream_lift_add for every chunk first (same r)"); return IB200_ERR_ARG; }
+    cudaSetDevice(h->device);
+    int rc = lift_stream_finish(h, r, h->strm_Nd, h->strm_ld);
+    if (rc) return rc;
+    tstart(h, T_DOWNLOAD);
+    if (mode_ptrs)
+        for (int i = 0; i < r; i++) {
+            if (!mode_ptrs[i]) { set_error(h, "pod_stream_lift_finish: null mode pointer"); return IB200_ERR_ARG; }
+            IB_CUDA(h, cudaMemcpyAsync(mode_ptrs[i], h->dPhi + (size_t)i * h->strm_ld, (size_t)h->strm_Nd * sizeof(double), cudaMemcpyDefault, h->stream));
+        }
+    if (normfact_out) IB_CUDA(h, cudaMemcpyAsync(normfact_out, h->dNorm, (size_t)r * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    tstop(h, T_DOWNLOAD);
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->have_lift = true;    // pod_lift_patch works on the eigenvectors and norm factors of this lift
+    h->strm_lift_chunks = 0;
     return IB200_OK;
 }
 

@@ -151,6 +151,11 @@ int lift_scaled_launch(ithaca_b200* h, int r, const double* dF);   // modes_i = 
 // snapshot-blocked lift: Phi (+)= S Q[first : first+nb, 0:r] (dTmp: r columns of ld doubles when accumulating); finish = norms + scale
 int lift_block_launch(ithaca_b200* h, const double* S, int nb, int first, int r, bool accumulate, double* dTmp);
 int lift_block_finish(ithaca_b200* h, int r, int norm_kind);
+// row-streamed lift: rows [row0, row0 + NdChunk) of the rank's mode matrix (columns of ldTotal doubles) = S_chunk Q_r, squared norms
+// added to h->dNorm (zeroed at the first chunk); finish = all-reduce, sqrt, scale of all NdTotal rows
+int lift_stream_add(ithaca_b200* h, const double* S, long long ldS, long long NdChunk, const double* Vchunk, int r, int norm_kind,
+                    long long row0, long long ldTotal, bool first_chunk);
+int lift_stream_finish(ithaca_b200* h, int r, long long NdTotal, long long ldTotal);
 // out[:, j] = Phi[:, 0:nmodes] * C[:, j] for j < kc <= 8 (C: nmodes x kc col-major on the device); out columns of ld doubles
 int reconstruct_launch(ithaca_b200* h, int nmodes, const double* dC, int kc, int clip, double* dOut);
 // gram.cu: general weighted contraction  out(i,j) = sum_k A(k,i) * V[k/dim] * B(k,j)  (V == nullptr: unweighted).
@@ -197,14 +202,14 @@ struct ithaca_b200 {
     int mat_cap = 0;           // capacity (m) of dG/dQ/dW/dEvals
     bool have_gram = false, have_eig = false;
     // lift state
-    int r = 0, rpad = 0;
-    double* dQr = nullptr;  // [m][rpad+2] k-major copy of Q_r for the lift kernel
+    int r = 0;
+    double* dQr = nullptr;  // [m][8 NB + 2] k-major copy of one column chunk of Q_r for the lift kernel
     size_t dQr_cap = 0;
     double* dPhi = nullptr;  // modes, r columns of ld doubles
     size_t dPhi_cap = 0;
     double* dNormPart = nullptr;
     size_t dNormPart_cap = 0;
-    double* dNorm = nullptr;  // rpad doubles: squared norms then norm factors
+    double* dNorm = nullptr;  // >= r doubles: squared norms then norm factors
     int norm_cap = 0;
     bool have_lift = false;
     bool have_modes = false;
@@ -227,6 +232,23 @@ struct ithaca_b200 {
     unsigned long long vol_gen = 1;  // bumped whenever a volume vector on the device may have changed
     int wexp_next = 0;
     int* dFlags = nullptr;
+    // row-streamed POD (pod_stream_*): the rank's shard passes through two chunk slots (slot 0 = dS, slot 1 = dS2)
+    struct StreamSlot {
+        double* V = nullptr;            // the chunk's cell volumes
+        int64_t V_cap = 0;
+        int64_t cell0 = 0, ncells = 0;  // which cells of the shard the slot holds (ncells = 0: empty)
+        int64_t ld = 0;
+        cudaEvent_t ready = nullptr;    // recorded on the copy stream after the chunk's last H2D copy
+        cudaEvent_t freed = nullptr;    // recorded on the compute stream after the slot's last consumer
+        bool ready_pending = false, freed_pending = false;
+    };
+    StreamSlot slot[2];
+    bool stream_mode = false;
+    int64_t strm_cells = 0, strm_Nd = 0, strm_ld = 0;   // the whole shard of this rank
+    int strm_gram_chunks = 0, strm_lift_chunks = 0;
+    cudaStream_t copy_stream = nullptr;
+    double* dGacc = nullptr;   // m x m partial Gram summed over the chunks
+    int gacc_cap = 0;
     ib200::DevBuf eigTmp; // eigensolve: m unsorted eigenvalues + 2 bounds
     ib200::DevBuf volT;   // pod_gram_volumes: the snapshot matrix scaled row-wise by sqrt|V_j|
 

@@ -37,7 +37,7 @@ __global__ void lift_prep_q_kernel(const double* __restrict__ Q, int m, int ldq,
 template <int NB>
 __global__ void __launch_bounds__(LIFT_THREADS, 1)
 lift_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUtensorMap tmQ,
-            const double* __restrict__ V, int dim, int norm_kind, long long Nd, long long ld, int m, int r,
+            const double* __restrict__ V, int dim, int norm_kind, long long Nd, long long ld /* of Phi */, int m, int r,
             int pitch, int qstage_bytes, int nstages, long long ntiles, double* __restrict__ Phi,
             double* __restrict__ norm_part)
 {
@@ -166,7 +166,7 @@ lift_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUt
 }
 
 // norm2[c] = sum over CTAs (fixed order) of the partial column sums.
-__global__ void lift_norm_reduce_kernel(const double* __restrict__ part, int nblocks, int ncol, double* __restrict__ norm2)
+__global__ void lift_norm_reduce_kernel(const double* __restrict__ part, int nblocks, int ncol, double* __restrict__ norm2, int accumulate)
 {
     const int c = blockIdx.x;
     __shared__ double sh[256];
@@ -178,7 +178,7 @@ __global__ void lift_norm_reduce_kernel(const double* __restrict__ part, int nbl
         if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
         __syncthreads();
     }
-    if (threadIdx.x == 0) norm2[c] = sh[0];
+    if (threadIdx.x == 0) norm2[c] = accumulate ? norm2[c] + sh[0] : sh[0];
 }
 
 __global__ void lift_sqrt_kernel(double* __restrict__ nrm, int r)
@@ -213,8 +213,14 @@ __global__ void lift_patch_kernel(const double* __restrict__ Sbc, long long rows
     }
 }
 
+// What one lift launch reads and writes: S = m columns of ldS doubles with Nd valid rows, weights V (one per dim rows),
+// Phi columns of ldPhi doubles (the row-streamed path writes a chunk's rows into the rank's full mode matrix).
+struct LiftSrc {
+    const double* S; long long ldS; long long Nd; const double* V; int dim; long long ldPhi;
+};
+
 template <int NB>
-static int lift_run(ithaca_b200* h, int m, double* Phi, int r, int norm_kind, const CUtensorMap& tmS, const CUtensorMap& tmQ,
+static int lift_run(ithaca_b200* h, const LiftSrc& src, int m, double* Phi, int r, int norm_kind, const CUtensorMap& tmS, const CUtensorMap& tmQ,
                     int pitch, int qstage_bytes, long long ntiles, int* grid_out)
 {
     const int stage_bytes = 8 * LIFT_SBOX + qstage_bytes;
@@ -233,7 +239,7 @@ static int lift_run(ithaca_b200* h, int m, double* Phi, int r, int norm_kind, co
         IB_CUDA(h, cudaMalloc(&h->dNormPart, need));
         h->dNormPart_cap = need;
     }
-    lift_kernel<NB><<<grid, LIFT_THREADS, smem, h->stream>>>(tmS, tmQ, h->dV, h->dim, norm_kind, h->Nd, h->ld,
+    lift_kernel<NB><<<grid, LIFT_THREADS, smem, h->stream>>>(tmS, tmQ, src.V, src.dim, norm_kind, src.Nd, src.ldPhi,
                                                              m, r, pitch, qstage_bytes, nstages, ntiles,
                                                              Phi, h->dNormPart);
     IB_CUDA(h, cudaGetLastError());
@@ -241,13 +247,19 @@ static int lift_run(ithaca_b200* h, int m, double* Phi, int r, int norm_kind, co
     return IB200_OK;
 }
 
-static int lift_ensure(ithaca_b200* h, int m, int r, int* NB_out)
+constexpr int LIFT_MAXC = 104;   // columns per launch (13 n8 fragments); wider lifts run as column chunks
+
+static int lift_pick_nb(int rc)
 {
-    if (r > 104) { set_error(h, "pod_lift: at most 104 modes per call are supported"); return IB200_ERR_ARG; }
     const int nbs[] = {2, 3, 4, 7, 13};
-    int NB = 13;
-    for (int c : nbs) if (c * 8 >= r) { NB = c; break; }
-    const int rpad = NB * 8, pitch = rpad + 2;
+    for (int c : nbs) if (c * 8 >= rc) return c;
+    return 13;
+}
+
+// Buffers of a lift of r columns from an m-row Q: the k-major Q stage, the norms, and (phi_ld > 0) r mode columns of phi_ld doubles.
+static int lift_ensure(ithaca_b200* h, int m, int r, long long phi_ld)
+{
+    const int pitch = lift_pick_nb(std::min(r, LIFT_MAXC)) * 8 + 2;
     const size_t qr_need = (size_t)m * pitch * sizeof(double);
     if (qr_need > h->dQr_cap) {
         if (h->dQr) cudaFree(h->dQr);
@@ -255,59 +267,80 @@ static int lift_ensure(ithaca_b200* h, int m, int r, int* NB_out)
         IB_CUDA(h, cudaMalloc(&h->dQr, qr_need));
         h->dQr_cap = qr_need;
     }
-    const size_t phi_need = (size_t)h->ld * r * sizeof(double);
+    const size_t phi_need = (size_t)phi_ld * r * sizeof(double);
     if (phi_need > h->dPhi_cap) {
         if (h->dPhi) cudaFree(h->dPhi);
         h->dPhi = nullptr; h->dPhi_cap = 0;
         IB_CUDA(h, cudaMalloc(&h->dPhi, phi_need));
         h->dPhi_cap = phi_need;
     }
-    if (rpad > h->norm_cap) {
+    if (r > h->norm_cap) {
         if (h->dNorm) cudaFree(h->dNorm);
         h->dNorm = nullptr; h->norm_cap = 0;
-        IB_CUDA(h, cudaMalloc(&h->dNorm, 104 * sizeof(double)));
-        h->norm_cap = 104;
+        const int cap = std::max(LIFT_MAXC, (r + 63) / 64 * 64);
+        IB_CUDA(h, cudaMalloc(&h->dNorm, (size_t)cap * sizeof(double)));
+        h->norm_cap = cap;
     }
-    *NB_out = NB;
     return IB200_OK;
 }
 
-// Phi = S Q: S = m columns of h->ld doubles, Q = rows [0, m) and columns [0, r) of a col-major matrix with leading
-// dimension ldq. The kernel also leaves the partial squared norms of what it wrote in h->dNormPart (grid x rpad).
-static int lift_core(ithaca_b200* h, const double* S, int m, const double* Q, int ldq, int r, int NB, int norm_kind, double* Phi,
+// Phi = S Q for ONE column chunk (r <= LIFT_MAXC): Q = rows [0, m) and columns [0, r) of a col-major matrix with leading
+// dimension ldq. The kernel also leaves the partial squared norms of what it wrote in h->dNormPart (grid x 8 NB).
+static int lift_core(ithaca_b200* h, const LiftSrc& src, int m, const double* Q, int ldq, int r, int NB, int norm_kind, double* Phi,
                      int* grid_out)
 {
     const int rpad = NB * 8, pitch = rpad + 2;
     lift_prep_q_kernel<<<std::min(1024, (m * pitch + 255) / 256), 256, 0, h->stream>>>(Q, m, ldq, r, pitch, h->dQr);
     CUtensorMap tmS, tmQ;
-    int rc = make_tmap_2d(h, &tmS, S, (uint64_t)h->Nd, (uint64_t)m, (uint64_t)h->ld * 8, 16, LIFT_KT, true);
+    int rc = make_tmap_2d(h, &tmS, src.S, (uint64_t)src.Nd, (uint64_t)m, (uint64_t)src.ldS * 8, 16, LIFT_KT, true);
     if (rc) return rc;
     rc = make_tmap_2d(h, &tmQ, h->dQr, (uint64_t)pitch, (uint64_t)m, (uint64_t)pitch * 8, (uint32_t)pitch, LIFT_KT, false);
     if (rc) return rc;
     const int qstage_bytes = (LIFT_KT * pitch * 8 + 1023) / 1024 * 1024;
-    const long long ntiles = (h->Nd + LIFT_ROWS - 1) / LIFT_ROWS;
+    const long long ntiles = (src.Nd + LIFT_ROWS - 1) / LIFT_ROWS;
     switch (NB) {
-        case 2: rc = lift_run<2>(h, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
-        case 3: rc = lift_run<3>(h, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
-        case 4: rc = lift_run<4>(h, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
-        case 7: rc = lift_run<7>(h, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
-        default: rc = lift_run<13>(h, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
+        case 2: rc = lift_run<2>(h, src, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
+        case 3: rc = lift_run<3>(h, src, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
+        case 4: rc = lift_run<4>(h, src, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
+        case 7: rc = lift_run<7>(h, src, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
+        default: rc = lift_run<13>(h, src, m, Phi, r, norm_kind, tmS, tmQ, pitch, qstage_bytes, ntiles, grid_out); break;
     }
     h->launches += 2;
     return rc;
 }
 
-// squared norms (already in h->dNorm, per rank) -> all-reduce -> sqrt -> Phi(:, c) /= n_c
-static int lift_finalize(ithaca_b200* h, int r)
+// Phi = S Q_r for any r <= m, in column chunks of at most LIFT_MAXC (the reference's default nmodes = 0 means m - 2 or m
+// modes, ITHACAPOD.C:111-130). norm2 != null: the r squared column norms (fixed-order sum over the CTAs of each chunk),
+// assigned or, for the row-streamed path, added to what is there.
+static int lift_cols(ithaca_b200* h, const LiftSrc& src, int m, const double* Q, int ldq, int r, int norm_kind, double* Phi,
+                     double* norm2, bool norm_accumulate)
+{
+    for (int c0 = 0; c0 < r; c0 += LIFT_MAXC) {
+        const int rc_ = std::min(LIFT_MAXC, r - c0);
+        const int NB = lift_pick_nb(rc_);
+        int grid = 0;
+        int rc = lift_core(h, src, m, Q + (size_t)c0 * ldq, ldq, rc_, NB, norm_kind, Phi + (size_t)c0 * src.ldPhi, &grid);
+        if (rc) return rc;
+        if (norm2) {
+            lift_norm_reduce_kernel<<<rc_, 256, 0, h->stream>>>(h->dNormPart, grid, NB * 8, norm2 + c0, norm_accumulate ? 1 : 0);
+            h->launches += 1;
+        }
+    }
+    IB_CUDA(h, cudaGetLastError());
+    return IB200_OK;
+}
+
+// squared norms (already in h->dNorm, per rank) -> all-reduce -> sqrt -> Phi(:, c) /= n_c   (Phi: Nd rows, columns of ld doubles)
+static int lift_finalize(ithaca_b200* h, int r, long long Nd, long long ld)
 {
     int rc = allreduce_sum(h, h->dNorm, (size_t)r);
     if (rc) return rc;
-    lift_sqrt_kernel<<<1, 128, 0, h->stream>>>(h->dNorm, r);
+    lift_sqrt_kernel<<<(r + 127) / 128, 128, 0, h->stream>>>(h->dNorm, r);
     cudaEventRecord(h->timers[T_LIFT].b, h->stream);
     h->timers[T_LIFT].used = true;
     cudaEventRecord(h->timers[T_SCALE].a, h->stream);
-    dim3 sg((unsigned)std::min<long long>((h->Nd + 1023) / 1024, 4LL * h->num_sms), (unsigned)r);
-    lift_scale_kernel<<<sg, 256, 0, h->stream>>>(h->dPhi, h->Nd, h->ld, r, h->dNorm);
+    dim3 sg((unsigned)std::min<long long>((Nd + 1023) / 1024, 4LL * h->num_sms), (unsigned)r);
+    lift_scale_kernel<<<sg, 256, 0, h->stream>>>(h->dPhi, Nd, ld, r, h->dNorm);
     cudaEventRecord(h->timers[T_SCALE].b, h->stream);
     h->timers[T_SCALE].used = true;
     IB_CUDA(h, cudaGetLastError());
@@ -317,16 +350,13 @@ static int lift_finalize(ithaca_b200* h, int r)
 
 int lift_launch(ithaca_b200* h, int r, int norm_kind)
 {
-    int NB = 0;
-    int rc = lift_ensure(h, h->m, r, &NB);
+    int rc = lift_ensure(h, h->m, r, h->ld);
     if (rc) return rc;
-    h->r = r; h->rpad = NB * 8;
+    h->r = r;
     cudaEventRecord(h->timers[T_LIFT].a, h->stream);
-    int grid = 0;
-    if ((rc = lift_core(h, h->dS, h->m, h->dQ, h->m, r, NB, norm_kind, h->dPhi, &grid))) return rc;
-    lift_norm_reduce_kernel<<<r, 256, 0, h->stream>>>(h->dNormPart, grid, h->rpad, h->dNorm);
-    h->launches += 1;
-    return lift_finalize(h, r);
+    const LiftSrc src{h->dS, h->ld, h->Nd, h->dV, h->dim, h->ld};
+    if ((rc = lift_cols(h, src, h->m, h->dQ, h->m, r, norm_kind, h->dPhi, h->dNorm, false))) return rc;
+    return lift_finalize(h, r, h->Nd, h->ld);
 }
 
 // Phi(:,c) *= f[c]; nrm[c] = 1 / f[c] (so that lift_patch's division applies the same factor)
@@ -347,19 +377,18 @@ __global__ void lift_inv_kernel(const double* __restrict__ f, int r, double* __r
 // modes_i = (S q_i) * factors[i] (getWeightedModes, ITHACAPOD.C:771-777). dF: r factors on the device.
 int lift_scaled_launch(ithaca_b200* h, int r, const double* dF)
 {
-    int NB = 0;
-    int rc = lift_ensure(h, h->m, r, &NB);
+    int rc = lift_ensure(h, h->m, r, h->ld);
     if (rc) return rc;
-    h->r = r; h->rpad = NB * 8;
+    h->r = r;
     cudaEventRecord(h->timers[T_LIFT].a, h->stream);
-    int grid = 0;
-    if ((rc = lift_core(h, h->dS, h->m, h->dQ, h->m, r, NB, 1, h->dPhi, &grid))) return rc;
+    const LiftSrc src{h->dS, h->ld, h->Nd, h->dV, h->dim, h->ld};
+    if ((rc = lift_cols(h, src, h->m, h->dQ, h->m, r, 1, h->dPhi, nullptr, false))) return rc;
     cudaEventRecord(h->timers[T_LIFT].b, h->stream);
     h->timers[T_LIFT].used = true;
     cudaEventRecord(h->timers[T_SCALE].a, h->stream);
     dim3 sg((unsigned)std::min<long long>((h->Nd + 1023) / 1024, 4LL * h->num_sms), (unsigned)r);
     lift_mul_kernel<<<sg, 256, 0, h->stream>>>(h->dPhi, h->Nd, h->ld, r, dF);
-    lift_inv_kernel<<<1, 128, 0, h->stream>>>(dF, r, h->dNorm);
+    lift_inv_kernel<<<(r + 127) / 128, 128, 0, h->stream>>>(dF, r, h->dNorm);
     cudaEventRecord(h->timers[T_SCALE].b, h->stream);
     h->timers[T_SCALE].used = true;
     IB_CUDA(h, cudaGetLastError());
@@ -399,12 +428,11 @@ phi_norm_part_kernel(const double* __restrict__ Phi, long long Nd, long long ld,
 
 int lift_block_launch(ithaca_b200* h, const double* S, int nb, int first, int r, bool accumulate, double* dTmp)
 {
-    int NB = 0;
-    int rc = lift_ensure(h, nb, r, &NB);
+    int rc = lift_ensure(h, nb, r, h->ld);
     if (rc) return rc;
-    h->r = r; h->rpad = NB * 8;
-    int grid = 0;
-    if ((rc = lift_core(h, S, nb, h->dQ + first, h->m, r, NB, 1, accumulate ? dTmp : h->dPhi, &grid))) return rc;
+    h->r = r;
+    const LiftSrc src{S, h->ld, h->Nd, h->dV, h->dim, h->ld};
+    if ((rc = lift_cols(h, src, nb, h->dQ + first, h->m, r, 1, accumulate ? dTmp : h->dPhi, nullptr, false))) return rc;
     if (accumulate) {
         dim3 g((unsigned)std::min<long long>((h->Nd + 1023) / 1024, 4LL * h->num_sms), (unsigned)r);
         axpy_cols_kernel<<<g, 256, 0, h->stream>>>(h->dPhi, dTmp, h->Nd, h->ld, r);
@@ -426,9 +454,27 @@ int lift_block_finish(ithaca_b200* h, int r, int norm_kind)
     }
     cudaEventRecord(h->timers[T_LIFT].a, h->stream);
     phi_norm_part_kernel<<<dim3(nblk, r), 256, 0, h->stream>>>(h->dPhi, h->Nd, h->ld, r, h->dV, h->dim, norm_kind, h->dNormPart);
-    lift_norm_reduce_kernel<<<r, 256, 0, h->stream>>>(h->dNormPart, nblk, r, h->dNorm);
+    lift_norm_reduce_kernel<<<r, 256, 0, h->stream>>>(h->dNormPart, nblk, r, h->dNorm, 0);
     h->launches += 2;
-    return lift_finalize(h, r);
+    return lift_finalize(h, r, h->Nd, h->ld);
+}
+
+// ---- row-streamed lift (pod_stream_*): the chunk's rows of the rank's mode matrix, squared norms added up over the chunks ----
+int lift_stream_add(ithaca_b200* h, const double* S, long long ldS, long long NdChunk, const double* Vchunk, int r, int norm_kind,
+                    long long row0, long long ldTotal, bool first_chunk)
+{
+    int rc = lift_ensure(h, h->m, r, ldTotal);
+    if (rc) return rc;
+    h->r = r;
+    if (first_chunk) IB_CUDA(h, cudaMemsetAsync(h->dNorm, 0, (size_t)r * sizeof(double), h->stream));
+    const LiftSrc src{S, ldS, NdChunk, Vchunk, h->dim, ldTotal};
+    return lift_cols(h, src, h->m, h->dQ, h->m, r, norm_kind, h->dPhi + row0, h->dNorm, true);
+}
+
+int lift_stream_finish(ithaca_b200* h, int r, long long NdTotal, long long ldTotal)
+{
+    cudaEventRecord(h->timers[T_LIFT].a, h->stream);
+    return lift_finalize(h, r, NdTotal, ldTotal);
 }
 
 // ---- Modes::reconstruct (Containers/Modes.C:294-305): out_j = Phi[:, 0:n] c_j, up to RC_K columns per launch -------------

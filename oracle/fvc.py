@@ -97,6 +97,20 @@ class Oracle:
         return out
 
     # ---- term builders ----
+    # threads > 1 (CPU-baseline timing only): the operator's outer loop is cut into slabs, one per host thread, through the
+    # *_range entry points (ctypes releases the GIL); every entry is computed by the same serial arithmetic either way.
+    @staticmethod
+    def _slabs(fn, args, n, threads):
+        import threading
+        threads = max(1, min(threads, n))
+        if threads == 1:
+            fn(*args, 0, n)
+            return
+        cuts = [n * t // threads for t in range(threads + 1)]
+        th = [threading.Thread(target=fn, args=(*args, cuts[t], cuts[t + 1])) for t in range(threads)]
+        [x.start() for x in th]
+        [x.join() for x in th]
+
     def mass_term(self, U):
         fs, pu = self._ptrs(U)
         N = len(fs)
@@ -104,37 +118,37 @@ class Oracle:
         self.L.fvo_mass_term(self._ref(), N, pu, P(M.ctypes.data))
         return M
 
-    def diffusive_term(self, U, Ub):
+    def diffusive_term(self, U, Ub, threads=1):
         fs, pu = self._ptrs(U)
         fb, pb = self._ptrs(Ub)
         N = len(fs)
         B = np.zeros((N, N), order="F")
-        self.L.fvo_diffusive_term(self._ref(), N, pu, pb, P(B.ctypes.data))
+        self._slabs(self.L.fvo_diffusive_term_range, (self._ref(), N, pu, pb, P(B.ctypes.data)), N, threads)
         return B
 
-    def pressure_gradient_term(self, U, Pm, Pb):
+    def pressure_gradient_term(self, U, Pm, Pb, threads=1):
         fs, pu = self._ptrs(U)
         fp, pp = self._ptrs(Pm)
         fb, pb = self._ptrs(Pb)
         K = np.zeros((len(fs), len(fp)), order="F")
-        self.L.fvo_pressure_gradient_term(self._ref(), len(fs), len(fp), pu, pp, pb, P(K.ctypes.data))
+        self._slabs(self.L.fvo_pressure_gradient_term_range, (self._ref(), len(fs), len(fp), pu, pp, pb, P(K.ctypes.data)), len(fp), threads)
         return K
 
-    def divergence_term(self, U, Ub, Pm):
+    def divergence_term(self, U, Ub, Pm, threads=1):
         fs, pu = self._ptrs(U)
         fb, pb = self._ptrs(Ub)
         fp, pp = self._ptrs(Pm)
         Pmat = np.zeros((len(fp), len(fs)), order="F")
-        self.L.fvo_divergence_term(self._ref(), len(fs), len(fp), pu, pb, pp, P(Pmat.ctypes.data))
+        self._slabs(self.L.fvo_divergence_term_range, (self._ref(), len(fs), len(fp), pu, pb, pp, P(Pmat.ctypes.data)), len(fs), threads)
         return Pmat
 
-    def convective_term_tens(self, U, Ub, cache=True):
+    def convective_term_tens(self, U, Ub, cache=True, threads=1):
         fs, pu = self._ptrs(U)
         fb, pb = self._ptrs(Ub)
         N = len(fs)
         C = np.zeros((N, N, N), order="F")
-        fn = self.L.fvo_convective_term_tens_cache if cache else self.L.fvo_convective_term_tens
-        fn(self._ref(), N, pu, pb, P(C.ctypes.data))
+        fn = self.L.fvo_convective_term_tens_cache_range if cache else self.L.fvo_convective_term_tens_range
+        self._slabs(fn, (self._ref(), N, pu, pb, P(C.ctypes.data)), N, threads)
         return C
 
     # ---- PPE operators (steadyNS::projectPPE) ----

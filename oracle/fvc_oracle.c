@@ -321,10 +321,10 @@ void fvo_mass_term(const fvo_mesh* m, int N, const double* const* U, double* M)
 
 /* steadyNS::diffusive_term, steadyNS.C:883-907: B(i,j) = domainIntegrate(U_i & laplacian(1, U_j)).
  * The laplacian of U_j is evaluated once per j instead of once per (i,j): same values, same order inside. */
-void fvo_diffusive_term(const fvo_mesh* m, int N, const double* const* U, const double* const* Ub, double* B)
+void fvo_diffusive_term_range(const fvo_mesh* m, int N, const double* const* U, const double* const* Ub, double* B, int j0, int j1)
 {
     double* L = (double*)malloc(sizeof(double) * 3 * m->nCells);
-    for (int j = 0; j < N; j++) {
+    for (int j = j0; j < j1; j++) {
         fvo_laplacian_vec(m, U[j], Ub[j], L);
         for (int i = 0; i < N; i++) B[i + (size_t)j * N] = fvo_domain_integrate_dot(m, U[i], L, 3);
     }
@@ -332,11 +332,11 @@ void fvo_diffusive_term(const fvo_mesh* m, int N, const double* const* U, const 
 }
 
 /* steadyNS::pressure_gradient_term, steadyNS.C:935-960: K(i,j) = domainIntegrate(U_i & grad(P_j)). K: N x Np. */
-void fvo_pressure_gradient_term(const fvo_mesh* m, int N, int Np, const double* const* U, const double* const* P,
-                                const double* const* Pb, double* K)
+void fvo_pressure_gradient_term_range(const fvo_mesh* m, int N, int Np, const double* const* U, const double* const* P,
+                                      const double* const* Pb, double* K, int j0, int j1)
 {
     double* G = (double*)malloc(sizeof(double) * 3 * m->nCells);
-    for (int j = 0; j < Np; j++) {
+    for (int j = j0; j < j1; j++) {
         fvo_grad_scalar(m, P[j], Pb[j], G);
         for (int i = 0; i < N; i++) K[i + (size_t)j * N] = fvo_domain_integrate_dot(m, U[i], G, 3);
     }
@@ -344,11 +344,11 @@ void fvo_pressure_gradient_term(const fvo_mesh* m, int N, int Np, const double* 
 }
 
 /* steadyNS::divergence_term, steadyNS.C:1112-1137: P(i,j) = domainIntegrate(P_i * div(U_j)). Pm: Np x N. */
-void fvo_divergence_term(const fvo_mesh* m, int N, int Np, const double* const* U, const double* const* Ub,
-                         const double* const* P, double* Pm)
+void fvo_divergence_term_range(const fvo_mesh* m, int N, int Np, const double* const* U, const double* const* Ub,
+                               const double* const* P, double* Pm, int j0, int j1)
 {
     double* D = (double*)malloc(sizeof(double) * m->nCells);
-    for (int j = 0; j < N; j++) {
+    for (int j = j0; j < j1; j++) {
         fvo_div_vec(m, U[j], Ub[j], D);
         for (int i = 0; i < Np; i++) Pm[i + (size_t)j * Np] = fvo_domain_integrate_dot(m, P[i], D, 1);
     }
@@ -357,11 +357,11 @@ void fvo_divergence_term(const fvo_mesh* m, int N, int Np, const double* const* 
 
 /* steadyNS::convective_term_tens, steadyNS.C:997-1036 (fluxMethod != "consistent"): the reference's own loop
  * nest, flux and div re-evaluated for every (i,j,k).  C(i,j,k) at C[i + N*(j + N*k)]. */
-void fvo_convective_term_tens(const fvo_mesh* m, int N, const double* const* U, const double* const* Ub, double* C)
+void fvo_convective_term_tens_range(const fvo_mesh* m, int N, const double* const* U, const double* const* Ub, double* C, int i0, int i1)
 {
     double* phi = (double*)malloc(sizeof(double) * (m->nInt + m->nBnd));
     double* D = (double*)malloc(sizeof(double) * 3 * m->nCells);
-    for (int i = 0; i < N; i++)
+    for (int i = i0; i < i1; i++)
         for (int j = 0; j < N; j++)
             for (int k = 0; k < N; k++) {
                 fvo_flux(m, U[j], Ub[j], phi);
@@ -373,11 +373,11 @@ void fvo_convective_term_tens(const fvo_mesh* m, int N, const double* const* U, 
 }
 
 /* steadyNS::convective_term_tens_cache, steadyNS.C:1038-1083: flux hoisted per j, div per (j,k). */
-void fvo_convective_term_tens_cache(const fvo_mesh* m, int N, const double* const* U, const double* const* Ub, double* C)
+void fvo_convective_term_tens_cache_range(const fvo_mesh* m, int N, const double* const* U, const double* const* Ub, double* C, int j0, int j1)
 {
     double* phi = (double*)malloc(sizeof(double) * (m->nInt + m->nBnd));
     double* D = (double*)malloc(sizeof(double) * 3 * m->nCells);
-    for (int j = 0; j < N; j++) {
+    for (int j = j0; j < j1; j++) {
         fvo_flux(m, U[j], Ub[j], phi);
         for (int k = 0; k < N; k++) {
             fvo_div_phi_vec(m, phi, U[k], Ub[k], D);
@@ -386,6 +386,31 @@ void fvo_convective_term_tens_cache(const fvo_mesh* m, int N, const double* cons
     }
     free(phi);
     free(D);
+}
+
+/* The whole operator = the slab [0, N) of its outer loop; the *_range forms let the CPU-baseline harness (bench_proj.py) give
+ * every host thread one slab (each entry is computed by the same serial arithmetic either way). */
+void fvo_diffusive_term(const fvo_mesh* m, int N, const double* const* U, const double* const* Ub, double* B)
+{
+    fvo_diffusive_term_range(m, N, U, Ub, B, 0, N);
+}
+void fvo_pressure_gradient_term(const fvo_mesh* m, int N, int Np, const double* const* U, const double* const* P,
+                                const double* const* Pb, double* K)
+{
+    fvo_pressure_gradient_term_range(m, N, Np, U, P, Pb, K, 0, Np);
+}
+void fvo_divergence_term(const fvo_mesh* m, int N, int Np, const double* const* U, const double* const* Ub,
+                         const double* const* P, double* Pm)
+{
+    fvo_divergence_term_range(m, N, Np, U, Ub, P, Pm, 0, N);
+}
+void fvo_convective_term_tens(const fvo_mesh* m, int N, const double* const* U, const double* const* Ub, double* C)
+{
+    fvo_convective_term_tens_range(m, N, U, Ub, C, 0, N);
+}
+void fvo_convective_term_tens_cache(const fvo_mesh* m, int N, const double* const* U, const double* const* Ub, double* C)
+{
+    fvo_convective_term_tens_cache_range(m, N, U, Ub, C, 0, N);
 }
 
 /* ---- PPE operators (steadyNS::projectPPE, steadyNS.C:354-553) ------------------------------------------------

@@ -20,6 +20,16 @@ CASES = [
 ]
 
 
+# the benchmark shapes (C3: m = 1000 vector snapshots, 50 modes; C5: m = 2000 scalar, 100 modes) on few cells: the 25- and
+# 50-tile-row Gram schedules, eig_jacobi_reg_kernel<32/64>, lift_kernel<7/13>. Outputs stored at a stride (G: every gs-th
+# row and column), the reference takes 8 s / 22 s per case, the test regenerates the inputs from the seed.
+SHAPE_CASES = [
+    # name, Nc, dim, m, r, seed, solver, gs
+    ("shape_c3", 6007, 3, 1000, 50, 77, "spectra", 7),
+    ("shape_c5", 6007, 1, 2000, 100, 78, "spectra", 13),
+]
+
+
 def variant_inputs():
     """Inputs of the getModesSVD / per-snapshot-volume getModes fixture (pod_variants.npz)."""
     Nc, dim, m, r = 1203, 3, 14, 4
@@ -53,6 +63,15 @@ if __name__ == "__main__":
             cum=out["cum"], evecs=out["evecs"], normfact=out["normfact"], modes_sub=out["modes"][::stride],
             stride=stride, modes_bc=(out["modes_bc"] if nbc else np.zeros((0, r))),
             meta=np.array([Nc, dim, m, r, seed, nbc]), solver=solver, norm=norm)
+        print("wrote", name, out["evals_norm"][:3])
+
+    for name, Nc, dim, m, r, seed, solver, gs in SHAPE_CASES:
+        S, V, _ = inputs(Nc, dim, m, r, seed, 0)
+        out = po.ref_getmodes(S, V, dim, r, solver, "L2")
+        stride = max(1, (Nc * dim) // 200)
+        np.savez_compressed(os.path.join(here, "pod_%s.npz" % name), G_sub=out["G"][::gs, ::gs], G_trace=np.trace(out["G"]),
+                            evals_norm=out["evals_norm"], cum=out["cum"], normfact=out["normfact"],
+                            modes_sub=out["modes"][::stride], stride=stride, gs=gs)
         print("wrote", name, out["evals_norm"][:3])
 
     Nc, dim, m, r, S, V, Ss, Vs = variant_inputs()

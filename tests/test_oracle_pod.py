@@ -8,7 +8,7 @@ import numpy as np
 import pytest
 
 sys.path.insert(0, os.path.join(os.path.dirname(__file__), "golden"))
-from make_golden import CASES, inputs  # noqa: E402
+from make_golden import CASES, SHAPE_CASES, inputs  # noqa: E402
 from oracle import pod_oracle as po, synth  # noqa: E402
 
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
@@ -129,3 +129,17 @@ def test_svd_and_per_snapshot_volume_variants_match_golden_and_reference_build()
         assert np.abs(c["evals_norm"] - d["evals_norm"]).max() <= 1e-12
         e = po.ref_getmodes_svd(S, V, dim, r)
         assert np.abs(e["evals_norm"] - g["svd_evals_norm"]).max() <= 1e-14
+
+
+@pytest.mark.parametrize("case", SHAPE_CASES, ids=[c[0] for c in SHAPE_CASES])
+def test_numpy_oracle_matches_reference_at_benchmark_shapes(case):
+    """m = 1000 vector (C3) and m = 2000 scalar (C5) on few cells: the restatement against the reference's stored results."""
+    name, Nc, dim, m, r, seed, solver, gs = case
+    g = load(name)
+    S, V, _ = inputs(Nc, dim, m, r, seed, 0)
+    out = po.getmodes(S, V, dim, r, solver, "L2")
+    assert np.abs(out["G"][::gs, ::gs] - g["G_sub"]).max() <= 1e-13 * np.abs(g["G_sub"]).max()
+    assert np.all(np.abs(out["evals_norm"][:r] - g["evals_norm"][:r]) <= 1e-10 * g["evals_norm"][:r])
+    assert np.all(np.abs(out["normfact"] - g["normfact"]) <= 1e-9 * g["normfact"])
+    sub = po.sign_align(out["modes"][::int(g["stride"])], g["modes_sub"])
+    assert (np.abs(sub - g["modes_sub"]).max(axis=0) / np.abs(g["modes_sub"]).max(axis=0)).max() <= 1e-8
