@@ -64,7 +64,7 @@ def oracle_checks_and_cpu_baseline(mesh, U, Ub, P, Pb, ops, N, Np, want_baseline
     Ko = orc.pressure_gradient_term(Uh[:n], Ph, Pbh)
     Po = orc.divergence_term(Uh[:n], Ubh[:n], Ph)
     Mo = orc.mass_term(Uh[:n])
-    checks = {"mesh": "the real C4 mesh, leading %d U / %d p fields, against oracle/fvc_oracle.c (1e-10 gate)" % (n, npp),
+    checks = {"mesh": "the benchmark's own mesh (%d cells), leading %d U / %d p fields, against oracle/fvc_oracle.c (1e-10 gate)" % (mesh.nCells, n, npp),
               "M_rel": rel(ops["M"][:n, :n], Mo), "B_rel": rel(ops["B"][:n, :n], Bo), "K_rel": rel(ops["K"][:n, :npp], Ko),
               "P_rel": rel(ops["P"][:npp, :n], Po), "C_rel": rel(ops["C"][:n, :n, :n], Co)}
     checks["pass"] = bool(max(checks[k] for k in ("M_rel", "B_rel", "K_rel", "P_rel", "C_rel")) <= 1e-10)
