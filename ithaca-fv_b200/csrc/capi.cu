@@ -10,6 +10,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
+#include <set>
 
 static thread_local std::string g_create_error;
 
@@ -19,6 +21,19 @@ void set_error(ithaca_b200* h, const std::string& msg)
 {
     if (h) h->err = msg;
     else g_create_error = msg;
+}
+
+const char* env_knob(const char* name)
+{
+    const char* v = getenv(name);
+    if (!v || !*v) return nullptr;
+    static std::mutex mu;
+    static std::set<std::string> seen;
+    std::lock_guard<std::mutex> lk(mu);
+    if (seen.insert(name).second)
+        fprintf(stderr, "[libithaca_b200] override active: %s=%s (measurement knob: changes kernel selection / schedule, not the "
+                        "defaults the parity tests cover)\n", name, v);
+    return v;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,

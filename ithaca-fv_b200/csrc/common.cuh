@@ -124,6 +124,9 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
                       const double* Ub, long long ldUb, int N, double* dC, double* ms_prep, double* ms_contract,
                       const double* Dfm = nullptr, long long ldD = 0, int Ni = 0);   // Dfm: Ni test fields for d_i (null: the basis)
 void set_error(ithaca_b200* h, const std::string& msg);
+// getenv for the ITHACA_B200_* measurement knobs: an active override is logged to stderr once per name, so that a drop-in
+// library never changes kernel selection or summation order silently.
+const char* env_knob(const char* name);
 
 // cuTensorMapEncodeTiled through cudaGetDriverEntryPoint (no link-time libcuda dependency).
 // 2-D FP64 tensor: inner dimension `inner` (contiguous), outer dimension `outer` with `pitch_bytes`.

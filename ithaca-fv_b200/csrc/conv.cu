@@ -286,7 +286,7 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
     const long long nFaces = m.nInt + m.nBnd;
     const long long nF = nFaces + (m.upwind ? m.nInt : 0);   // rank-one records: upwind doubles the internal faces
     int CV_KT = 32;   // faces per stage (ITHACA_B200_CONV_KT=16 selects the shorter stage)
-    if (const char* e = getenv("ITHACA_B200_CONV_KT")) CV_KT = (atoi(e) == 16) ? 16 : 32;
+    if (const char* e = env_knob("ITHACA_B200_CONV_KT")) CV_KT = (atoi(e) == 16) ? 16 : 32;
     const long long ntiles = (nF + CV_KT - 1) / CV_KT, nFpad = ntiles * CV_KT;
     const int Jpad = (N + 7) / 8 * 8;
     const int njblk = (Jpad + 8 * CV_JF - 1) / (8 * CV_JF);

@@ -408,6 +408,7 @@ __global__ void __launch_bounds__(NE > 32 ? 256 : NE > 16 ? 320 : 512, 1) eig_ja
                                 y[32 * e] = sn * xv + cs * yv;
                             }
                             a -= tt * c;
+                            __syncwarp();                       // every lane has read nrm[j] (bn) before lane 0 replaces it
                             if (lane == 0) nrm[j] = bn + tt * c;
                             rot++;
                         }
@@ -553,7 +554,7 @@ int eig_launch(ithaca_b200* h, int* sweeps)
     for (int attempt = 0; attempt < 3 && !ok; attempt++) {
         sigma = shifts[attempt];
         if (attempt > 0 && !(sigma > shifts[attempt - 1])) continue;
-        const char* evc = getenv("ITHACA_B200_CHOL");   // "blocked" keeps the multi-launch factorisation (A/B measurements)
+        const char* evc = env_knob("ITHACA_B200_CHOL");   // "blocked" keeps the multi-launch factorisation (A/B measurements)
         if (m <= CHS_MAX && !(evc && strcmp(evc, "blocked") == 0)) {
             const size_t csm = (size_t)m * (m + 1) / 2 * sizeof(double);
             IB_CUDA(h, cudaFuncSetAttribute(chol_small_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csm));
@@ -580,8 +581,8 @@ int eig_launch(ithaca_b200* h, int* sweeps)
     IB_CUDA(h, cudaMemsetAsync(flags, 0, 48 * sizeof(int), h->stream));
     double tol = std::sqrt((double)m) * eps;
     double* X = h->dW;
-    const char* ev = getenv("ITHACA_B200_EIG");       // "block" selects the shared-memory kernel (A/B measurements)
-    const char* evb = getenv("ITHACA_B200_EIG_B");    // columns per block (tuning)
+    const char* ev = env_knob("ITHACA_B200_EIG");       // "block" selects the shared-memory kernel (A/B measurements)
+    const char* evb = env_knob("ITHACA_B200_EIG_B");    // columns per block (tuning)
     const bool use_reg = m <= 2048 && !(ev && strcmp(ev, "block") == 0);
     int b, threads;
     size_t smem;

@@ -593,7 +593,7 @@ int atvb_launch(ithaca_b200* h, const double* A, long long lda, int Ma, const do
     for (double c : cost) total += c * (double)ksteps;
     const long long minlen = std::min<long long>(64, ksteps);     // shortest slab worth its pipeline fill and epilogue
     long long nctas = std::min<long long>(h->num_sms, std::max<long long>(1, (long long)njobs * ksteps / 128));
-    if (const char* e = getenv("ITHACA_B200_GRAM_CTAS")) nctas = std::max(1, atoi(e));
+    if (const char* e = env_knob("ITHACA_B200_GRAM_CTAS")) nctas = std::max(1, atoi(e));
     std::vector<GramSeg> segs;
     std::vector<int> seg_off, nsplit;
     gram_partition(cost, ksteps, K, nctas, minlen, segs, seg_off, nsplit);
@@ -609,11 +609,11 @@ int atvb_launch(ithaca_b200* h, const double* A, long long lda, int Ma, const do
     const int fixed = maxseg * (int)(sizeof(GramSeg) + sizeof(GramJob)) + 64;
     const int smem_cap = 227 * 1024 - 1024;
     int nstages = std::min(8, (smem_cap - fixed) / (stage_bytes + GRAM_KT * 8 + 16));
-    if (const char* e = getenv("ITHACA_B200_GRAM_STAGES")) nstages = std::max(2, std::min(nstages, atoi(e)));
+    if (const char* e = env_knob("ITHACA_B200_GRAM_STAGES")) nstages = std::max(2, std::min(nstages, atoi(e)));
     if (nstages < 2) { set_error(h, "gram: job does not fit shared memory"); return IB200_ERR_ARG; }
     const size_t smem = (size_t)nstages * (stage_bytes + GRAM_KT * 8 + 16) + fixed;
 
-    if (getenv("ITHACA_B200_DEBUG")) {
+    if (env_knob("ITHACA_B200_DEBUG")) {
         double useful = 0.0, crit = 0.0, tmax = 0.0, tsum = 0.0;
         for (int j = 0; j < njobs; j++) {
             int ld[4] = {0, 0, 0, 0};
@@ -666,7 +666,7 @@ int atvb_launch(ithaca_b200* h, const double* A, long long lda, int Ma, const do
     if (rc) return rc;
 
     long long* dbg = nullptr;   // ITHACA_B200_GRAM_TRACE=file: per (segment, warp) cycle counts, for calibrating the cost model
-    const char* trace = getenv("ITHACA_B200_GRAM_TRACE");
+    const char* trace = env_knob("ITHACA_B200_GRAM_TRACE");
     if (trace) IB_CUDA(h, cudaMalloc(&dbg, segs.size() * GRAM_MMA_WARPS * sizeof(long long)));
     IB_CUDA(h, cudaFuncSetAttribute(gram_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     Timer& tk = h->timers[T_GRAMK];

@@ -1354,7 +1354,7 @@ static int run_laplacians(ithaca_b200* h, ProjState* s, double* out)
         const size_t need = per * ((size_t)s->nCells * (3 + 3 + (s->corrected ? 9 : 0)) + (size_t)std::max<long long>(s->nBnd, 1) * 3);
         size_t have = s->conv.Ucm.cap + s->conv.Ubcm.cap + s->Tcm.cap + s->Lcm.cap, fr = 0, tot = 0;
         cudaMemGetInfo(&fr, &tot);
-        const char* ev = getenv("ITHACA_B200_LAP");
+        const char* ev = env_knob("ITHACA_B200_LAP");
         if (ev && strcmp(ev, "cm") == 0 && need <= have + fr / 2 && !(s->limK > 0.0) && s->snPsi < 0.0) {
             int rc;
             if ((rc = ensure(h, s->conv.Ucm, (size_t)s->nCells * 3 * per)) ||
@@ -1383,7 +1383,7 @@ static int run_laplacians(ithaca_b200* h, ProjState* s, double* out)
         }
     }
     int batch = 8;   // fields per launch (T holds batch gradient tensors); ITHACA_B200_LAP_BATCH overrides (tuning)
-    if (const char* e = getenv("ITHACA_B200_LAP_BATCH")) batch = std::max(1, std::min(atoi(e), 64));
+    if (const char* e = env_knob("ITHACA_B200_LAP_BATCH")) batch = std::max(1, std::min(atoi(e), 64));
     const long long ldT = 9 * pad16(s->nCells);
     if (s->corrected) {
         int rc = ensure(h, s->T, (size_t)batch * ldT * sizeof(double));
@@ -1476,7 +1476,7 @@ int ithaca_b200_mesh_upload(ithaca_b200_t* h, int64_t nCells, int64_t nIntFaces,
         for (long long f = 0; f < nIntFaces && !bad; f++)
             bad = ho[f] < 0 || ho[f] >= nCells || hn[f] < 0 || hn[f] >= nCells;
         if (bad) { drop(); set_error(h, "mesh_upload: owner/neighbour label out of range"); return IB200_ERR_ARG; }
-        const char* off_env = getenv("ITHACA_B200_NO_RENUMBER");
+        const char* off_env = env_knob("ITHACA_B200_NO_RENUMBER");
         if (off_env && *off_env == '1') {
             old2new.resize((size_t)nCells);
             fnew2old.resize((size_t)nIntFaces);
@@ -1488,7 +1488,7 @@ int ithaca_b200_mesh_upload(ithaca_b200_t* h, int64_t nCells, int64_t nIntFaces,
             // (laplacian 15.7 -> 17.8..25.2 ms): inside a breadth-first ball the neighbours of consecutive cells are no
             // longer consecutive, and coalescing matters more than L1 reuse
             int blk = 0;
-            if (const char* e = getenv("ITHACA_B200_RENUMBER_BLOCK")) blk = std::max(0, atoi(e));
+            if (const char* e = env_knob("ITHACA_B200_RENUMBER_BLOCK")) blk = std::max(0, atoi(e));
             if (blk > 1) mesh_renumber_blocked(nCells, nIntFaces, ho.data(), hn.data(), blk, old2new, fnew2old);
             else mesh_renumber(nCells, nIntFaces, ho.data(), hn.data(), old2new, fnew2old);
         }
@@ -1909,7 +1909,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
         }
         // fused face-based form (conv.cu), as for C: G(i,j,k) = sum_f flux_j(f) (Uf_k(f) . (g_i[own] - g_i[nei])), g_i = grad(P_i);
         // ITHACA_B200_G=mat keeps the materialised div(phi_j, U_k) fields (cross-check)
-        const char* gev = getenv("ITHACA_B200_G");
+        const char* gev = env_knob("ITHACA_B200_G");
         if (Np <= N && !(gev && strcmp(gev, "mat") == 0) && s->convScheme != 2) {
             ConvMesh cm;
             cm.nInt = s->nInt; cm.nBnd = s->nBnd; cm.owner = m.owner; cm.neigh = m.neigh; cm.Sf = m.Sf; cm.w = m.w; cm.bmask = m.bmask;
