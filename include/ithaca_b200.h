@@ -121,6 +121,14 @@ int ithaca_b200_pod_lift(ithaca_b200_t* h, int r, int norm_kind, double* const* 
  * (:780-785). factors: r doubles, host. mode_ptrs as in pod_lift. */
 int ithaca_b200_pod_lift_scaled(ithaca_b200_t* h, int r, const double* factors, double* const* mode_ptrs);
 
+/* getModes(snapshots, modes, fields2, ...) (ITHACAPOD.C:1940-2086): correlation matrix, eigensolve from `fields2` (pod_upload,
+ * pod_gram, pod_eig as usual), the modes are combinations of ANOTHER list of m fields (surfaceScalarField fluxes or
+ * volScalarFields in the reference's instantiations): modes_i = lambda_i^(-1/2) sum_j Q(j,i) snapshots[j] (:2016-2033).
+ * This call replaces the resident snapshot matrix by that second list (nValues doubles per field, any field type, host or
+ * device) and KEEPS the eigenvectors; follow with pod_lift_scaled(factors = |lambda_i|^(-1/2)) and, for the boundary values,
+ * pod_lift_patch. pod_gram afterwards is refused until the next pod_upload. */
+int ithaca_b200_pod_upload_second(ithaca_b200_t* h, const double* const* snap_ptrs, int m, int64_t nValues);
+
 /* Boundary rows: out = (Sbc * Q_r) with column i divided by normfact_i. Replaces ITHACAPOD.C:245-264
  * (modesEigBC). Sbc: rows*m col-major (what Foam2Eigen::PtrList2EigenBC returns for one patch,
  * Foam2Eigen.C:272-411); out: rows*r col-major. Host pointers. Must follow pod_lift. */
@@ -273,6 +281,14 @@ int ithaca_b200_mesh_addressing(ithaca_b200_t* h, int32_t* off, int32_t* ent, in
  * patch values in face order). which = 1: the n scalar fields of Pmodes (nCells / nBnd doubles). */
 int ithaca_b200_basis_upload(ithaca_b200_t* h, int which, const double* const* int_ptrs,
                              const double* const* bnd_ptrs, int n);
+
+/* fluxMethod == "consistent" (steadyNS.C:1010-1015, :1056, :1722): the convecting flux of mode j is the STORED face-flux field
+ * L_PHImodes[j] (the POD modes of phi, steadyNS.C:733-740) instead of linearInterpolate(L_U_SUPmodes[j]) & Sf.
+ * phi_ptrs[j] -> nInt+nBnd doubles in the caller's face order (internal field, then the boundary patches in order), n = the
+ * number of velocity basis fields; call after basis_upload(which = 0) (which resets to the interpolated flux, like
+ * phi_ptrs == NULL). Affects every fvc::div(phi_j, U_k) on the path: C (fused and materialised), G, BC2, Cf and
+ * fvc_eval(DIV_PHI); fvc::div(U_j) of the divergence term keeps the interpolated flux. Host or device pointers. */
+int ithaca_b200_flux_upload(ithaca_b200_t* h, const double* const* phi_ptrs, int n);
 
 enum { IB200_OP_M = 0, IB200_OP_B = 1, IB200_OP_K = 2, IB200_OP_P = 3, IB200_OP_C = 4, IB200_OP_C_MATERIALISED = 5,
        IB200_OP_D = 6, IB200_OP_G = 7, IB200_OP_BC3 = 8, IB200_OP_BC4 = 9, IB200_OP_BC1 = 10, IB200_OP_BC2 = 11,

@@ -20,7 +20,7 @@ SYMBOLS = [
     "ithaca_b200_create", "ithaca_b200_destroy", "ithaca_b200_last_error", "ithaca_b200_stream",
     "ithaca_b200_launch_count", "ithaca_b200_timings", "ithaca_b200_nccl_unique_id",
     "ithaca_b200_comm_init", "ithaca_b200_cell_range", "ithaca_b200_pod_set_volumes",
-    "ithaca_b200_pod_upload", "ithaca_b200_pod_gram", "ithaca_b200_pod_eig", "ithaca_b200_pod_set_gram",
+    "ithaca_b200_pod_upload", "ithaca_b200_pod_upload_second", "ithaca_b200_pod_gram", "ithaca_b200_pod_eig", "ithaca_b200_pod_set_gram",
     "ithaca_b200_pod_postprocess_eigenvalues", "ithaca_b200_pod_lift", "ithaca_b200_pod_lift_patch",
     "ithaca_b200_dmma_peak",
     "ithaca_b200_pod_set_modes", "ithaca_b200_pod_project", "ithaca_b200_pod_modes_mass", "ithaca_b200_pod_get_coeffs",
@@ -30,7 +30,7 @@ SYMBOLS = [
     "ithaca_b200_pod_stream_begin", "ithaca_b200_pod_stream_upload", "ithaca_b200_pod_stream_slot", "ithaca_b200_pod_stream_gram_add",
     "ithaca_b200_pod_stream_gram_finish", "ithaca_b200_pod_stream_lift_add", "ithaca_b200_pod_stream_lift_finish",
     "ithaca_b200_synth_snapshots", "ithaca_b200_synth_volumes",
-    "ithaca_b200_mesh_upload", "ithaca_b200_mesh_addressing", "ithaca_b200_basis_upload", "ithaca_b200_project",
+    "ithaca_b200_mesh_upload", "ithaca_b200_mesh_addressing", "ithaca_b200_basis_upload", "ithaca_b200_flux_upload", "ithaca_b200_project",
     "ithaca_b200_fvc_eval", "ithaca_b200_proj_timings", "ithaca_b200_project_background", "ithaca_b200_project_bc_velocity",
     "ithaca_b200_partition_create", "ithaca_b200_partition_destroy", "ithaca_b200_partition_sizes",
     "ithaca_b200_partition_addressing", "ithaca_b200_partition_gather", "ithaca_b200_mesh_upload_shard",
@@ -71,6 +71,7 @@ def lib():
         L.ithaca_b200_cell_range.argtypes = [L64, I, I, ctypes.POINTER(L64), ctypes.POINTER(L64)]
         L.ithaca_b200_pod_set_volumes.argtypes = [P, P, L64]
         L.ithaca_b200_pod_upload.argtypes = [P, P, I, I, L64]
+        L.ithaca_b200_pod_upload_second.argtypes = [P, P, I, L64]
         L.ithaca_b200_pod_gram.argtypes = [P, P]
         L.ithaca_b200_pod_gram_volumes.argtypes = [P, P, P]
         L.ithaca_b200_pod_eig.argtypes = [P, I, P, P, ctypes.POINTER(I)]
@@ -106,6 +107,7 @@ def lib():
         L.ithaca_b200_mesh_addressing.argtypes = [P, P, P, P, ctypes.POINTER(ctypes.c_uint64)]
         L.ithaca_b200_basis_upload.argtypes = [P, I, P, P, I]
         L.ithaca_b200_project.argtypes = [P, I, P]
+        L.ithaca_b200_flux_upload.argtypes = [P, P, I]
         L.ithaca_b200_fvc_eval.argtypes = [P, I, I, I, P]
         L.ithaca_b200_proj_timings.argtypes = [P, P, I]
         L.ithaca_b200_project_background.argtypes = [P, I, P, P, P]
@@ -310,6 +312,20 @@ class Pod:
         arr = (ctypes.c_void_p * m)(*ptrs)
         self._chk(self.L.ithaca_b200_pod_upload(self.h, arr, m, dim, nCells))
         self.m, self.dim = m, dim
+
+    def upload_second(self, snaps):
+        """The second field list of getModes(snapshots, modes, fields2, ...): replaces the resident matrix, keeps the eigensolve."""
+        if isinstance(snaps, np.ndarray) and snaps.ndim == 2:
+            assert snaps.flags.f_contiguous and snaps.dtype == np.float64
+            ptrs = [snaps.ctypes.data + j * snaps.strides[1] for j in range(snaps.shape[1])]
+            n = snaps.shape[0]
+        else:
+            ptrs = [_ptr(s) for s in snaps]
+            n = int(snaps[0].numel()) if hasattr(snaps[0], "numel") else int(snaps[0].size)
+        self._keep = snaps
+        arr = (ctypes.c_void_p * len(ptrs))(*ptrs)
+        self._chk(self.L.ithaca_b200_pod_upload_second(self.h, arr, len(ptrs), n))
+        self.nCells, self.dim = n, 1
 
     def gram(self, want=True):
         G = np.zeros((self.m, self.m), order="F") if want else None
@@ -606,6 +622,16 @@ class Projector:
         else:
             self.Np = n
 
+    def set_flux(self, phis):
+        """fluxMethod 'consistent': the stored face-flux modes L_PHImodes (steadyNS.C:1010-1015) convect instead of
+        linearInterpolate(U_j) & Sf. phis: N arrays of nInt+nBnd doubles (caller's face order), or None to reset."""
+        if phis is None:
+            self.pod._chk(self.L.ithaca_b200_flux_upload(self.h, None, 0))
+            return
+        keep = [np.ascontiguousarray(f, dtype=np.float64) if isinstance(f, np.ndarray) else f for f in phis]
+        a = (ctypes.c_void_p * len(keep))(*[_ptr(f) for f in keep])
+        self.pod._chk(self.L.ithaca_b200_flux_upload(self.h, a, len(keep)))
+
     def project(self, op):
         N, Np = self.N, self.Np
         shape = {"M": (N, N), "B": (N, N), "K": (N, Np), "P": (Np, N), "C": (N, N, N), "Cmat": (N, N, N), "D": (Np, Np),
@@ -735,6 +761,26 @@ def getModesVolumes(pod, snapshots, volumes, nmodes=0, solver="spectra", Sbc=Non
     Pbc = pod.lift_patch(Sbc, nmodes) if Sbc is not None else None   # same factors applied to the boundary rows
     evn = ev / ev.sum()
     return dict(G=G, evals=ev, evals_norm=evn, cum=np.cumsum(evn), evecs=Q, modes=Phi, modes_bc=Pbc)
+
+
+def getModesFields2(pod, snapshots, fields2, V, dim2, nmodes=0, solver="spectra", Sbc=None):
+    """getModes(snapshots, modes, fields2, ...) (ITHACAPOD.C:1940-2086): Gram and eigenvectors of `fields2` (dim2 components,
+    volumes V), modes_i = |lambda_i|^(-1/2) sum_j Q(j,i) snapshots[j] for a second list of the same length (any field type:
+    (n, m) Fortran array or m buffers; Sbc: its boundary rows). Both solvers keep nmodes eigenvalues here (:2004, :2011), there
+    is no negative shift, and they are normalised by their own sum (:2036)."""
+    m = fields2.shape[1] if isinstance(fields2, np.ndarray) else len(fields2)
+    nmodes = check_nmodes(m, nmodes, solver)
+    pod.set_volumes(V)
+    pod.upload(fields2, dim2)
+    G = pod.gram()
+    ev_all, Q = pod.eig(nmodes)
+    ev = ev_all[:nmodes]
+    factors = 1.0 / np.sqrt(np.abs(ev))
+    pod.upload_second(snapshots)
+    Phi = pod.lift_scaled(factors)
+    Pbc = pod.lift_patch(Sbc, nmodes) if Sbc is not None else None
+    evn = ev / ev.sum()
+    return dict(G=G, evals=ev, evals_norm=evn, cum=np.cumsum(evn), evecs=Q, factors=factors, modes=Phi, modes_bc=Pbc)
 
 
 def DEIMmodes(pod, snapshots, V, dim, nmodes=0, solver="spectra", norm="L2", Sbc=None):

@@ -348,6 +348,33 @@ int ithaca_b200_pod_upload(ithaca_b200_t* h, const double* const* snap_ptrs, int
     return IB200_OK;
 }
 
+// getModes(snapshots, modes, fields2, ...) (ITHACAPOD.C:1940-2086): the correlation matrix and the eigenvectors come from fields2,
+// the modes are combinations of ANOTHER field list of the same length. Replaces the resident snapshot matrix, keeps the eigensolve.
+int ithaca_b200_pod_upload_second(ithaca_b200_t* h, const double* const* snap_ptrs, int m, int64_t nValues)
+{
+    if (!h) return IB200_ERR_ARG;
+    if (!snap_ptrs || m <= 0 || nValues <= 0) { set_error(h, "pod_upload_second: bad argument"); return IB200_ERR_ARG; }
+    if (!h->have_eig || h->block_mode || h->stream_mode || m != h->m) {
+        set_error(h, "pod_upload_second: needs pod_upload / pod_gram / pod_eig of a field list with the same number of snapshots");
+        return IB200_ERR_ARG;
+    }
+    cudaSetDevice(h->device);
+    const int64_t ld = (nValues + 15) / 16 * 16;
+    int rc = ensure(h, &h->dS, &h->dS_cap, (size_t)ld * m * sizeof(double));
+    if (rc) return rc;
+    tstart(h, T_UPLOAD);
+    for (int j = 0; j < m; j++) {
+        if (!snap_ptrs[j]) { set_error(h, "pod_upload_second: null snapshot pointer"); return IB200_ERR_ARG; }
+        IB_CUDA(h, cudaMemcpyAsync(h->dS + (size_t)j * ld, snap_ptrs[j], (size_t)nValues * sizeof(double), cudaMemcpyDefault, h->stream));
+    }
+    tstop(h, T_UPLOAD);
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->dim = 1; h->Nd = nValues; h->ld = ld;
+    h->have_gram = false;          // the resident matrix no longer belongs to the Gram; the eigenvectors stay
+    h->have_lift = h->have_modes = false;
+    return IB200_OK;
+}
+
 int ithaca_b200_pod_gram(ithaca_b200_t* h, double* G_out)
 {
     if (!h) return IB200_ERR_ARG;

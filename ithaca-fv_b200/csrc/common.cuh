@@ -114,6 +114,8 @@ struct ConvMesh {
     const double *Sf, *w;
     const unsigned char* bmask;
     const unsigned char* cmask;   // per cell: 1 owned, 0 halo (null = all owned); scales U_i in d_i = U_i[own] - U_i[nei]
+    const double* flux = nullptr; // caller-supplied face fluxes (fluxMethod "consistent": L_PHImodes), field-major flux[j*ldF + f] in
+    long long ldF = 0;            // the kernels' face order; null: a_j = linearInterpolate(U_j) & Sf
     int upwind = 0;               // 1: "Gauss upwind" face value. Every internal face becomes TWO rank-one records,
                                   // (max(a,0), U_k[own], d) at f and (min(a,0), U_k[nei], d) at nInt + nBnd + f
 };

@@ -76,7 +76,8 @@ conv_face_prep_kernel(ConvMesh m, const double* __restrict__ Ucm, const double* 
             const double n0 = un[j], n1 = un[NP + j], n2 = un[2 * NP + j];
             const double b0 = w * o0 + w1 * n0, b1 = w * o1 + w1 * n1, b2 = w * o2 + w1 * n2;
             double a = 0.0;
-            a += b0 * s0; a += b1 * s1; a += b2 * s2;   // the flux is linearInterpolate(U_j) & Sf in every scheme
+            a += b0 * s0; a += b1 * s1; a += b2 * s2;   // the flux is linearInterpolate(U_j) & Sf in every scheme ...
+            if (m.flux) a = j < N ? m.flux[(size_t)j * m.ldF + f] : 0.0;   // ... unless the caller supplied L_PHImodes[j] ("consistent")
             if (!UPW) {
                 Aj[(size_t)f * NP + j] = a;
                 double* d = Dd + (size_t)f * 3 * NP;
@@ -124,6 +125,7 @@ conv_face_prep_kernel(ConvMesh m, const double* __restrict__ Ucm, const double* 
             const double b0 = ub[j], b1 = ub[NP + j], b2 = ub[2 * NP + j];
             double a = 0.0;
             if (on) { a += b0 * s0; a += b1 * s1; a += b2 * s2; }
+            if (m.flux) a = (on && j < N) ? m.flux[(size_t)j * m.ldF + f] : 0.0;
             Aj[(size_t)f * NP + j] = a;
             double* d = Dd + (size_t)f * 3 * NP;
             const double* qo = Dcm ? Dcm + (size_t)o * 3 * NP : uo;

@@ -70,6 +70,8 @@ struct ProjState {
     DevBuf U, Ub, P, Pb;
     DevBuf flux;   // nU columns of ldF doubles (all faces)
     bool have_flux = false;
+    DevBuf fluxUser;          // caller-supplied convecting fluxes (ithaca_b200_flux_upload: L_PHImodes of fluxMethod "consistent")
+    bool flux_user = false;   // the convective operators take fluxUser instead of linearInterpolate(U_j) & Sf
     DevBuf work;   // operator fields, columns of ldU (vector) or ldP (scalar) doubles
     DevBuf T;      // gradient tensors of a batch of fields, 9*nCells doubles each
     DevBuf gradP;      // grad(P_i), Np columns of ldU doubles (D and G operators)
@@ -106,7 +108,7 @@ void proj_destroy(ithaca_b200* h)
     ProjState* s = h->proj;
     if (!s) return;
     for (DevBuf* b : {&s->owner, &s->neigh, &s->Sf, &s->magSf, &s->w, &s->dc, &s->dcB, &s->corr, &s->V, &s->bmask,
-                      &s->off, &s->ent, &s->other, &s->cnt, &s->blocksum, &s->U, &s->Ub, &s->P, &s->Pb, &s->flux,
+                      &s->off, &s->ent, &s->other, &s->cnt, &s->blocksum, &s->U, &s->Ub, &s->P, &s->Pb, &s->flux, &s->fluxUser,
                       &s->owner0, &s->neigh0, &s->off0, &s->ent0, &s->other0, &s->entL, &s->otherL, &s->Cc, &s->Cf, &s->Tall, &s->perm, &s->fperm, &s->stage, &s->Vw, &s->cmask, &s->Tcm, &s->Lcm, &s->gradP, &s->bndA, &s->bndB,
                       &s->work, &s->T, &s->out, &s->conv.Ucm, &s->conv.Ubcm, &s->conv.Dcm, &s->conv.Aj, &s->conv.Bk, &s->conv.Dd,
                       &s->conv.ws, &s->conv.chunks})
@@ -1309,6 +1311,9 @@ static int need_flux(ithaca_b200* h, ProjState* s)
     return IB200_OK;
 }
 
+// the convecting flux of mode j in fvc::div(phi_j, U_k): the caller's (fluxMethod "consistent", steadyNS.C:1010-1015) or the computed one
+static inline const double* conv_flux(const ProjState* s) { return s->flux_user ? s->fluxUser.as<double>() : s->flux.as<double>(); }
+
 // grad(U_k) of ALL basis fields for the linearUpwind correction (limited when the cellMDLimited gradient is selected, as the
 // scheme's "grad(U)" argument names the case's gradient scheme)
 static int need_gradU_all(ithaca_b200* h, ProjState* s)
@@ -1443,7 +1448,7 @@ int ithaca_b200_mesh_upload(ithaca_b200_t* h, int64_t nCells, int64_t nIntFaces,
     if (!h->proj) h->proj = new ProjState();
     ProjState* s = h->proj;
     s->have_mesh = false;
-    s->have_flux = false;
+    s->have_flux = false; s->flux_user = false;
     h->vol_gen++;
     s->nCells = nCells; s->nInt = nIntFaces; s->nBnd = nBndFaces;
     const long long nF = nIntFaces + nBndFaces;
@@ -1671,8 +1676,40 @@ int ithaca_b200_basis_upload(ithaca_b200_t* h, int which, const double* const* i
                                        cudaMemcpyDefault, h->stream));
     }
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
-    if (which == 0) { s->nU = n; s->ldU = ld; s->ldUb = ldb; s->ldF = pad16(s->nInt + s->nBnd); s->have_flux = false; s->have_Tall = false; }
+    if (which == 0) { s->nU = n; s->ldU = ld; s->ldUb = ldb; s->ldF = pad16(s->nInt + s->nBnd); s->have_flux = false; s->flux_user = false; s->have_Tall = false; }
     else { s->nP = n; s->ldP = ld; s->ldPb = ldb; }
+    return IB200_OK;
+}
+
+// phi in the caller's face order -> the kernels' order (internal face at new position f sat at fperm[f]); 0 on `empty` faces
+__global__ void permute_flux_in_kernel(const double* __restrict__ in, const int* __restrict__ fperm, const unsigned char* __restrict__ bmask,
+                                       long long nInt, long long nF, double* __restrict__ out)
+{
+    for (long long f = blockIdx.x * (long long)blockDim.x + threadIdx.x; f < nF; f += (long long)gridDim.x * blockDim.x)
+        out[f] = (f < nInt) ? in[fperm[f]] : (bmask[f - nInt] ? in[f] : 0.0);
+}
+
+int ithaca_b200_flux_upload(ithaca_b200_t* h, const double* const* phi_ptrs, int n)
+{
+    if (!h) return IB200_ERR_ARG;
+    ProjState* s = h->proj;
+    PROJ_REQUIRE(s && s->have_mesh && s->nU > 0, "flux_upload: call mesh_upload and basis_upload(U) first");
+    cudaSetDevice(h->device);
+    if (!phi_ptrs) { s->flux_user = false; return IB200_OK; }   // back to linearInterpolate(U_j) & Sf
+    PROJ_REQUIRE(n == s->nU, "flux_upload: one flux field per velocity basis field (L_PHImodes has the size of L_U_SUPmodes)");
+    const long long nF = s->nInt + s->nBnd;
+    int rc = ensure(h, s->fluxUser, (size_t)s->nU * s->ldF * sizeof(double));
+    if (rc) return rc;
+    for (int j = 0; j < n; j++) {
+        PROJ_REQUIRE(phi_ptrs[j], "flux_upload: null field pointer");
+        IB_CUDA(h, cudaMemcpyAsync(s->stage.p, phi_ptrs[j], (size_t)nF * sizeof(double), cudaMemcpyDefault, h->stream));
+        permute_flux_in_kernel<<<(unsigned)std::min<long long>((nF + 255) / 256, 64LL * h->num_sms), 256, 0, h->stream>>>(
+            s->stage.as<double>(), s->fperm.as<int>(), mesh_dev(s).bmask, s->nInt, nF, s->fluxUser.as<double>() + (size_t)j * s->ldF);
+        h->launches += 1;
+    }
+    IB_CUDA(h, cudaGetLastError());
+    IB_CUDA(h, cudaStreamSynchronize(h->stream));
+    s->flux_user = true;
     return IB200_OK;
 }
 
@@ -1705,7 +1742,7 @@ int ithaca_b200_fvc_eval(ithaca_b200_t* h, int op, int j, int k, double* out)
         if ((rc = need_flux(h, s))) return rc;
         if ((rc = ensure(h, s->work, (size_t)s->nU * s->ldU * sizeof(double)))) return rc;
         LAUNCH_DIV_PHI(div_phi_kernel, dim3(gx(s->nCells), gy(s->nU)), 
-            m, s->flux.as<double>() + (size_t)j * s->ldF, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb, s->nU,
+            m, conv_flux(s) + (size_t)j * s->ldF, s->U.as<double>(), s->ldU, s->Ub.as<double>(), s->ldUb, s->nU,
             s->work.as<double>(), s->ldU);
         h->launches += 1;
         nout = (size_t)3 * s->nCells;
@@ -1844,6 +1881,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
         cm.nInt = s->nInt; cm.nBnd = s->nBnd; cm.owner = m.owner; cm.neigh = m.neigh; cm.Sf = m.Sf; cm.w = m.w; cm.bmask = m.bmask;
         cm.cmask = shard ? s->cmask.as<unsigned char>() : nullptr;
         cm.upwind = s->convScheme == 1 ? 1 : 0;
+        if (s->flux_user) { cm.flux = s->fluxUser.as<double>(); cm.ldF = s->ldF; }
         rc = conv_fused_launch(h, &s->conv, cm, s->nCells, U, s->ldU, s->Ub.as<double>(), s->ldUb, N, s->out.as<double>(), &s->ms[6],
                                &s->ms[5]);
         if (rc) return rc;
@@ -1863,7 +1901,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
                 StageTimer t(h->stream, &s->ms[1]);
                 for (int jj = 0; jj < nj; jj++) {
                     LAUNCH_DIV_PHI(div_phi_kernel, dim3(gx(s->nCells), gy(N)), 
-                        m, s->flux.as<double>() + (size_t)(j0 + jj) * s->ldF, U, s->ldU, s->Ub.as<double>(), s->ldUb, N,
+                        m, conv_flux(s) + (size_t)(j0 + jj) * s->ldF, U, s->ldU, s->Ub.as<double>(), s->ldUb, N,
                         s->work.as<double>() + (size_t)jj * N * s->ldU, s->ldU);
                     h->launches += 1;
                 }
@@ -1915,6 +1953,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
             cm.nInt = s->nInt; cm.nBnd = s->nBnd; cm.owner = m.owner; cm.neigh = m.neigh; cm.Sf = m.Sf; cm.w = m.w; cm.bmask = m.bmask;
             cm.cmask = shard ? s->cmask.as<unsigned char>() : nullptr;
         cm.upwind = s->convScheme == 1 ? 1 : 0;
+        if (s->flux_user) { cm.flux = s->fluxUser.as<double>(); cm.ldF = s->ldF; }
             rc = conv_fused_launch(h, &s->conv, cm, s->nCells, U, s->ldU, s->Ub.as<double>(), s->ldUb, N, s->out.as<double>(), &s->ms[6],
                                    &s->ms[5], s->gradP.as<double>(), s->ldU, Np);   // writes G(i,j,k) at i + Np*(j + N*k)
             if (rc) return rc;
@@ -1930,7 +1969,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
                 StageTimer t(h->stream, &s->ms[1]);
                 for (int jj = 0; jj < nj; jj++) {
                     LAUNCH_DIV_PHI(div_phi_kernel, dim3(gx(s->nCells), gy(N)), 
-                        m, s->flux.as<double>() + (size_t)(j0 + jj) * s->ldF, U, s->ldU, s->Ub.as<double>(), s->ldUb, N,
+                        m, conv_flux(s) + (size_t)(j0 + jj) * s->ldF, U, s->ldU, s->Ub.as<double>(), s->ldUb, N,
                         s->work.as<double>() + (size_t)jj * N * s->ldU, s->ldU);
                     h->launches += 1;
                 }
@@ -2029,7 +2068,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
                     StageTimer t(h->stream, &s->ms[1]);
                     for (int jj = 0; jj < nj; jj++) {
                         LAUNCH_DIV_PHI(bnd_div_phi_dot_sf_kernel, dim3(gx(s->nBnd), gy(N)), 
-                            m, shard ? s->cmask.as<unsigned char>() : nullptr, s->flux.as<double>() + (size_t)(j0 + jj) * s->ldF, U, s->ldU,
+                            m, shard ? s->cmask.as<unsigned char>() : nullptr, conv_flux(s) + (size_t)(j0 + jj) * s->ldF, U, s->ldU,
                             s->Ub.as<double>(), s->ldUb, N, s->bndA.as<double>() + (size_t)jj * N * ldB, ldB);
                         h->launches += 1;
                     }
@@ -2075,6 +2114,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
             cm.nInt = s->nInt; cm.nBnd = s->nBnd; cm.owner = m.owner; cm.neigh = m.neigh; cm.Sf = m.Sf; cm.w = m.w; cm.bmask = m.bmask;
             cm.cmask = shard ? s->cmask.as<unsigned char>() : nullptr;
         cm.upwind = s->convScheme == 1 ? 1 : 0;
+        if (s->flux_user) { cm.flux = s->fluxUser.as<double>(); cm.ldF = s->ldF; }
             rc = conv_fused_launch(h, &s->conv, cm, s->nCells, U, s->ldU, s->Ub.as<double>(), s->ldUb, N, s->out.as<double>(), &s->ms[6],
                                    &s->ms[5], s->gradP.as<double>(), s->ldU, Np);   // writes Cf(i,j,k) at i + Np*(j + N*k)
             if (rc) return rc;
@@ -2088,7 +2128,7 @@ int ithaca_b200_project(ithaca_b200_t* h, int op, double* out)
             const int nj = std::min(jb, N - j0);
             for (int jj = 0; jj < nj; jj++) {
                 LAUNCH_DIV_PHI(div_phi_kernel, dim3(gx(s->nCells), gy(N)), 
-                    m, s->flux.as<double>() + (size_t)(j0 + jj) * s->ldF, U, s->ldU, s->Ub.as<double>(), s->ldUb, N,
+                    m, conv_flux(s) + (size_t)(j0 + jj) * s->ldF, U, s->ldU, s->Ub.as<double>(), s->ldUb, N,
                     s->work.as<double>() + (size_t)jj * N * s->ldU, s->ldU);
                 h->launches += 1;
             }

@@ -151,6 +151,19 @@ class Oracle:
         self._slabs(fn, (self._ref(), N, pu, pb, P(C.ctypes.data)), N, threads)
         return C
 
+    def convective_term_tens_consistent(self, U, Ub, Phi):
+        """fluxMethod == "consistent" (steadyNS.C:1010-1015): C(i,j,k) = domainIntegrate(U_i & fvc::div(L_PHImodes[j], U_k)),
+        the reference's loop nest with the stored flux fields Phi[j] (nInt+nBnd values, 0 on `empty` faces)."""
+        N = len(U)
+        C = np.zeros((N, N, N), order="F")
+        V3 = np.repeat(_c(self.mesh.V), 3)
+        for j in range(N):
+            for k in range(N):
+                D = self.div_phi(_c(Phi[j]), U[k], Ub[k])
+                for i in range(N):
+                    C[i, j, k] = np.dot(V3 * _c(U[i]), D)
+        return C
+
     # ---- PPE operators (steadyNS::projectPPE) ----
     def laplacian_pressure(self, Pm, Pb):
         fp, pp = self._ptrs(Pm)

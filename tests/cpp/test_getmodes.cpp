@@ -2,6 +2,7 @@
 // file written by tests/test_cpp_shim.py, modes written back for comparison with the oracle.
 //   usage: test_getmodes <input.bin> <output.bin> <outDir>
 #include "../../host/ITHACAPOD_b200.H"
+#include <unistd.h>
 
 #include <cstdint>
 #include <cstring>
@@ -60,7 +61,7 @@ int main(int argc, char** argv)
 {
     if (argc < 4)
     {
-        std::fprintf(stderr, "usage: %s in.bin out.bin outDir\n", argv[0]);
+        std::fprintf(stderr, "usage: %s in.bin out.bin outDir [rank nranks idfile]\n", argv[0]);
         return 2;
     }
     FILE* fi = std::fopen(argv[1], "rb");
@@ -105,6 +106,40 @@ int main(int argc, char** argv)
     para.outDir = argv[3];
     para.precision = 16;
     para.outytpe = std::ios_base::scientific;
+    if (argc >= 7)
+    {
+        // Pstream::parRun() stand-in: this process is one rank with its own cell shard and GPU; rank 0's NCCL id travels
+        // through a file (in ITHACA-FV: Pstream::broadcast)
+        para.parallel.rank = std::atoi(argv[4]);
+        para.parallel.nranks = std::atoi(argv[5]);
+        para.device = para.parallel.rank;
+        const std::string idfile = argv[6];
+        const int rank = para.parallel.rank;
+        para.parallel.broadcastId = [idfile, rank](void* id128)
+        {
+            if (rank == 0)
+            {
+                FILE* f = std::fopen((idfile + ".tmp").c_str(), "wb");
+                std::fwrite(id128, 1, 128, f);
+                std::fclose(f);
+                std::rename((idfile + ".tmp").c_str(), idfile.c_str());
+                return;
+            }
+            for (int tries = 0; tries < 6000; tries++)
+            {
+                FILE* f = std::fopen(idfile.c_str(), "rb");
+                if (f)
+                {
+                    const size_t n = std::fread(id128, 1, 128, f);
+                    std::fclose(f);
+                    if (n == 128) return;
+                }
+                usleep(10000);
+            }
+            std::fprintf(stderr, "id transport timed out\n");
+            std::abort();
+        };
+    }
     mkdir(argv[3], 0777);
     mkdir((std::string(argv[3]) + "/POD").c_str(), 0777);
     int exported = 0, readCalls = 0;

@@ -70,7 +70,7 @@ def test_projectSUP_files_match_oracle_and_are_read_back(pkg, tmp_path):
     NU, NP, NSUP = 4, 3, 2
     name, typ, sl = [p for p in mesh.patch_slices() if p[1] != "empty" and p[2].stop > p[2].start][0]
     pidx = [p[0] for p in mesh.patch_slices()].index(name)
-    write_input(tmp_path / "in.bin", mesh, lift, U, sup, P, NU, NP, NSUP, penalty=True, inlet=[(pidx, 0), (pidx, 1)], exports=1 | 8)
+    write_input(tmp_path / "in.bin", mesh, lift, U, sup, P, NU, NP, NSUP, penalty=True, inlet=[(pidx, 0), (pidx, 1)], exports=1 | 4 | 8)
     mdir = str(tmp_path / "ITHACAoutput" / "Matrices") + "/"
     r = subprocess.run([exe, str(tmp_path / "in.bin"), mdir], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
@@ -90,6 +90,10 @@ def test_projectSUP_files_match_oracle_and_are_read_back(pkg, tmp_path):
     assert C.shape == Cr.shape and rel(C, Cr) <= TOL
     # exports: python text and cnpy .npy of the same operators
     assert np.array_equal(np.load(mdir + "C.npy"), C) and os.path.exists(mdir + "B_mat.py")
+    # projectSUP's export block as coded (steadyNS.C:680, :698-699): the C tensor goes out in the "python" format under every
+    # switch, into Matrices/ for exportPython and into Matrices/C for exportTxt; the matrices follow the switch
+    assert os.path.exists(mdir + "C_mat.py") and os.path.exists(mdir + "C/C_mat.py") and os.path.exists(mdir + "B_mat.txt")
+    assert not os.path.exists(mdir + "C0_mat.txt") and not os.path.exists(mdir + "C/C0_mat.txt")
     # penalty terms: the leading NU + NSUP fields of L_U_SUPmodes, one file per inletIndex row
     X = np.stack([b.reshape(-1, 3)[sl, 1] for b in Ub[:NU + NSUP]], axis=1)
     v1 = np.loadtxt(mdir + "bcVelVec/bcVelVec1_mat.txt")

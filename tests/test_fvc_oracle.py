@@ -241,3 +241,21 @@ def test_flux_method_operators_definitions(cyl):
     A = o.div_phi(o.flux(U[2], Ub[2]), U[0], Ub[0])
     d = o.div(A, np.ascontiguousarray(A.reshape(-1, 3)[own].ravel()))
     assert abs(Cf[1, 2, 0] - np.sum(m.V * P[0] * d)) <= 1e-12 * np.abs(Cf).max()
+
+
+def test_consistent_flux_nest_reduces_to_the_interpolated_one():
+    """steadyNS.C:1010-1015: with L_PHImodes[j] = linearInterpolate(U_j) & Sf the "consistent" loop nest is the other branch;
+    C is linear in the flux field."""
+    from oracle import fvc, polymesh as pm
+    mesh = pm.synthetic_hex(6, 5, 4, kind="box", seed=3, perturb=0.1)
+    U, Ub, P, Pb = fvc.synthetic_basis(mesh, 3, 2, seed=1)
+    orc = fvc.Oracle(mesh)
+    Phi = [orc.flux(U[j], Ub[j]) for j in range(3)]
+    C = orc.convective_term_tens_consistent(U, Ub, Phi)
+    Cr = orc.convective_term_tens(U, Ub)
+    assert np.abs(C - Cr).max() <= 1e-13 * np.abs(Cr).max()
+    C2 = orc.convective_term_tens_consistent(U, Ub, [2.0 * p for p in Phi])
+    assert np.abs(C2 - 2.0 * C).max() <= 1e-13 * np.abs(C).max()
+    # slabs of the outer loop over host threads give the same entries (CPU-baseline harness)
+    assert np.array_equal(orc.convective_term_tens(U, Ub, threads=3), Cr)
+    assert np.array_equal(orc.diffusive_term(U, Ub, threads=2), orc.diffusive_term(U, Ub))

@@ -143,3 +143,19 @@ def test_numpy_oracle_matches_reference_at_benchmark_shapes(case):
     assert np.all(np.abs(out["normfact"] - g["normfact"]) <= 1e-9 * g["normfact"])
     sub = po.sign_align(out["modes"][::int(g["stride"])], g["modes_sub"])
     assert (np.abs(sub - g["modes_sub"]).max(axis=0) / np.abs(g["modes_sub"]).max(axis=0)).max() <= 1e-8
+
+
+def test_getmodes_fields2_definition():
+    """getModes(snapshots, modes, fields2, ...) restatement (ITHACAPOD.C:1940-2086): with snapshots == fields2 the modes
+    (S Q) lambda^-1/2 are V-orthonormal; a second list only changes what is combined, not the eigenpairs."""
+    Nc, m, r = 700, 12, 4
+    S2 = synth.snapshots(Nc, 3, m, 6, 1)
+    V = synth.volumes(Nc, 1)
+    o = po.getmodes_fields2(S2, S2, V, 3, r, "eigen")
+    W = np.repeat(V, 3)
+    assert np.abs(o["modes"].T @ (W[:, None] * o["modes"]) - np.eye(r)).max() <= 1e-12
+    S = np.random.default_rng(0).standard_normal((333, m))
+    o2 = po.getmodes_fields2(S, S2, V, 3, r, "spectra")
+    assert np.array_equal(o2["evals"], o["evals"]) and len(o2["evals_norm"]) == r
+    assert np.abs(o2["modes"] - (S @ o["evecs"]) / np.sqrt(o["evals"])).max() <= 1e-12 * np.abs(o2["modes"]).max()
+    assert abs(o2["evals_norm"].sum() - 1.0) <= 1e-14

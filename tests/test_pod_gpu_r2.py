@@ -250,3 +250,27 @@ def test_row_streamed_in_place_producer(pkg, pod):
     assert rel_max(G, ref["G"]) <= 1e-13
     assert np.all(np.abs(nf - ref["normfact"]) <= 1e-9 * ref["normfact"])
     assert modes_rel(Phi, ref["modes"]) <= 1e-8
+
+
+def test_getmodes_fields2_overload(pkg, pod):
+    """getModes(snapshots, modes, fields2, ...) (ITHACAPOD.C:1940-2086): eigenvectors of the vector fields' correlation matrix
+    applied to a second list of another field type (flux-like: its own length, no volumes), boundary rows included."""
+    Nc, m, r = 3001, 40, 9
+    S2 = synth.snapshots(Nc, 3, m, 2 * r, 51)            # fields2: volVectorField snapshots
+    V = synth.volumes(Nc, 51)
+    rng = np.random.default_rng(6)
+    nF = 8123                                            # snapshots: e.g. surfaceScalarField (internal faces), another size
+    S = np.asfortranarray(rng.standard_normal((nF, m)))
+    Sbc = np.asfortranarray(rng.standard_normal((77, m)))
+    for solver in ("spectra", "eigen"):
+        out = pkg.getModesFields2(pod, S, S2, V, 3, r, solver, Sbc)
+        ref = po.getmodes_fields2(S, S2, V, 3, r, solver, Sbc)
+        assert rel_max(out["G"], ref["G"]) <= 1e-13
+        assert len(out["evals_norm"]) == r
+        assert np.all(np.abs(out["evals_norm"] - ref["evals_norm"]) <= 1e-10 * ref["evals_norm"])
+        assert modes_rel(out["modes"], ref["modes"]) <= 1e-8
+        s = np.sign(np.einsum("ij,ij->j", out["modes"], ref["modes"]))
+        assert rel_max(out["modes_bc"] * s, ref["modes_bc"]) <= 1e-8
+    assert pod.L.ithaca_b200_pod_gram(pod.h, None) == 1   # the resident matrix is the second list now: no Gram of it
+    with pytest.raises(pkg.IthacaB200Error):
+        pod.upload_second(np.asfortranarray(S[:, :m - 1]))   # another number of snapshots

@@ -364,3 +364,39 @@ def test_linear_upwind_needs_centres(pkg, pod):
     with pytest.raises(pkg.IthacaB200Error, match="needs mesh.C"):
         pr.set_convection("linearUpwind")
     pr.set_convection("upwind")
+
+
+@pytest.mark.parametrize("name,scheme", [("tutorial04", "linear"), ("cyl", "linear"), ("box", "upwind")])
+def test_consistent_flux_method_uses_the_uploaded_fluxes(pkg, pod, name, scheme):
+    """fluxMethod == "consistent" (steadyNS.C:1010-1015): C(i,j,k) = int U_i . div(L_PHImodes[j], U_k) with caller-supplied flux
+    fields (there was no ABI entry). Fused and materialised forms against the reference's loop nest over the
+    oracle's div(phi, U); G, the divergence term (which must keep the interpolated flux) and the reset are checked too."""
+    mesh = meshes()[name]()
+    N, Np = 5, 3
+    U, Ub, P, Pb = fvc.synthetic_basis(mesh, N, Np, seed=17)
+    orc = fvc.Oracle(mesh, corrected=True, convection=scheme)
+    rng = np.random.default_rng(8)
+    nF = mesh.nInt + mesh.nBnd
+    mask = np.concatenate([np.ones(mesh.nInt), np.asarray(mesh.bmask, dtype=np.float64)])
+    # "POD modes of phi": the interpolated fluxes perturbed face by face (sign changes included), 0 on `empty` faces
+    Phi = [mask * (orc.flux(U[j], Ub[j]) * (1.0 + 0.3 * rng.standard_normal(nF)) + 1e-3 * rng.standard_normal(nF)) for j in range(N)]
+    pr = pkg.Projector(pod)
+    pr.set_mesh(mesh, corrected=True)
+    pr.set_convection(scheme)
+    pr.set_basis("U", U, Ub)
+    pr.set_basis("P", P, Pb)
+    C_interp = pr.project("C")
+    P_interp = pr.project("P")
+    pr.set_flux(Phi)
+    Cr = orc.convective_term_tens_consistent(U, Ub, Phi)
+    assert rel(pr.project("C"), Cr) <= TOL
+    assert rel(pr.project("Cmat"), Cr) <= TOL
+    assert rel(pr.fvc("div_phi", 1, 3), orc.div_phi(Phi[1], U[3], Ub[3])) <= 1e-12
+    assert rel(pr.fvc("flux", 2), orc.flux(U[2], Ub[2])) <= 1e-13          # fvc_eval(FLUX) stays the interpolated flux
+    assert np.array_equal(pr.project("P"), P_interp)                       # fvc::div(U_j) does not take L_PHImodes
+    assert rel(C_interp, Cr) > 1e-3                                        # the uploaded fluxes really differ
+    pr.set_flux(None)
+    assert np.array_equal(pr.project("C"), C_interp)
+    with pytest.raises(pkg.IthacaB200Error):
+        pr.set_flux(Phi[:-1])
+    pr.set_convection("linear")
