@@ -67,5 +67,47 @@ def full(src, dst):
     print(open(dst).read())
 
 
+def full_many(dst, traffic_json, *srcs):
+    """Several per-kernel reports -> one markdown; traffic_json gets {kernel: dram bytes (read + write) per launch}."""
+    import json
+    import re
+    traffic = {}
+    with open(dst, "w") as f:
+        f.write("# ncu --set full summaries (one capture per kernel, --clock-control none, per launch)\n")
+        for src in srcs:
+            raw = subprocess.run(["ncu", "-i", src, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+            rows = list(csv.reader(raw.splitlines()))
+            if len(rows) < 3:
+                f.write("\n(no launches captured in `%s`)\n" % src)
+                continue
+            hdr, units = rows[0], rows[1]
+            for r in rows[2:]:
+                name = r[hdr.index("Kernel Name")]
+                f.write("\n## `%s`  (%s)\n\n| metric | value | unit |\n|---|---|---|\n" % (name[:100], src.split("/")[-1]))
+                vals = {}
+                for k in KEYS:
+                    if k in hdr:
+                        i = hdr.index(k)
+                        f.write("| %s | %s | %s |\n" % (k, r[i], units[i]))
+                        vals[k] = (r[i], units[i])
+
+                def nbytes(k):
+                    if k not in vals:
+                        return 0.0
+                    v, u = vals[k]
+                    v = float(v.replace(",", ""))
+                    return v * {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}.get(u, 1.0)
+
+                short = re.sub(r"<.*", "", name.split("(")[0]).split("::")[-1]
+                t = nbytes("dram__bytes_read.sum") + nbytes("dram__bytes_write.sum")
+                traffic.setdefault(short, []).append(t)
+    if traffic_json != "-":
+        json.dump({k: {"dram_bytes_per_launch": v, "source": dst} for k, v in traffic.items()}, open(traffic_json, "w"), indent=1)
+    print(open(dst).read())
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2], sys.argv[3])
+    if sys.argv[1] == "full_many":
+        full_many(sys.argv[2], sys.argv[3], *sys.argv[4:])
+    else:
+        {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2], sys.argv[3])

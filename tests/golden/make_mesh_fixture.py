@@ -1,6 +1,7 @@
-"""Generates tests/golden/mesh_04unsteadyNS.npz from the reference's own ASCII polyMesh
-(/root/reference/tutorials/CFD/04unsteadyNS/constant/polyMesh: 11 644 cells, unstructured snappyHexMesh with a
-cylinder and two `empty` patches). Run in the build container only (the reference tree does not travel)."""
+"""Generates tests/golden/mesh_<tutorial>.npz from the reference's own ASCII polyMeshes
+(/root/reference/tutorials/CFD/<tutorial>/constant/polyMesh): 04unsteadyNS (11 644 cells, unstructured, a cylinder and two
+`empty` patches), 01POD (10 000 hex cells, the lid-driven cavity block) and 03steadyNS (9 000 cells, backward-facing step).
+Run in the build container only (the reference tree does not travel)."""
 import os
 import sys
 
@@ -8,6 +9,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspa
 from oracle import polymesh as pm  # noqa: E402
 
 if __name__ == "__main__":
-    out = os.path.join(os.path.dirname(os.path.abspath(__file__)), "mesh_04unsteadyNS.npz")
-    pm.save_compact(out, "/root/reference/tutorials/CFD/04unsteadyNS")
-    print(out, os.path.getsize(out))
+    for tut in ("04unsteadyNS", "01POD", "03steadyNS"):
+        out = os.path.join(os.path.dirname(os.path.abspath(__file__)), "mesh_%s.npz" % tut)
+        pm.save_compact(out, "/root/reference/tutorials/CFD/" + tut)
+        print(out, os.path.getsize(out))

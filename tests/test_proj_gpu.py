@@ -19,12 +19,14 @@ def rel(A, B):
 def meshes():
     return {
         "tutorial04": lambda: pm.load_compact(os.path.join(GOLD, "mesh_04unsteadyNS.npz")),
+        "tutorial01": lambda: pm.load_compact(os.path.join(GOLD, "mesh_01POD.npz")),        # 10 000 hex cells, lid-driven cavity
+        "tutorial03": lambda: pm.load_compact(os.path.join(GOLD, "mesh_03steadyNS.npz")),   # 9 000 cells, backward-facing step
         "box": lambda: pm.synthetic_hex(9, 7, 5, kind="box", seed=3, perturb=0.15),
         "cyl": lambda: pm.synthetic_hex(12, 40, 6, kind="cylinder", seed=4, perturb=0.2),
     }
 
 
-@pytest.fixture(scope="module", params=["tutorial04", "box", "cyl"])
+@pytest.fixture(scope="module", params=["tutorial04", "tutorial01", "tutorial03", "box", "cyl"])
 def case(request, pkg, pod):
     mesh = meshes()[request.param]()
     N, Np = (7, 3) if request.param != "cyl" else (11, 4)
