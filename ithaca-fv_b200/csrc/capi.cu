@@ -343,6 +343,7 @@ int ithaca_b200_pod_upload(ithaca_b200_t* h, const double* const* snap_ptrs, int
     h->m = m; h->dim = dim; h->Nd = Nd; h->ld = ld;
     h->block_mode = false;
     h->stream_mode = false;
+    h->second_list = false;
     h->slot[0].ncells = h->slot[1].ncells = 0;
     h->have_gram = h->have_eig = h->have_lift = h->have_modes = false;
     return IB200_OK;
@@ -370,6 +371,7 @@ int ithaca_b200_pod_upload_second(ithaca_b200_t* h, const double* const* snap_pt
     tstop(h, T_UPLOAD);
     IB_CUDA(h, cudaStreamSynchronize(h->stream));
     h->dim = 1; h->Nd = nValues; h->ld = ld;
+    h->second_list = true;         // pod_gram is refused until the next pod_upload: the volumes belong to the first list
     h->have_gram = false;          // the resident matrix no longer belongs to the Gram; the eigenvectors stay
     h->have_lift = h->have_modes = false;
     return IB200_OK;
@@ -378,7 +380,7 @@ int ithaca_b200_pod_upload_second(ithaca_b200_t* h, const double* const* snap_pt
 int ithaca_b200_pod_gram(ithaca_b200_t* h, double* G_out)
 {
     if (!h) return IB200_ERR_ARG;
-    if (!h->dS || h->m <= 0 || !h->dV || h->stream_mode) { set_error(h, "pod_gram: upload snapshots and volumes first"); return IB200_ERR_ARG; }
+    if (!h->dS || h->m <= 0 || !h->dV || h->stream_mode || h->second_list) { set_error(h, "pod_gram: upload snapshots and volumes first"); return IB200_ERR_ARG; }
     cudaSetDevice(h->device);
     int rc = ensure_mats(h, h->m);
     if (rc) return rc;
@@ -412,7 +414,7 @@ scale_by_sqrt_abs_kernel(const double* __restrict__ S, double* __restrict__ T, l
 int ithaca_b200_pod_gram_volumes(ithaca_b200_t* h, const double* const* vol_ptrs, double* G_out)
 {
     if (!h) return IB200_ERR_ARG;
-    if (!h->dS || h->m <= 0 || h->block_mode || h->stream_mode) { set_error(h, "pod_gram_volumes: upload snapshots first"); return IB200_ERR_ARG; }
+    if (!h->dS || h->m <= 0 || h->block_mode || h->stream_mode || h->second_list) { set_error(h, "pod_gram_volumes: upload snapshots first"); return IB200_ERR_ARG; }
     if (!vol_ptrs) { set_error(h, "pod_gram_volumes: null volume list"); return IB200_ERR_ARG; }
     cudaSetDevice(h->device);
     int rc = ensure_mats(h, h->m);
@@ -618,6 +620,7 @@ static int modes_contract(ithaca_b200* h, int n, bool weighted, bool with_modes,
 static int modes_args(ithaca_b200* h, const char* who, int& nmodes, const void* out)
 {
     if (!h->have_modes || h->Nd <= 0) { set_error(h, std::string(who) + ": no resident modes (call pod_lift or pod_set_modes)"); return IB200_ERR_ARG; }
+    if (h->second_list) { set_error(h, std::string(who) + ": the resident fields are the second list of pod_upload_second (no volumes of their own)"); return IB200_ERR_ARG; }
     if (!out) { set_error(h, std::string(who) + ": null output"); return IB200_ERR_ARG; }
     if (nmodes == 0) nmodes = h->r;
     if (nmodes < 0 || nmodes > h->r) {
@@ -764,6 +767,7 @@ int ithaca_b200_pod_block_begin(ithaca_b200_t* h, int m_total, int dim, int64_t 
     if (rc) return rc;
     h->m = m_total; h->dim = dim; h->Nd = nCells * dim; h->ld = (h->Nd + 15) / 16 * 16;
     h->stream_mode = false;
+    h->second_list = false;
     h->slot[0].ncells = h->slot[1].ncells = 0;
     IB_CUDA(h, cudaMemsetAsync(h->dG, 0, (size_t)m_total * m_total * sizeof(double), h->stream));
     h->blk_n[0] = h->blk_n[1] = 0;
@@ -993,7 +997,7 @@ int ithaca_b200_pod_stream_begin(ithaca_b200_t* h, int m, int dim, int64_t nCell
     h->strm_cells = nCellsTotal; h->strm_Nd = nCellsTotal * dim; h->strm_ld = (h->strm_Nd + 15) / 16 * 16;
     h->Nd = 0; h->ld = 0; h->nCells = 0;          // no resident snapshot matrix in this mode
     h->strm_gram_chunks = h->strm_lift_chunks = 0;
-    h->stream_mode = true; h->block_mode = false;
+    h->stream_mode = true; h->block_mode = false; h->second_list = false;
     h->have_gram = h->have_eig = h->have_lift = h->have_modes = false;
     return IB200_OK;
 }

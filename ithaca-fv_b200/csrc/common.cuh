@@ -206,6 +206,7 @@ struct ithaca_b200 {
     double* dEvals = nullptr;  // m
     int mat_cap = 0;           // capacity (m) of dG/dQ/dW/dEvals
     bool have_gram = false, have_eig = false;
+    bool second_list = false;   // dS holds the second field list of pod_upload_second (liftable, but not the Gram's matrix)
     // lift state
     int r = 0;
     double* dQr = nullptr;  // [m][8 NB + 2] k-major copy of one column chunk of Q_r for the lift kernel

@@ -75,8 +75,8 @@ def full_many(dst, traffic_json, *srcs):
     with open(dst, "w") as f:
         f.write("# ncu --set full summaries (one capture per kernel, --clock-control none, per launch)\n")
         for src in srcs:
-            raw = subprocess.run(["ncu", "-i", src, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-            rows = list(csv.reader(raw.splitlines()))
+            raw = open(src).read() if src.endswith(".csv") else subprocess.run(["ncu", "-i", src, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+            rows = list(csv.reader([l for l in raw.splitlines() if not l.startswith("==")]))
             if len(rows) < 3:
                 f.write("\n(no launches captured in `%s`)\n" % src)
                 continue
