@@ -435,6 +435,25 @@ int ithaca_b200_export_matrix(const char* folder, const char* name, int type, co
 int ithaca_b200_export_tensor(const char* folder, const char* name, int type, const double* T, int64_t d0, int64_t d1,
                               int64_t d2);
 
+/* ---- allocation-free entry point ------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid allocation). It is a variant of the norm-factor
+ * computation of pod_lift / pod_block_lift_finish (n_c = sqrt(sum_k w_k Phi(k,c)^2), w_k = V[k / dim] for norm_kind 0 "L2",
+ * 1 for norm_kind 1 "Frobenius") whose per-block partial sums live in a file-scope static __device__ array instead of a
+ * cudaMalloc'ed buffer. The call performs NO cudaMalloc, cudaFree or allocating library routine.
+ *   Phi        DEVICE pointer: nCols columns of ld doubles, nRows valid rows each (ld >= nRows)
+ *   V          DEVICE pointer: nRows / dim cell volumes (may be NULL for norm_kind 1)
+ *   norms_out  DEVICE pointer: nCols doubles
+ *   stream     NULL: the handle's stream, and the call blocks until the result is there (like every other entry point);
+ *              otherwise a cudaStream_t of the caller's on which the two kernels are only enqueued.
+ * Limit: nCols <= IB200_NOALLOC_MAX_COLS (256); more columns are refused with IB200_ERR_ARG and a message. The scratch array
+ * (592 x 256 doubles = 1.2 MB) is held by every GPU that loads the library until the process exits; all calls on a device share
+ * it and it keeps the last call's contents (every slot read by a call is first written by that call, nothing needs clearing).
+ * Calls that overlap on the GPU -- two streams, two host threads -- RACE on it: serialise them. */
+#define IB200_NOALLOC_MAX_COLS 256
+int ithaca_b200_col_norms_noalloc(ithaca_b200_t* h, const double* Phi, int64_t nRows, int64_t ld, int nCols, const double* V,
+                                  int dim, int norm_kind, double* norms_out, void* stream);
+
 /* ---- measurement helpers -------------------------------------------------------------------- */
 /* Register-resident DMMA.8x8x4 (mma.sync.m8n8k4.f64) issue-rate microbenchmark on `device`:
  * the measured FP64 tensor peak used as the Gram kernel's roofline denominator. */

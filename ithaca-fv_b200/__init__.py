@@ -29,7 +29,7 @@ SYMBOLS = [
     "ithaca_b200_pod_block_gram_finish", "ithaca_b200_pod_block_gram_get", "ithaca_b200_pod_block_gram_set", "ithaca_b200_pod_block_lift", "ithaca_b200_pod_block_lift_finish",
     "ithaca_b200_pod_stream_begin", "ithaca_b200_pod_stream_upload", "ithaca_b200_pod_stream_slot", "ithaca_b200_pod_stream_gram_add",
     "ithaca_b200_pod_stream_gram_finish", "ithaca_b200_pod_stream_lift_add", "ithaca_b200_pod_stream_lift_finish",
-    "ithaca_b200_synth_snapshots", "ithaca_b200_synth_volumes",
+    "ithaca_b200_synth_snapshots", "ithaca_b200_synth_volumes", "ithaca_b200_col_norms_noalloc",
     "ithaca_b200_mesh_upload", "ithaca_b200_mesh_addressing", "ithaca_b200_basis_upload", "ithaca_b200_flux_upload", "ithaca_b200_project",
     "ithaca_b200_fvc_eval", "ithaca_b200_proj_timings", "ithaca_b200_project_background", "ithaca_b200_project_bc_velocity",
     "ithaca_b200_partition_create", "ithaca_b200_partition_destroy", "ithaca_b200_partition_sizes",
@@ -99,6 +99,7 @@ def lib():
         L.ithaca_b200_pod_stream_lift_finish.argtypes = [P, I, P, P]
         L.ithaca_b200_synth_snapshots.argtypes = [P, P, L64, L64, L64, L64, I, P, I, D, ctypes.c_uint64]
         L.ithaca_b200_synth_volumes.argtypes = [P, P, L64, L64, L64, ctypes.c_uint64]
+        L.ithaca_b200_col_norms_noalloc.argtypes = [P, P, L64, L64, I, P, I, I, P, P]
         L.ithaca_b200_pod_project.argtypes = [P, I, I, P]
         L.ithaca_b200_pod_modes_mass.argtypes = [P, I, P]
         L.ithaca_b200_pod_get_coeffs.argtypes = [P, I, P]
@@ -483,6 +484,11 @@ class Pod:
 
     def synth_volumes(self, V_ptr, cell0, ncells, ncells_global, seed):
         self._chk(self.L.ithaca_b200_synth_volumes(self.h, V_ptr, cell0, ncells, ncells_global, seed))
+
+    def col_norms_noalloc(self, Phi_ptr, nrows, ld, ncols, V_ptr, dim, norm="L2", out_ptr=None, stream=None):
+        """Norm factors of caller-held DEVICE columns through the allocation-free entry point (all pointers are device addresses)."""
+        self._chk(self.L.ithaca_b200_col_norms_noalloc(self.h, Phi_ptr, nrows, ld, ncols, V_ptr, dim, 0 if norm == "L2" else 1,
+                                                       out_ptr, stream))
 
     def lift_patch(self, Sbc, r):
         Sbc = np.asfortranarray(Sbc, dtype=np.float64)
