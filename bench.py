@@ -47,6 +47,7 @@ METRIC = "pod_time_to_modes"
 UNIT = "s"
 RESIDENT_MAX_BYTES = 125e9     # a shard up to this size stays in HBM as one chunk
 CHUNK_BYTES = 60e9             # chunk size of the row-streamed path (two slots + the resident modes must fit 180 GB)
+E2E_CHUNK_BYTES = 30e9         # chunk size of the end-to-end leg (host pool, upload / compute overlap)
 SYNTH_R, SYNTH_EPS = 64, 1e-6  # rank of the smooth part and noise level of the synthetic snapshots
 SEED = 20251104
 
@@ -478,27 +479,35 @@ class ShardedPod:
     # ---- end to end: host buffers in, host buffers out ----
     def host_setup(self):
         """Pinned host copies of the shard (or, when host RAM is smaller than the shard, of its first chunks: the pool is then
-        read periodically) and of the modes. Filled from the device generator, outside the timed region."""
+        read periodically) and of the modes. Filled from the device generator, outside the timed region.
+        The end-to-end leg has its own chunking (<= E2E_CHUNK_BYTES per chunk, also when the device-resident leg holds the shard
+        as ONE chunk): the upload of chunk k+1 then overlaps the contraction of chunk k, and the host pool stays small."""
         torch, env = self.env.torch, self.env
         local_world = int(os.environ.get("LOCAL_WORLD_SIZE", env.world))
         modes_bytes = self.r * self.Nd * 8
+        n = max(len(self.chunks), int(-(-self.shard_bytes // E2E_CHUNK_BYTES)))
+        cc = -(-self.cells // n)
+        self.e2e_chunks = [(c0, min(cc, self.cells - c0)) for c0 in range(0, self.cells, cc)]
         budget = mem_available_bytes() * 0.55 / local_world - modes_bytes
-        chunk_bytes = self.chunks[0][1] * self.dim * self.m * 8
+        chunk_bytes = self.e2e_chunks[0][1] * self.dim * self.m * 8
         if budget < chunk_bytes:
             raise RuntimeError("host RAM: %.0f GB available per rank, one chunk needs %.0f GB" % (budget / 1e9, chunk_bytes / 1e9))
-        npool = int(min(len(self.chunks), budget // chunk_bytes))
+        npool = int(min(len(self.e2e_chunks), budget // chunk_bytes))
         self.pool_chunks = npool
-        pool_cells = sum(nc for _, nc in self.chunks[:npool])
+        pool_cells = sum(nc for _, nc in self.e2e_chunks[:npool])
         self.S_host = torch.empty((self.m, pool_cells * self.dim), dtype=torch.float64, pin_memory=True)
         self.V_host = torch.empty(pool_cells, dtype=torch.float64, pin_memory=True)
         self.modes_host = torch.empty((self.r, self.Nd), dtype=torch.float64, pin_memory=True)
         self.pool_off = []
         off = 0
+        self.in_slot = {}                                # slot 0 is reused as the generator's target
         for k in range(npool):
-            c0, nc = self.chunks[k]
-            slot = self.ensure(k)
+            c0, nc = self.e2e_chunks[k]
+            Sp, ld, Vp = self.pod.stream_slot(0, c0, nc)
+            self.pod.synth_snapshots(Sp, ld, (self.cell0 + c0) * self.dim, nc * self.dim, self.Nd_global, self.m,
+                                     self.dcoef.data_ptr(), SYNTH_R, SYNTH_EPS, SEED)
+            self.pod.synth_volumes(Vp, self.cell0 + c0, nc, self.cells_global, SEED)
             self.pod.timings()                           # the generator has finished
-            Sp, ld, Vp = self.ptrs[slot]
             St = torch.as_tensor(_RawDevice(Sp, (self.m, ld)), device=env.dev)
             Vt = torch.as_tensor(_RawDevice(Vp, (nc,)), device=env.dev)
             self.S_host[:, off * self.dim:(off + nc) * self.dim].copy_(St[:, :nc * self.dim])
@@ -506,8 +515,13 @@ class ShardedPod:
             torch.cuda.synchronize()
             self.pool_off.append(off)
             off += nc
-        return {"pinned_snapshot_pool_GB": self.S_host.numel() * 8 / 1e9, "pool_chunks": npool, "chunks": len(self.chunks),
-                "periodic_pool": npool < len(self.chunks), "pinned_modes_GB": modes_bytes / 1e9}
+        return {"pinned_snapshot_pool_GB": self.S_host.numel() * 8 / 1e9, "pool_chunks": npool, "chunks": len(self.e2e_chunks),
+                "chunk_GB": chunk_bytes / 1e9, "periodic_pool": npool < len(self.e2e_chunks), "pinned_modes_GB": modes_bytes / 1e9,
+                "host_mem_available_GB": mem_available_bytes() / 1e9}
+
+    def e2e_lift_order(self):
+        n = len(self.e2e_chunks)
+        return [k for k in (n - 1, n - 2) if k >= 0] + list(range(n - 3, -1, -1))
 
     def step_e2e(self):
         """Every chunk host -> device from the pinned pool (pipelined with the contraction), modes device -> host."""
@@ -515,16 +529,17 @@ class ShardedPod:
         base = [self.S_host[j].data_ptr() for j in range(self.m)]
         vbase = self.V_host.data_ptr()
         uploads = 0
+        chunks = self.e2e_chunks
 
         def up(slot, k):
             nonlocal uploads
-            c0, nc = self.chunks[k]
+            c0, nc = chunks[k]
             off = self.pool_off[k % self.pool_chunks]    # a pool smaller than the shard is read periodically (same sizes: only the
             pod.stream_upload(slot, c0, nc, vbase + 8 * off, [b + 8 * off * self.dim for b in base])   # last chunk may be shorter)
             uploads += 1
 
         self.in_slot = {}                                # the slots are overwritten with host data
-        n = len(self.chunks)
+        n = len(chunks)
         up(0, 0)
         for k in range(n):
             if k + 1 < n:
@@ -532,7 +547,7 @@ class ShardedPod:
             pod.stream_gram_add(k & 1)
         pod.stream_gram_finish(want=False)
         ev, Q = pod.eig(r)
-        order = self.lift_order()
+        order = self.e2e_lift_order()
         slot_of = {k: k & 1 for k in order[:2]}
         pending = order[len(slot_of):]
         for k in order:
@@ -595,9 +610,9 @@ def run_headline(args, env, wl):
             wall_e = (time.perf_counter() - t0) / esteps
             dev_e = e0.elapsed_time(e1) / 1e3 / esteps
             dev_e, wall_e = env.max_over_ranks([dev_e, wall_e])
-            chunk_b = [nc * dim * m * 8 + nc * 8 for _, nc in sp.chunks]
-            n = len(sp.chunks)
-            h2d = sum(chunk_b) + sum(chunk_b[k] for k in sp.lift_order()[min(2, n):])
+            chunk_b = [nc * dim * m * 8 + nc * 8 for _, nc in sp.e2e_chunks]
+            n = len(sp.e2e_chunks)
+            h2d = sum(chunk_b) + sum(chunk_b[k] for k in sp.e2e_lift_order()[min(2, n):])
             e2e = {"value": wall_e, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int((r * sp.Nd + m + m * r + r) * 8),
                    "device_s": dev_e, "steps": esteps, "chunk_uploads_per_step": uploads,
                    "h2d_GBps_per_rank": h2d / wall_e / 1e9, "host": info,
