@@ -485,10 +485,14 @@ class ShardedPod:
         torch, env = self.env.torch, self.env
         local_world = int(os.environ.get("LOCAL_WORLD_SIZE", env.world))
         modes_bytes = self.r * self.Nd * 8
-        n = max(len(self.chunks), int(-(-self.shard_bytes // E2E_CHUNK_BYTES)))
+        budget = mem_available_bytes() * 0.55 / local_world - modes_bytes
+        # streamed shards keep the device leg's chunking (the two chunks that stay resident for pass 2 are as large as possible);
+        # a resident shard is cut into <= E2E_CHUNK_BYTES pieces; either is halved until one chunk fits the host pool
+        n = len(self.chunks) if not self.resident else int(-(-self.shard_bytes // E2E_CHUNK_BYTES))
+        while self.shard_bytes / n > budget and n < 4096:
+            n *= 2
         cc = -(-self.cells // n)
         self.e2e_chunks = [(c0, min(cc, self.cells - c0)) for c0 in range(0, self.cells, cc)]
-        budget = mem_available_bytes() * 0.55 / local_world - modes_bytes
         chunk_bytes = self.e2e_chunks[0][1] * self.dim * self.m * 8
         if budget < chunk_bytes:
             raise RuntimeError("host RAM: %.0f GB available per rank, one chunk needs %.0f GB" % (budget / 1e9, chunk_bytes / 1e9))
@@ -646,7 +650,13 @@ def run_headline(args, env, wl):
                      "frac": achieved / peak_dmma, "frac_of_nominal_40": achieved / 40.0, "traffic": gram_traffic(args.workload),
                      "peak_source": "measured live: register-resident DMMA.8x8x4 microbenchmark (ithaca_b200_dmma_peak); "
                                     "MEASURED_PEAKS.json holds no FP64 figure; nominal B200 FP64 tensor = 40 TFLOP/s",
-                     "algorithmic_flops_per_step": gram_flops, "launches_per_step": len(sp.chunks), "kernel_ms": gram_kernel_ms},
+                     "algorithmic_flops_per_step": gram_flops, "launches_per_step": len(sp.chunks), "kernel_ms": gram_kernel_ms,
+                     "algorithmic_flops_per_launch": gram_flops / len(sp.chunks), "kernel_ms_per_launch": gram_kernel_ms / len(sp.chunks),
+                     "algorithmic_bytes_per_launch": (8.0 * Nd * m + 8.0 * sp.cells) / len(sp.chunks),
+                     "traffic_note": "dram bytes (read + write) of ONE launch over a 60 GB chunk (2.5M cells x 1000 vector snapshots), ncu --set "
+                                     "full, profiles/r2f_pod_full.md: 7.5x the algorithmic bytes -- at m = 1000 the 30 jobs of the lower triangle "
+                                     "re-read their column panels and a 60 GB chunk does not fit the 126 MB L2; the kernel stays tensor-bound "
+                                     "(DRAM 22 % of peak, tensor pipe 88.9 % active)"},
         "roofline_lift": {"bound": "tensor" if m >= 1000 else "hbm", "kernel": "lift_kernel", "ms": stages.get("lift"),
                           "GBps": lift_bytes / (stages["lift"] * 1e-3) / 1e9, "frac_hbm": lift_bytes / (stages["lift"] * 1e-3) / 1e9 / hbm_peak,
                           "tflops": lift_flops / (stages["lift"] * 1e-3) / 1e12,
