@@ -245,6 +245,9 @@ def mem_available_bytes():
     return 64 << 30
 
 
+HOST_MEM_AT_START = mem_available_bytes()   # before any rank pins memory: the same figure on every rank of the box
+
+
 class Env:
     """One rank's plumbing: torch.distributed (NCCL) for the harness, library handles with their own communicator."""
 
@@ -476,6 +479,29 @@ class ShardedPod:
             st[stage] = st.get(stage, 0.0) + a.elapsed_time(b)
         return sum(st.values()), st, gk
 
+    def step_checked(self):
+        """One UNTIMED step that brings the small results back: G (m x m), all eigenvalues, the r norm factors. Size-independent
+        identities at the workload's full size: sum(lambda) = trace(G) (eigensolve), normfact_i^2 = lambda_i (because
+        |S q_i|_V^2 = q_i^T G q_i: ties the Gram, its all-reduce, the eigensolve, the lift and the norm all-reduce together),
+        G symmetric."""
+        pod, r = self.pod, self.r
+        for k in range(len(self.chunks)):
+            pod.stream_gram_add(self.ensure(k))
+        G = pod.stream_gram_finish(want=True)
+        ev, _ = pod.eig(r)
+        for k in self.lift_order():
+            pod.stream_lift_add(self.ensure(k), r, "L2")
+        _, nf = pod.stream_lift_finish(r, want=False)
+        tr = float(np.trace(G))
+        res = {"trace_vs_eigenvalue_sum_rel": abs(float(ev.sum()) - tr) / tr,
+               "normfact_sq_vs_eigenvalue_rel": float(np.max(np.abs(nf * nf / ev[:r] - 1.0))),
+               "gram_asymmetry_rel": float(np.abs(G - G.T).max() / np.abs(G).max()),
+               "eigenvalues_descending": bool(np.all(np.diff(ev) <= 0)),
+               "lambda_1": float(ev[0]), "lambda_r": float(ev[r - 1]), "lambda_min": float(ev[-1])}
+        res["pass"] = bool(res["trace_vs_eigenvalue_sum_rel"] <= 1e-10 and res["normfact_sq_vs_eigenvalue_rel"] <= 1e-8 and
+                           res["gram_asymmetry_rel"] <= 1e-13 and res["eigenvalues_descending"])
+        return res
+
     # ---- end to end: host buffers in, host buffers out ----
     def host_setup(self):
         """Pinned host copies of the shard (or, when host RAM is smaller than the shard, of its first chunks: the pool is then
@@ -485,7 +511,7 @@ class ShardedPod:
         torch, env = self.env.torch, self.env
         local_world = int(os.environ.get("LOCAL_WORLD_SIZE", env.world))
         modes_bytes = self.r * self.Nd * 8
-        budget = mem_available_bytes() * 0.55 / local_world - modes_bytes
+        budget = HOST_MEM_AT_START * 0.6 / local_world - modes_bytes
         # streamed shards keep the device leg's chunking (the two chunks that stay resident for pass 2 are as large as possible);
         # a resident shard is cut into <= E2E_CHUNK_BYTES pieces; either is halved until one chunk fits the host pool
         n = len(self.chunks) if not self.resident else int(-(-self.shard_bytes // E2E_CHUNK_BYTES))
@@ -521,7 +547,7 @@ class ShardedPod:
             off += nc
         return {"pinned_snapshot_pool_GB": self.S_host.numel() * 8 / 1e9, "pool_chunks": npool, "chunks": len(self.e2e_chunks),
                 "chunk_GB": chunk_bytes / 1e9, "periodic_pool": npool < len(self.e2e_chunks), "pinned_modes_GB": modes_bytes / 1e9,
-                "host_mem_available_GB": mem_available_bytes() / 1e9}
+                "host_mem_available_at_start_GB": HOST_MEM_AT_START / 1e9}
 
     def e2e_lift_order(self):
         n = len(self.e2e_chunks)
@@ -596,6 +622,7 @@ def run_headline(args, env, wl):
     launches = pod.launch_count()
     ms_step, gram_kernel_ms, wall = env.max_over_ranks([tot / args.steps, gk / args.steps, wall])
     stages = {k: v / args.steps for k, v in stages.items()}
+    full_size = None if args.no_checks else sp.step_checked()       # untimed; every rank takes part in the all-reduces
 
     e2e = None
     if not args.no_e2e:
@@ -666,7 +693,7 @@ def run_headline(args, env, wl):
         "stages_ms": stages, "gpu_launches": int(launches), "clocks": clk, "e2e": e2e,
     }
     if not args.no_checks:
-        line["checks"] = {"multi_gpu_parity" if env.multi else "parity_small": checks}
+        line["checks"] = {"multi_gpu_parity" if env.multi else "parity_small": checks, "full_size_identities": full_size}
     pod.close()
     return line, peak_dmma, hbm_peak
 
@@ -818,7 +845,7 @@ def run_b200(args, wl, rank, local_rank, world):
         print(json.dumps(line), flush=True)
         chk = (line.get("checks") or {})
         res = chk.get("multi_gpu_parity") or chk.get("parity_small")
-        ok = (res is None) or bool(res.get("pass"))
+        ok = ((res is None) or bool(res.get("pass"))) and bool((chk.get("full_size_identities") or {"pass": True}).get("pass"))
     flag = env.max_over_ranks([0.0 if ok else 1.0])[0]
     env.close()
     if flag > 0:

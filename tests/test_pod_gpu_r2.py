@@ -274,3 +274,48 @@ def test_getmodes_fields2_overload(pkg, pod):
     assert pod.L.ithaca_b200_pod_gram(pod.h, None) == 1   # the resident matrix is the second list now: no Gram of it
     with pytest.raises(pkg.IthacaB200Error):
         pod.upload_second(np.asfortranarray(S[:, :m - 1]))   # another number of snapshots
+
+
+def test_row_streamed_identities_at_scale(pkg, pod):
+    """Size-independent properties of the row-streamed path at a size no oracle run covers (2.4 GB: 400k cells x 256 vector
+    snapshots, five ragged chunks produced in place): sum(lambda) = trace(G), normfact_i^2 = lambda_i (|S q_i|_V^2 = q_i^T G q_i),
+    V-orthonormal modes, and the same eigenvalues whatever the chunking (chunk sums differ only in the summation order)."""
+    torch = pytest.importorskip("torch")
+    dev = torch.device("cuda", 0)
+    Nc, dim, m, r, R, seed = 400_003, 3, 256, 24, 48, 7
+    Nd = Nc * dim
+    rng = np.random.default_rng(12)
+    coef, _ = np.linalg.qr(rng.standard_normal((m, R)))
+    dcoef = torch.tensor(np.asfortranarray(coef).T.copy(), device=dev)
+
+    def run(chunk):
+        chunks = [(c0, min(chunk, Nc - c0)) for c0 in range(0, Nc, chunk)]
+        pod.stream_begin(m, dim, Nc)
+
+        def fill(slot, c0, nc):
+            Sp, ld, Vp = pod.stream_slot(slot, c0, nc)
+            pod.synth_snapshots(Sp, ld, c0 * dim, nc * dim, Nd, m, dcoef.data_ptr(), R, 1e-6, seed)
+            pod.synth_volumes(Vp, c0, nc, Nc, seed)
+
+        for k, (c0, nc) in enumerate(chunks):
+            fill(k & 1, c0, nc)
+            pod.stream_gram_add(k & 1)
+        G = pod.stream_gram_finish()
+        ev, Q = pod.eig(r)
+        for k, (c0, nc) in enumerate(chunks):
+            fill(k & 1, c0, nc)
+            pod.stream_lift_add(k & 1, r, "L2")
+        Phi, nf = pod.stream_lift_finish(r)
+        return G, ev, nf, Phi
+
+    G, ev, nf, Phi = run(90_001)
+    assert abs(ev.sum() - np.trace(G)) <= 1e-12 * np.trace(G)
+    assert np.all(np.abs(nf * nf / ev[:r] - 1.0) <= 1e-9)
+    Vd = torch.zeros(Nc, device=dev, dtype=torch.float64)
+    pod.synth_volumes(Vd.data_ptr(), 0, Nc, Nc, seed)
+    pod.timings()
+    W = np.repeat(Vd.cpu().numpy(), dim)
+    assert np.abs(Phi.T @ (W[:, None] * Phi) - np.eye(r)).max() <= 1e-9
+    G1, ev1, nf1, _ = run(Nc)                              # one chunk = the resident arithmetic
+    assert rel_max(G, G1) <= 1e-13
+    assert np.all(np.abs(ev[:r] - ev1[:r]) <= 1e-10 * ev1[:r])
