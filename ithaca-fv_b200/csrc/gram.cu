@@ -551,6 +551,63 @@ void gram_partition(const std::vector<double>& cost, long long ksteps, long long
     }
 }
 
+// Type-balanced static partition (round 2). The stage-time model above is off by -9 .. +7.5 % for the minority job shapes
+// (measured per segment with ITHACA_B200_GRAM_TRACE at m = 1000: CTA cycles max / mean = 1.08 under gram_partition, i.e. the
+// slowest CTA set the kernel time 8 % above the mean). Instead of trusting a model ACROSS shapes, jobs are grouped by their exact
+// composition (boxes + fragments per warp: jobs of one type cost the same per stage whatever that cost is), the concatenated
+// stage range of every type is cut into equal slices, and CTA c gets slice c of EVERY type: all CTAs run the same mix, so the
+// balance no longer depends on the model. Still static (fixed slab order in the reduction: bit-reproducible run to run).
+// A type too small for nctas slices of minlen stages gets fewer slices, spread over the CTAs.
+void gram_partition_typed(const std::vector<int>& type, int ntypes, long long ksteps, long long K, long long nctas, long long minlen,
+                          std::vector<GramSeg>& segs, std::vector<int>& seg_off, std::vector<int>& nsplit)
+{
+    const int njobs = (int)type.size();
+    std::vector<std::vector<GramSeg>> per(nctas);
+    for (int t = 0; t < ntypes; t++) {
+        std::vector<int> js;
+        for (int j = 0; j < njobs; j++) if (type[j] == t) js.push_back(j);
+        if (js.empty()) continue;
+        const long long L = (long long)js.size() * ksteps;
+        const long long nt = std::max<long long>(1, std::min<long long>(nctas, L / std::max<long long>(minlen, 1)));
+        std::vector<long long> b(nt + 1, 0);
+        b[nt] = L;
+        for (long long i = 1; i < nt; i++) {
+            long long pos = (long long)std::llround((double)L * (double)i / (double)nt);
+            const long long jj = std::min<long long>(pos / ksteps, (long long)js.size() - 1);
+            long long x = pos - jj * ksteps;
+            if (x < minlen) x = 0;
+            else if (ksteps - x < minlen) x = ksteps;
+            b[i] = std::max(b[i - 1], jj * ksteps + x);
+        }
+        for (long long i = 0; i < nt; i++) {
+            const long long cta = ((i * nctas) / nt + 37LL * t) % nctas;   // small types do not all land on the same CTAs
+            long long pos = b[i];
+            while (pos < b[i + 1]) {
+                const long long jj = pos / ksteps;
+                const long long x0 = pos - jj * ksteps;
+                const long long x1 = std::min(ksteps, x0 + (b[i + 1] - pos));
+                GramSeg sg;
+                sg.job = js[(size_t)jj];
+                sg.slot = 0;
+                sg.k_begin = x0 * GRAM_KT;
+                sg.k_end = std::min<long long>(K, x1 * GRAM_KT);
+                per[(size_t)cta].push_back(sg);
+                pos += x1 - x0;
+            }
+        }
+    }
+    segs.clear();
+    seg_off.assign(1, 0);
+    nsplit.assign(njobs, 0);
+    for (long long c = 0; c < nctas; c++) {
+        for (GramSeg sg : per[(size_t)c]) {
+            sg.slot = nsplit[sg.job]++;
+            segs.push_back(sg);
+        }
+        seg_off.push_back((int)segs.size());
+    }
+}
+
 }  // namespace
 
 // cached dim-times repeated weights (two slots: the projection uses V with dim 3 and dim 1 alternately)
@@ -596,7 +653,24 @@ int atvb_launch(ithaca_b200* h, const double* A, long long lda, int Ma, const do
     if (const char* e = env_knob("ITHACA_B200_GRAM_CTAS")) nctas = std::max(1, atoi(e));
     std::vector<GramSeg> segs;
     std::vector<int> seg_off, nsplit;
-    gram_partition(cost, ksteps, K, nctas, minlen, segs, seg_off, nsplit);
+    // job types = exact compositions (boxes, per-warp pattern / fragment count): see gram_partition_typed
+    std::vector<int> type(njobs, 0);
+    int ntypes = 0;
+    {
+        std::vector<std::vector<int>> keys;
+        for (int j = 0; j < njobs; j++) {
+            std::vector<int> key(1, jobs[j].nbox);
+            for (int w = 0; w < GRAM_WARPS; w++) { key.push_back(jobs[j].pat[w]); key.push_back(__builtin_popcount(jobs[j].mask[w])); }
+            size_t t = 0;
+            while (t < keys.size() && keys[t] != key) t++;
+            if (t == keys.size()) keys.push_back(key);
+            type[j] = (int)t;
+        }
+        ntypes = (int)keys.size();
+    }
+    const char* part = env_knob("ITHACA_B200_GRAM_PART");   // "model": the cost-model stream-K of round 1 (A/B measurements)
+    if (part && strcmp(part, "model") == 0) gram_partition(cost, ksteps, K, nctas, minlen, segs, seg_off, nsplit);
+    else gram_partition_typed(type, ntypes, ksteps, K, nctas, minlen, segs, seg_off, nsplit);
     int maxseg = 1;
     for (size_t c = 0; c + 1 < seg_off.size(); c++) maxseg = std::max(maxseg, seg_off[c + 1] - seg_off[c]);
     long long ws_doubles = 0;
