@@ -17,6 +17,7 @@
 #include "common.cuh"
 #include <algorithm>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 namespace ib200 {
@@ -140,8 +141,11 @@ conv_face_prep_kernel(ConvMesh m, const double* __restrict__ Ucm, const double* 
 
 // ---- contraction over faces -------------------------------------------------------------------------------------
 struct ConvChunk { int r_lo, r_hi, k_lo, pad; };  // output rows [r_lo, r_hi) of the flattened (k,i) index, first k
+// one CTA = (row chunk, column block, K slab [t_begin, t_end) in stages of KT faces). Chunks with fewer rows get fewer slabs
+// (round 2): the slab counts follow the chunks' cost so that all SMs finish together.
+struct ConvCta { int chunk, jblk, slab, pad; long long t_begin, t_end; };
 
-// grid: blockIdx.x = chunk + nchunks * (jblk + njblk * slab). Stage layout in smem: [A: KT x NP][B: KT x bp][D: KT x 3NP].
+// grid: one CTA per ConvCta descriptor. Stage layout in smem: [A: KT x NP][B: KT x bp][D: KT x 3NP].
 // DMMA without `volatile` (see gram.cu)
 __device__ __forceinline__ void conv_dmma(double& c0, double& c1, double a, double b)
 {
@@ -174,8 +178,8 @@ __device__ __forceinline__ void conv_stage(double (&acc)[2][CV_JF][2], const dou
 template <int KT>
 __global__ void __launch_bounds__(CV_THREADS, 1)
 conv_contract_kernel(const __grid_constant__ CUtensorMap tmB, const double* __restrict__ Aj, const double* __restrict__ Dd,
-                     const ConvChunk* __restrict__ chunks, int nchunks, int njblk, int N, int NI, int NP, int bp, int Jpad,
-                     long long tiles_per_slab, long long ntiles, int nstages, double* __restrict__ ws)
+                     const ConvChunk* __restrict__ chunks, const ConvCta* __restrict__ ctas, int N, int NI, int NP, int bp, int Jpad,
+                     int nstages, double* __restrict__ ws)
 {
     extern __shared__ __align__(1024) unsigned char smem[];
     const int a_bytes = KT * NP * 8, b_bytes = KT * bp * 8, d_bytes = KT * 3 * NP * 8;
@@ -184,13 +188,12 @@ conv_contract_kernel(const __grid_constant__ CUtensorMap tmB, const double* __re
     uint64_t* empty = full + nstages;
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int chunk = blockIdx.x % nchunks;
-    const int jblk = (blockIdx.x / nchunks) % njblk;
-    const long long slab = blockIdx.x / (nchunks * njblk);
-    const ConvChunk ch = chunks[chunk];
-    const long long t_begin = slab * tiles_per_slab;
-    const long long t_end = min(ntiles, t_begin + tiles_per_slab);
-    const int niter = (int)max(0LL, t_end - t_begin);
+    const ConvCta me = ctas[blockIdx.x];
+    const int jblk = me.jblk;
+    const long long slab = me.slab;
+    const ConvChunk ch = chunks[me.chunk];
+    const long long t_begin = me.t_begin;
+    const int niter = (int)max(0LL, me.t_end - t_begin);
 
     if (tid == 0) {
         for (int s = 0; s < nstages; s++) { mbar_init(&full[s], 1); mbar_init(&empty[s], CV_WARPS); }
@@ -311,12 +314,47 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
         r = r_hi;
     }
     const int nchunks = (int)chunks.size();
-    if ((rc = dev_ensure(h, cb->chunks, chunks.size() * sizeof(ConvChunk)))) return rc;
+    // K slabs per chunk: a CTA's time per stage follows the DMMAs of its busiest sub-partition (warp w runs on sub-partition w & 3,
+    // two 8-row fragments per warp) plus a fixed part (~2 fragments' worth: barrier, A / B / D loads, E generation); one slab to
+    // every chunk, then the remaining SMs one by one to the chunk with the largest cost per slab
+    std::vector<double> ccost(nchunks);
+    for (int c = 0; c < nchunks; c++) {
+        const int frags = (chunks[c].r_hi - chunks[c].r_lo + 7) / 8;
+        int per[4] = {0, 0, 0, 0};
+        for (int f = 0; f < frags; f++) per[(f / 2) & 3]++;
+        ccost[c] = 2.0 + std::max({per[0], per[1], per[2], per[3]});
+    }
+    std::vector<int> nsl(nchunks, 1);
+    const bool uniform = [] { const char* e = env_knob("ITHACA_B200_CONV_SLABS"); return e && strcmp(e, "uniform") == 0; }();
+    if (uniform) {
+        const int u = (int)std::max<long long>(1, std::min<long long>(h->num_sms / (nchunks * njblk), ntiles));
+        for (int c = 0; c < nchunks; c++) nsl[c] = u;
+    } else {
+        for (int left = h->num_sms / njblk - nchunks; left > 0; left--) {
+            int best = -1;
+            for (int c = 0; c < nchunks; c++)
+                if (nsl[c] < ntiles && (best < 0 || ccost[c] / nsl[c] > ccost[best] / nsl[best])) best = c;
+            if (best < 0) break;
+            nsl[best]++;
+        }
+    }
+    std::vector<ConvCta> ctas;
+    int nslabs = 1;
+    for (int c = 0; c < nchunks; c++) {
+        const long long tps = (ntiles + nsl[c] - 1) / nsl[c];
+        const int ns = (int)((ntiles + tps - 1) / tps);
+        nslabs = std::max(nslabs, ns);
+        for (int jb = 0; jb < njblk; jb++)
+            for (int q = 0; q < ns; q++) ctas.push_back({c, jb, q, 0, q * tps, std::min(ntiles, (q + 1) * tps)});
+    }
+    if ((rc = dev_ensure(h, cb->chunks, chunks.size() * sizeof(ConvChunk) + 256 + ctas.size() * sizeof(ConvCta)))) return rc;
+    const size_t cta_off = (chunks.size() * sizeof(ConvChunk) + 255) / 256 * 256;
     IB_CUDA(h, cudaMemcpyAsync(cb->chunks.p, chunks.data(), chunks.size() * sizeof(ConvChunk), cudaMemcpyHostToDevice, h->stream));
-    int nslabs = (int)std::max<long long>(1, std::min<long long>(h->num_sms / (nchunks * njblk), ntiles));
-    const long long tps = (ntiles + nslabs - 1) / nslabs;
-    nslabs = (int)((ntiles + tps - 1) / tps);
-    if ((rc = dev_ensure(h, cb->ws, (size_t)nslabs * N * NI * Jpad * 8))) return rc;
+    IB_CUDA(h, cudaMemcpyAsync((char*)cb->chunks.p + cta_off, ctas.data(), ctas.size() * sizeof(ConvCta), cudaMemcpyHostToDevice, h->stream));
+    const size_t ws_bytes = (size_t)nslabs * N * NI * Jpad * 8;
+    if ((rc = dev_ensure(h, cb->ws, ws_bytes))) return rc;
+    // chunks with fewer slabs leave their rows of the higher slabs untouched: the reduction sums all nslabs slabs
+    IB_CUDA(h, cudaMemsetAsync(cb->ws.p, 0, ws_bytes, h->stream));
 
     cudaEvent_t e0, e1, e2;
     cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
@@ -352,9 +390,9 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
     const size_t smem = (size_t)nstages * (stage_bytes + 16) + 64;
     auto kern = (CV_KT == 16) ? conv_contract_kernel<16> : conv_contract_kernel<32>;
     IB_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<nchunks * njblk * nslabs, CV_THREADS, smem, h->stream>>>(
-        tmB, cb->Aj.as<double>(), cb->Dd.as<double>(), cb->chunks.as<ConvChunk>(), nchunks, njblk, N, NI, NP, bp, Jpad, tps, ntiles,
-        nstages, cb->ws.as<double>());
+    kern<<<(unsigned)ctas.size(), CV_THREADS, smem, h->stream>>>(
+        tmB, cb->Aj.as<double>(), cb->Dd.as<double>(), cb->chunks.as<ConvChunk>(),
+        reinterpret_cast<const ConvCta*>((const char*)cb->chunks.p + cta_off), N, NI, NP, bp, Jpad, nstages, cb->ws.as<double>());
     IB_CUDA(h, cudaGetLastError());
     conv_reduce_kernel<<<std::min(4 * h->num_sms, (N * NI * N + 255) / 256), 256, 0, h->stream>>>(cb->ws.as<double>(), nslabs, N, NI, Jpad, dC);
     IB_CUDA(h, cudaGetLastError());
