@@ -24,7 +24,9 @@ namespace ib200 {
 
 constexpr int CV_KTMAX = 32;   // faces per pipeline stage: template parameter KT = 16 or 32 (4 / 8 DMMA k-steps)
 constexpr int CV_ROWS = 240;   // output rows (k,i) per CTA
-constexpr int CV_KC = 7;       // distinct k per CTA: the b box is 4*CV_KC doubles per face (pitch 28 = 12 mod 16)
+constexpr int CV_KC = 7;       // distinct k per CTA when the test fields are the basis (NI = N): the b box is 4*CV_KC doubles per
+                               // face (pitch 28 = 12 mod 16). With fewer test fields (G: NI = Np) a chunk takes up to CV_KCMAX k's
+constexpr int CV_KCMAX = 25;   // (odd: 4*kc = 4 or 12 mod 16 keeps the b reads of the four k-lanes on distinct banks)
 constexpr int CV_WARPS = 15;   // MMA warps, two row fragments (16 rows) each; + 1 producer warp = 512 threads
 constexpr int CV_THREADS = (CV_WARPS + 1) * 32;
 constexpr int CV_JF = 7;       // column fragments (8 j each) per CTA
@@ -178,8 +180,8 @@ __device__ __forceinline__ void conv_stage(double (&acc)[2][CV_JF][2], const dou
 template <int KT>
 __global__ void __launch_bounds__(CV_THREADS, 1)
 conv_contract_kernel(const __grid_constant__ CUtensorMap tmB, const double* __restrict__ Aj, const double* __restrict__ Dd,
-                     const ConvChunk* __restrict__ chunks, const ConvCta* __restrict__ ctas, int N, int NI, int NP, int bp, int Jpad,
-                     int nstages, double* __restrict__ ws)
+                     const ConvChunk* __restrict__ chunks, const ConvCta* __restrict__ ctas, int N, int NI, int NP, int bp, int kc,
+                     int Jpad, int nstages, double* __restrict__ ws)
 {
     extern __shared__ __align__(1024) unsigned char smem[];
     const int a_bytes = KT * NP * 8, b_bytes = KT * bp * 8, d_bytes = KT * 3 * NP * 8;
@@ -229,7 +231,7 @@ conv_contract_kernel(const __grid_constant__ CUtensorMap tmB, const double* __re
         act[r] = row0 < ch.r_hi;                       // warp-uniform
         const int row = min(row0 + g, N * NI - 1);   // rows are (k, i) pairs, i < NI test fields
         const int k = row / NI, i = row - k * NI;
-        boff[r] = 4 * min(max(k - ch.k_lo, 0), CV_KC - 1);
+        boff[r] = 4 * min(max(k - ch.k_lo, 0), kc - 1);
         doff[r] = i;
     }
     const int j0 = jblk * (8 * CV_JF);
@@ -290,12 +292,17 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
     const int NP = (N + 3) / 8 * 8 + 4;  // smallest NP >= N with NP = 4 (mod 8): conflict-free smem pitches
     const long long nFaces = m.nInt + m.nBnd;
     const long long nF = nFaces + (m.upwind ? m.nInt : 0);   // rank-one records: upwind doubles the internal faces
-    int CV_KT = 32;   // faces per stage (ITHACA_B200_CONV_KT=16 selects the shorter stage)
+    const int NI = Dfm ? Ni : N;   // test fields of the d_i records: rows of the contraction are (k, i), i < NI
+    // distinct k per row chunk: enough to fill the CTA's CV_ROWS rows (G has NI = Np = 10 test fields: 7 k's were 70 of 240 rows)
+    int kc = std::min(N, std::max(CV_KC, std::min(CV_KCMAX, (CV_ROWS + NI - 1) / NI)));
+    if (kc > CV_KC && (kc & 1) == 0) kc--;
+    const int bp = std::min(4 * kc, 4 * N);
+    int CV_KT = 32;   // faces per stage; 16 when the wider b box would leave fewer than 3 stages (or ITHACA_B200_CONV_KT=16)
+    if (((226 * 1024 - 256) / (32 * 8 * (4 * NP + bp) + 16)) < 3) CV_KT = 16;
     if (const char* e = env_knob("ITHACA_B200_CONV_KT")) CV_KT = (atoi(e) == 16) ? 16 : 32;
     const long long ntiles = (nF + CV_KT - 1) / CV_KT, nFpad = ntiles * CV_KT;
     const int Jpad = (N + 7) / 8 * 8;
     const int njblk = (Jpad + 8 * CV_JF - 1) / (8 * CV_JF);
-    const int bp = std::min(4 * CV_KC, 4 * N);
     int rc;
     if ((rc = dev_ensure(h, cb->Ucm, (size_t)nCells * 3 * NP * 8))) return rc;
     if ((rc = dev_ensure(h, cb->Ubcm, (size_t)std::max<long long>(m.nBnd, 1) * 3 * NP * 8))) return rc;
@@ -304,12 +311,11 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
     if ((rc = dev_ensure(h, cb->Bk, (size_t)nFpad * N * 32))) return rc;
     if ((rc = dev_ensure(h, cb->Dd, (size_t)nFpad * 3 * NP * 8))) return rc;
 
-    // output row chunks: <= CV_ROWS rows and <= CV_KC distinct k each
-    const int NI = Dfm ? Ni : N;   // test fields of the d_i records: rows of the contraction are (k, i), i < NI
+    // output row chunks: <= CV_ROWS rows and <= kc distinct k each
     std::vector<ConvChunk> chunks;
     for (int r = 0; r < N * NI;) {
         const int k_lo = r / NI;
-        const int r_hi = std::min({r + CV_ROWS, (k_lo + CV_KC) * NI, N * NI});
+        const int r_hi = std::min({r + CV_ROWS, (k_lo + kc) * NI, N * NI});
         chunks.push_back({r, r_hi, k_lo, 0});
         r = r_hi;
     }
@@ -392,7 +398,7 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
     IB_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     kern<<<(unsigned)ctas.size(), CV_THREADS, smem, h->stream>>>(
         tmB, cb->Aj.as<double>(), cb->Dd.as<double>(), cb->chunks.as<ConvChunk>(),
-        reinterpret_cast<const ConvCta*>((const char*)cb->chunks.p + cta_off), N, NI, NP, bp, Jpad, nstages, cb->ws.as<double>());
+        reinterpret_cast<const ConvCta*>((const char*)cb->chunks.p + cta_off), N, NI, NP, bp, kc, Jpad, nstages, cb->ws.as<double>());
     IB_CUDA(h, cudaGetLastError());
     conv_reduce_kernel<<<std::min(4 * h->num_sms, (N * NI * N + 255) / 256), 256, 0, h->stream>>>(cb->ws.as<double>(), nslabs, N, NI, Jpad, dC);
     IB_CUDA(h, cudaGetLastError());
