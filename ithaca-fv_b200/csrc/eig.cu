@@ -289,10 +289,19 @@ __global__ void eig_jacobi_block_kernel(double* X, int m, int b, int nb, double 
 // 32*NE doubles per column, so the hot loop has no bounds checks), and the squared norms travel with the columns and
 // are updated by the rotation (|x'|^2 = a - t c, |y'|^2 = b + t c; recomputed from scratch at every block-pair visit),
 // so a rotation costs ONE warp reduction (the dot product) instead of three.
-template <int NE>
+// CL = true: the whole grid is ONE thread-block cluster (<= 16 CTAs: m <= 256 with b = 8) and the barrier between block rounds is
+// the hardware cluster barrier (barrier.cluster release / acquire, ~380 cycles) instead of the cooperative grid barrier (~2 us of
+// global atomics and polling), 27 of them per sweep at m = 200.
+template <int NE, bool CL>
+__device__ __forceinline__ void eig_grid_sync()
+{
+    if constexpr (CL) cg::this_cluster().sync();
+    else cg::this_grid().sync();
+}
+
+template <int NE, bool CL = false>
 __global__ void __launch_bounds__(NE > 32 ? 256 : NE > 16 ? 320 : 512, 1) eig_jacobi_reg_kernel(double* X, int m, int b, int nb, double tol, int* flags)
 {
-    cg::grid_group grid = cg::this_grid();
     extern __shared__ double sx[];           // b columns of LDC doubles | b squared norms
     constexpr int LDC = 32 * NE;
     double* nrm = sx + (size_t)b * LDC;
@@ -350,7 +359,7 @@ __global__ void __launch_bounds__(NE > 32 ? 256 : NE > 16 ? 320 : 512, 1) eig_ja
             store_block(blk, nc);
             __syncthreads();
         }
-        grid.sync();
+        eig_grid_sync<NE, CL>();
         // ---- block tournament ----
         for (int rd = 0; rd < nbp - 1; rd++) {
             for (int p = blockIdx.x; p < npairs; p += gridDim.x) {
@@ -425,10 +434,10 @@ __global__ void __launch_bounds__(NE > 32 ? 256 : NE > 16 ? 320 : 512, 1) eig_ja
                 store_block(J, nj);
                 __syncthreads();
             }
-            grid.sync();
+            eig_grid_sync<NE, CL>();
         }
         if (lane == 0 && rot) atomicAdd(&flags[sweep], rot);
-        grid.sync();
+        eig_grid_sync<NE, CL>();
         if (*(volatile int*)&flags[sweep] == 0) { sweep++; break; }
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) flags[EIG_MAX_SWEEPS] = sweep;
@@ -616,6 +625,19 @@ int eig_launch(ithaca_b200* h, int* sweeps)
         kern = (void*)eig_jacobi_block_kernel;
     }
     const int nb = (m + b - 1) / b;
+    // one thread-block cluster when the grid has <= 16 CTAs (register kernel, NE <= 8: m <= 256)
+    bool clustered = false;
+    if (use_reg && m <= 256 && (nb + 1) / 2 <= 16) {
+        const char* es = env_knob("ITHACA_B200_EIG_SYNC");   // "grid": keep the cooperative grid barrier (A/B measurements)
+        if (!(es && strcmp(es, "grid") == 0)) {
+            clustered = true;
+            switch (m <= 64 ? 2 : m <= 128 ? 4 : 8) {
+                case 2: kern = (void*)eig_jacobi_reg_kernel<2, true>; break;
+                case 4: kern = (void*)eig_jacobi_reg_kernel<4, true>; break;
+                default: kern = (void*)eig_jacobi_reg_kernel<8, true>; break;
+            }
+        }
+    }
     if (smem > 227 * 1024) { set_error(h, "pod_eig: too many snapshots for the Jacobi block kernel"); return fail(IB200_ERR_ARG); }
     IB_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int maxb = 0;
@@ -625,7 +647,36 @@ int eig_launch(ithaca_b200* h, int* sweeps)
     const int nblocks = std::max(1, std::min(want, maxb * h->num_sms));
     int mm = m, bb = b, nbb = nb;
     void* args[] = {&X, &mm, &bb, &nbb, &tol, &flags};
-    IB_CUDA(h, cudaLaunchCooperativeKernel(kern, dim3(nblocks), dim3(threads), args, smem, h->stream));
+    bool launched = false;
+    if (clustered) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(nblocks);
+        cfg.blockDim = dim3(threads);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = h->stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = (unsigned)nblocks;
+        at[0].val.clusterDim.y = 1;
+        at[0].val.clusterDim.z = 1;
+        cfg.attrs = at;
+        cfg.numAttrs = 1;
+        int ncl = 0;
+        if ((nblocks <= 8 || cudaFuncSetAttribute(kern, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) == cudaSuccess) &&
+            cudaOccupancyMaxActiveClusters(&ncl, kern, &cfg) == cudaSuccess && ncl >= 1 &&
+            cudaLaunchKernelExC(&cfg, kern, args) == cudaSuccess)
+            launched = true;
+        else {
+            cudaGetLastError();   // the cluster does not fit this device / configuration: cooperative launch of the grid-barrier kernel
+            switch (m <= 64 ? 2 : m <= 128 ? 4 : 8) {
+                case 2: kern = (void*)eig_jacobi_reg_kernel<2>; break;
+                case 4: kern = (void*)eig_jacobi_reg_kernel<4>; break;
+                default: kern = (void*)eig_jacobi_reg_kernel<8>; break;
+            }
+            IB_CUDA(h, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        }
+    }
+    if (!launched) IB_CUDA(h, cudaLaunchCooperativeKernel(kern, dim3(nblocks), dim3(threads), args, smem, h->stream));
     eig_finalize_kernel<<<(m + 7) / 8, 256, 0, h->stream>>>(h->dW, m, sigma, 1.0 / scale, lam_tmp);
     eig_sort_permute_kernel<<<m, 128, 0, h->stream>>>(lam_tmp, h->dW, m, h->dEvals, h->dQ);
     IB_CUDA(h, cudaGetLastError());
