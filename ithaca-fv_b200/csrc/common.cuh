@@ -36,6 +36,24 @@ __device__ __forceinline__ void mbar_arrive(uint64_t* bar)
 {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
+// DELAYED RELEASE -- the rule for every consumer warp of a TMA ring that reads a stage with ordinary shared-memory loads
+// (LDS) feeding DMMAs (gram.cu, lift.cu, conv.cu): stage s is handed back to the producer only after the wait for stage
+// s + 1, never at the end of its own iteration.
+// A `__syncwarp(); if (lane == 0) mbar_arrive(&empty[s]);` at the end of the iteration is a write-after-read race: nothing
+// orders the arrive against the DMMAs, so ptxas schedules it right behind the last LDS *issue* -- ahead of the DMMAs that consume
+// the data and without a scoreboard wait -- and the arrive then overtakes loads that are still in flight: the producer's next
+// TMA box lands under them. Measured with scripts/exp/lift_stress.py (m = 256, r = 24, two CTAs per SM): one warp's A or B
+// fragment of one stage wrong in 8 of 40 passes over 1.2 M rows with the arrive at 3 LDS in flight, 0 of 300 since.
+// Behind the NEXT wait (a spin loop: no instruction is moved across it) every DMMA of the released stage has issued, and a
+// DMMA cannot issue before the LDS results it reads have returned -- whatever the instruction scheduler does inside the loop
+// body. Cost: the ring holds one stage less in flight. tests/test_sass_ring_release.py checks the order in the SASS of the build.
+__device__ __forceinline__ void mbar_release_previous(uint64_t* empty, int prev, int lane)
+{
+    if (prev >= 0) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty + prev);
+    }
+}
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
 {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)

@@ -245,13 +245,12 @@ conv_contract_kernel(const __grid_constant__ CUtensorMap tmB, const double* __re
     for (int it = 0; it < niter; it++) {
         const int s = it % nstages;
         mbar_wait(&full[s], (it / nstages) & 1);
+        mbar_release_previous(empty, it > 0 ? (it - 1) % nstages : -1, lane);   // delayed release (common.cuh)
         const double* As = reinterpret_cast<const double*>(smem + (size_t)s * stage_bytes);
         const double* Bs = As + KT * NP;
         const double* Ds = Bs + KT * bp;
         if (nact == 2) conv_stage<KT, 2>(acc, As, Bs, Ds, NP, bp, j0 + g, t, boff, doff);
         else if (nact == 1) conv_stage<KT, 1>(acc, As, Bs, Ds, NP, bp, j0 + g, t, boff, doff);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&empty[s]);
     }
 
     // ---------------- epilogue: partial rows -> workspace slab [row][Jpad] ----------------

@@ -78,6 +78,7 @@ __device__ __forceinline__ void gram_dmma(double& c0, double& c1, double a, doub
 // ring position of a consumer warp
 struct GramRing {
     int s, ph;
+    int prev;   // stage this warp still has to hand back, -1: none (delayed release, common.cuh)
 };
 
 // One (job, K slab) segment of one MMA warp: NR x NC fragments (LI0 < 0; the runtime row offset is folded into a_off)
@@ -102,9 +103,10 @@ __device__ __forceinline__ void gram_run(GramRing& r, int niter, int nstages, in
 #pragma unroll
         for (int j = 0; j < NCM; j++) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-    int s = r.s, ph = r.ph;
+    int s = r.s, ph = r.ph, prev = r.prev;
     for (int it = 0; it < niter; it++) {
         mbar_wait(full + s, (uint32_t)ph);
+        mbar_release_previous(empty, prev, lane);
         const unsigned char* st = panels + (size_t)s * stage_bytes;
         const unsigned char* pa = st + a_off;
         const unsigned char* pb = st + b_off;
@@ -124,12 +126,12 @@ __device__ __forceinline__ void gram_run(GramRing& r, int niter, int nstages, in
                     if (LI0 < 0 || j <= LI0 + i) gram_dmma(acc[i][j][0], acc[i][j][1], a, b[j]);
             }
         }
-        __syncwarp();
-        if (lane == 0) mbar_arrive(empty + s);
+        prev = s;
         if (++s == nstages) { s = 0; ph ^= 1; }
     }
     r.s = s;
     r.ph = ph;
+    r.prev = prev;
     // partial tile -> workspace [40][40]
 #pragma unroll
     for (int i = 0; i < NR; i++)
@@ -204,6 +206,7 @@ gram_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     GramRing ring;
     ring.s = 0;
     ring.ph = 0;
+    ring.prev = -1;
     for (int sgi = 0; sgi < nseg; sgi++) {
         const GramJob* jb = sjob + sgi;
         const int niter = (int)((sseg[sgi].k_end - sseg[sgi].k_begin + GRAM_KT - 1) / GRAM_KT);
@@ -224,7 +227,9 @@ gram_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
             GRAM_LOW(2, 1) GRAM_LOW(2, 2) GRAM_LOW(2, 3)
             GRAM_LOW(3, 1) GRAM_LOW(3, 2)
             GRAM_LOW(4, 1)
-        default:  // idle warp: keep the ring moving
+        default:  // idle warp: keep the ring moving (it reads nothing from the stages: immediate release)
+            mbar_release_previous(empty, ring.prev, lane);
+            ring.prev = -1;
             for (int it = 0; it < niter; it++) {
                 mbar_wait(full + ring.s, (uint32_t)ring.ph);
                 __syncwarp();

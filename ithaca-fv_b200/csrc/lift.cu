@@ -105,10 +105,12 @@ lift_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUt
 
     double* mycol = colsum + warp * NB * 8;
     long long it = 0;
+    int prev = -1;   // stage still to be handed back
     for (long long tl = 0; tl < my_tiles; tl++) {
         for (int kk = 0; kk < kiters; kk++, it++) {
             const int s = (int)(it % nstages);
             mbar_wait(&full[s], (uint32_t)(it / nstages) & 1);
+            mbar_release_previous(empty, prev, lane);   // delayed release (common.cuh)
             const unsigned char* pa = smem + (size_t)s * stage_bytes + warp * LIFT_SBOX;
             const double* qs = reinterpret_cast<const double*>(smem + (size_t)s * stage_bytes + 8 * LIFT_SBOX);
 #pragma unroll
@@ -122,8 +124,7 @@ lift_kernel(const __grid_constant__ CUtensorMap tmS, const __grid_constant__ CUt
                     dmma884(acc[1][j][0], acc[1][j][1], a1, b);
                 }
             }
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&empty[s]);
+            prev = s;
         }
         // ---- epilogue of this row tile: store unnormalised modes, accumulate weighted column sums ----
         const long long row0 = ((long long)blockIdx.x + tl * gridDim.x) * LIFT_ROWS + warp * 16;
@@ -228,7 +229,12 @@ static int lift_run(ithaca_b200* h, const LiftSrc& src, int m, double* Phi, int 
     int nstages = std::min(8, (220 * 1024 - fixed) / (stage_bytes + 16));
     // two CTAs per SM when they fit: more loads in flight for the small-r (HBM-bound) case
     int per_sm = 1;
-    if (nstages >= 8) { per_sm = 2; nstages = 4; }
+    if (nstages >= 8) {
+        per_sm = 2;
+        nstages = std::max(4, std::min(8, (113 * 1024 - fixed) / (stage_bytes + 16)));   // (227 KB - 2 x 1 KB reserved) / 2 CTAs
+    }
+    if (const char* e = env_knob("ITHACA_B200_LIFT_PERSM")) { if (atoi(e) == 1 && per_sm == 2) { per_sm = 1; nstages = 8; } }   // A/B
+    if (const char* e = env_knob("ITHACA_B200_LIFT_STAGES")) nstages = std::max(2, std::min(nstages, atoi(e)));
     const size_t smem = (size_t)nstages * (stage_bytes + 16) + fixed;
     IB_CUDA(h, cudaFuncSetAttribute(lift_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int grid = (int)std::min<long long>(ntiles, (long long)per_sm * h->num_sms);

@@ -306,16 +306,17 @@ def test_row_streamed_identities_at_scale(pkg, pod):
             fill(k & 1, c0, nc)
             pod.stream_lift_add(k & 1, r, "L2")
         Phi, nf = pod.stream_lift_finish(r)
-        return G, ev, nf, Phi
+        return G, ev, nf, Phi, Q
 
-    G, ev, nf, Phi = run(90_001)
+    G, ev, nf, Phi, Q = run(90_001)
     assert abs(ev.sum() - np.trace(G)) <= 1e-12 * np.trace(G)
-    assert np.all(np.abs(nf * nf / ev[:r] - 1.0) <= 1e-9)
+    qGq = np.einsum("ij,ij->j", Q[:, :r], G @ Q[:, :r])   # on failure: tells an eigenvector error from a lift / norm error
+    assert np.all(np.abs(nf * nf / ev[:r] - 1.0) <= 1e-9), (np.abs(qGq / ev[:r] - 1).max(), np.abs(nf * nf / qGq - 1).max())
     Vd = torch.zeros(Nc, device=dev, dtype=torch.float64)
     pod.synth_volumes(Vd.data_ptr(), 0, Nc, Nc, seed)
     pod.timings()
     W = np.repeat(Vd.cpu().numpy(), dim)
     assert np.abs(Phi.T @ (W[:, None] * Phi) - np.eye(r)).max() <= 1e-9
-    G1, ev1, nf1, _ = run(Nc)                              # one chunk = the resident arithmetic
+    G1, ev1, nf1, _, _ = run(Nc)                             # one chunk = the resident arithmetic
     assert rel_max(G, G1) <= 1e-13
     assert np.all(np.abs(ev[:r] - ev1[:r]) <= 1e-10 * ev1[:r])
