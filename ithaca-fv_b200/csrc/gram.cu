@@ -106,7 +106,7 @@ __device__ __forceinline__ void gram_run(GramRing& r, int niter, int nstages, in
     int s = r.s, ph = r.ph, prev = r.prev;
     for (int it = 0; it < niter; it++) {
         mbar_wait(full + s, (uint32_t)ph);
-        mbar_release_previous(empty, prev, lane);
+        mbar_release_previous(empty, prev, lane);   // delayed release (common.cuh)
         const unsigned char* st = panels + (size_t)s * stage_bytes;
         const unsigned char* pa = st + a_off;
         const unsigned char* pb = st + b_off;
@@ -687,7 +687,12 @@ int atvb_launch(ithaca_b200* h, const double* A, long long lda, int Ma, const do
 
     const int fixed = maxseg * (int)(sizeof(GramSeg) + sizeof(GramJob)) + 64;
     const int smem_cap = 227 * 1024 - 1024;
-    int nstages = std::min(8, (smem_cap - fixed) / (stage_bytes + GRAM_KT * 8 + 16));
+    // Ring depth: a stage of the big shapes lasts ~2.8 us (1500 DMMAs), far longer than a TMA round trip, so depth buys nothing
+    // there -- and shared memory beyond ~160 KB costs the L1 the job tables, weights and workspace stores go through. Measured
+    // (scripts/gram_sweep.py, 1M cells x 3 x m = 1000): 6 stages (216 KB) 96.2 ms, 5 / 4 / 3 stages 92.6 ms; m = 2000: 190.9 ->
+    // 181.7 ms; m = 200 at C2: 2.91 -> 2.73 ms. Small stages (m = 50: 10 KB, 0.26 ms at >= 4 stages, 0.36 ms at 3) keep up to 8.
+    const int per_stage = stage_bytes + GRAM_KT * 8 + 16;
+    int nstages = std::min((smem_cap - fixed) / per_stage, std::max(4, std::min(8, 160 * 1024 / per_stage)));
     if (const char* e = env_knob("ITHACA_B200_GRAM_STAGES")) nstages = std::max(2, std::min(nstages, atoi(e)));
     if (nstages < 2) { set_error(h, "gram: job does not fit shared memory"); return IB200_ERR_ARG; }
     const size_t smem = (size_t)nstages * (stage_bytes + GRAM_KT * 8 + 16) + fixed;

@@ -6,6 +6,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 import torch
 pkg = importlib.import_module("ithaca-fv_b200")
+if os.environ.get("GRAM_SWEEP_LIB"):
+    pkg.LIB_PATH = os.environ["GRAM_SWEEP_LIB"]   # A/B of two builds on one box
 dev = torch.device("cuda", 0)
 torch.cuda.set_device(0)
 shapes = sys.argv[1:] or ["10000:3:100", "4099:3:37", "2000000:1:200", "250000:3:1000", "100000:1:2000", "400000:3:50"]
