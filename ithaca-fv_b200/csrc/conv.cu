@@ -391,6 +391,7 @@ int conv_fused_launch(ithaca_b200* h, ConvBufs* cb, const ConvMesh& m, long long
     if (rc) return rc;
     const int stage_bytes = CV_KT * 8 * (4 * NP + bp);
     int nstages = std::min(8, (226 * 1024 - 256) / (stage_bytes + 16));
+    if (const char* e = env_knob("ITHACA_B200_CONV_STAGES")) nstages = std::max(2, std::min(nstages, atoi(e)));   // A/B
     if (nstages < 2) { set_error(h, "project(C): too many modes for one pipeline stage"); return IB200_ERR_ARG; }
     const size_t smem = (size_t)nstages * (stage_bytes + 16) + 64;
     auto kern = (CV_KT == 16) ? conv_contract_kernel<16> : conv_contract_kernel<32>;
