@@ -681,9 +681,9 @@ def run_headline(args, env, wl):
                      "algorithmic_flops_per_launch": gram_flops / len(sp.chunks), "kernel_ms_per_launch": gram_kernel_ms / len(sp.chunks),
                      "algorithmic_bytes_per_launch": (8.0 * Nd * m + 8.0 * sp.cells) / len(sp.chunks),
                      "traffic_note": "dram bytes (read + write) of ONE launch over a 60 GB chunk (2.5M cells x 1000 vector snapshots), ncu --set "
-                                     "full, profiles/r2f_pod_full.md: 7.5x the algorithmic bytes -- at m = 1000 the 30 jobs of the lower triangle "
+                                     "full, profiles/r2w_pod_full.md: 6.7x the algorithmic bytes -- at m = 1000 the 31 jobs of the lower triangle "
                                      "re-read their column panels and a 60 GB chunk does not fit the 126 MB L2; the kernel stays tensor-bound "
-                                     "(DRAM 22 % of peak, tensor pipe 88.9 % active)"},
+                                     "(DRAM 21 % of peak, tensor pipe 87.9 % active)"},
         "roofline_lift": {"bound": "tensor" if m >= 1000 else "hbm", "kernel": "lift_kernel", "ms": stages.get("lift"),
                           "GBps": lift_bytes / (stages["lift"] * 1e-3) / 1e9, "frac_hbm": lift_bytes / (stages["lift"] * 1e-3) / 1e9 / hbm_peak,
                           "tflops": lift_flops / (stages["lift"] * 1e-3) / 1e12,
