@@ -320,3 +320,11 @@ def test_row_streamed_identities_at_scale(pkg, pod):
     G1, ev1, nf1, _, _ = run(Nc)                             # one chunk = the resident arithmetic
     assert rel_max(G, G1) <= 1e-13
     assert np.all(np.abs(ev[:r] - ev1[:r]) <= 1e-10 * ev1[:r])
+    # bit-reproducible run to run (fixed summation orders everywhere): the same five-chunk pass three more times. This is the
+    # check that catches a race in the TMA rings -- the stage-release race fixed in round 2 (common.cuh)
+    # put one wrong 8 x 24 fragment into one pass in five at exactly this size
+    for _ in range(3):
+        G2, ev2, nf2, Phi2, _ = run(90_001)
+        assert np.array_equal(G2, G) and np.array_equal(ev2, ev)
+        assert np.array_equal(nf2, nf)
+        assert np.array_equal(Phi2, Phi)
